@@ -1,0 +1,173 @@
+/*
+ * pcp_cuda.h -- C ABI of libpcp_cuda.so: the B200 (sm_100a) replacement for the data-parallel hot path of
+ * RioWong/PointCloudProcess.  Plain pointers and sizes only; every entry point names the reference
+ * interface it replaces (file:line relative to the reference checkout).
+ *
+ * Conventions
+ *   - Every function returns 0 on success, a negative pcp_status on failure; text via pcp_last_error().
+ *   - Points are (base pointer, count, byte stride); the first 24 bytes of a record are x,y,z doubles.
+ *     PointXYZRGBA (point_type.h:9-82) has stride 48 with rgba at byte 32 and stamp_id at byte 36,
+ *     PointC (point_type.h:300-323) stride 64, a packed double[3] array stride 24.
+ *   - Every data pointer may be a HOST pointer (pageable or pinned) or a DEVICE pointer on the context's
+ *     GPU; the library finds out with cudaPointerGetAttributes.  Host buffers are staged through the
+ *     context's own device arena; device buffers are used in place.  All pointers of one call that
+ *     describe outputs may be mixed freely.
+ *   - The caller owns every buffer it passes; the library owns its device arena (freed by pcp_destroy).
+ *   - There is no CPU fallback: without a usable CUDA device pcp_create fails and nothing else works.
+ *   - A pcp_ctx is not thread-safe; a built pcp_index is immutable and may be queried from several host
+ *     threads (calls are serialised on the context's stream by an internal mutex).
+ */
+#ifndef PCP_CUDA_H
+#define PCP_CUDA_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define PCP_API __attribute__((visibility("default")))
+#else
+#define PCP_API
+#endif
+
+typedef struct pcp_ctx pcp_ctx;
+typedef struct pcp_index pcp_index;
+
+typedef enum pcp_status {
+    PCP_OK = 0,
+    PCP_ERR_INVALID = -1, /* bad argument */
+    PCP_ERR_CUDA = -2,    /* CUDA runtime error, see pcp_last_error */
+    PCP_ERR_NOMEM = -3,
+    PCP_ERR_RANGE = -4,   /* value not representable (e.g. > 2^31-1 points, voxel grid wider than 2^21) */
+    PCP_ERR_NCCL = -5
+} pcp_status;
+
+/* LAS_POINT_PROPERTY, data_struct.h:161-173.  48 bytes. */
+typedef struct pcp_point_property {
+    float normal_x, normal_y, normal_z;
+    double Distance;
+    double curvature;
+    int32_t PointID;
+    int32_t SegmentID;
+    float dis_from_point_plane;
+} pcp_point_property;
+
+/* PlanSegment (data_struct.h:188-198) without its std::vector member, + the three eigenvalues. */
+typedef struct pcp_plan_segment {
+    float normal_x, normal_y, normal_z;
+    float min_value; /* lambda3 */
+    float curvature;
+    float Distance;
+    double eig[3]; /* lambda1 >= lambda2 >= lambda3 of the un-normalised scatter X*X^T */
+} pcp_plan_segment;
+
+/* ---- context ------------------------------------------------------------------------------------ */
+PCP_API int pcp_create(pcp_ctx** out, int cuda_device);
+PCP_API void pcp_destroy(pcp_ctx* ctx);
+PCP_API const char* pcp_last_error(const pcp_ctx* ctx); /* ctx may be NULL: error of a failed pcp_create */
+/* Run on a caller-owned stream (a cudaStream_t passed as void*); NULL restores the context's own stream. */
+PCP_API int pcp_set_stream(pcp_ctx* ctx, void* cuda_stream);
+PCP_API int pcp_synchronize(pcp_ctx* ctx);
+PCP_API int pcp_device_count(void);
+PCP_API const char* pcp_version(void);
+/* Release cached arena blocks back to the driver. */
+PCP_API int pcp_trim(pcp_ctx* ctx);
+
+/* Stage timing: when enabled the library brackets each kernel stage with CUDA events on its stream.
+ * pcp_profile_get copies up to cap entries (name, accumulated ms, launches) recorded since the last
+ * pcp_profile_reset and returns the number of stages via *n. */
+typedef struct pcp_stage_time {
+    char name[48];
+    double ms;
+    int64_t launches;
+    double bytes; /* algorithmic bytes attributed to the stage (0 if not applicable) */
+} pcp_stage_time;
+PCP_API int pcp_profile_enable(pcp_ctx* ctx, int on);
+PCP_API int pcp_profile_reset(pcp_ctx* ctx);
+PCP_API int pcp_profile_get(pcp_ctx* ctx, pcp_stage_time* out, int cap, int* n);
+/* Number of kernels launched by this context since creation (bench.py's gpu_launches). */
+PCP_API int64_t pcp_launch_count(const pcp_ctx* ctx);
+
+/* Raw device / pinned-host memory for callers that keep clouds resident between calls. */
+PCP_API int pcp_dev_alloc(pcp_ctx* ctx, size_t bytes, void** dptr);
+PCP_API int pcp_dev_free(pcp_ctx* ctx, void* dptr);
+PCP_API int pcp_host_alloc_pinned(pcp_ctx* ctx, size_t bytes, void** hptr);
+PCP_API int pcp_host_free_pinned(pcp_ctx* ctx, void* hptr);
+PCP_API int pcp_memcpy(pcp_ctx* ctx, void* dst, const void* src, size_t bytes); /* any direction, synchronous */
+
+/* ---- search structure ------------------------------------------------------------------------------
+ * Replaces KdTreeFLANN<PointT>::setInputCloud + convertCloudToArray (kd_tree.h:772-798, 928-956):
+ * non-finite points are dropped and results carry ORIGINAL cloud indices.  The FLANN kd-tree is replaced
+ * by Morton-sorted points with per-level cell tables.  cell_size <= 0 picks the base cell from the data. */
+PCP_API int pcp_index_build(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double cell_size,
+                            pcp_index** out);
+PCP_API void pcp_index_free(pcp_index* index);
+PCP_API int64_t pcp_index_size(const pcp_index* index);      /* valid (finite) points, total_nr_points_ */
+PCP_API double pcp_index_cell_size(const pcp_index* index);
+
+/* KdTreeFLANN::nearestKSearch (kd_tree.h:814-845) for nq query points at once.
+ * idx: nq*k original indices ascending by (d2, index), padded with -1; d2: nq*k squared distances
+ * (L2_Simple order x,y,z, no FMA) padded with +inf, or NULL; found: nq counts (= min(k, valid)), or NULL. */
+PCP_API int pcp_knn(const pcp_index* index, const void* q, size_t nq, size_t qstride, int k, int32_t* idx,
+                    double* d2, int32_t* found);
+
+/* KdTreeFLANN::radiusSearch (kd_tree.h:863-903): strict d2 < r*r, sorted ascending by (d2, index),
+ * capped at max_nn (0 or > valid = unlimited).  Two calls: count fills offsets[nq+1] (exclusive prefix
+ * sums), fill writes idx / d2 (d2 may be NULL) at those offsets. */
+PCP_API int pcp_radius_count(const pcp_index* index, const void* q, size_t nq, size_t qstride, double r,
+                             uint32_t max_nn, int64_t* offsets);
+PCP_API int pcp_radius_fill(const pcp_index* index, const void* q, size_t nq, size_t qstride, double r,
+                            uint32_t max_nn, const int64_t* offsets, int32_t* idx, double* d2);
+
+/* ---- features --------------------------------------------------------------------------------------
+ * The deterministic per-point feature pass the reference declares but never defines,
+ * CalculateFeature::calculate_plan_parameter(CloudPtr, double radius) (calculate_feature.h:15):
+ * for every cloud point j (in original order) neighbours = nearestKSearch(point j, k) -- self included,
+ * as at calculate_feature.cpp:230-233 -- then calculate_plan_parameter_h_points on them
+ * (calculate_feature.cpp:119-206) and the N<=3 fallback of calculate_feature.cpp:356-363.
+ * props: n records of pcp_point_property for the ORIGINAL n points (dropped points get the fallback).
+ * eig3 (n*3 doubles lambda1>=lambda2>=lambda3), lps3 (n*3 floats linearity, planarity, scattering =
+ * (l1-l2)/l1, (l2-l3)/l1, l3/l1), knn_idx (n*k) are optional (NULL). */
+PCP_API int pcp_features_knn(const pcp_index* index, int k, void* props, double* eig3, float* lps3,
+                             int32_t* knn_idx);
+/* Same with radius neighbourhoods (strict d2 < r*r, max_nn as above); counts (n) optional. */
+PCP_API int pcp_features_radius(const pcp_index* index, double r, uint32_t max_nn, void* props, double* eig3,
+                                float* lps3, int32_t* counts);
+
+/* CalculateFeature::calculate_plan_parameter_h_points (calculate_feature.cpp:119-206) for nseg segments:
+ * segment s is the points [seg_offsets[s], seg_offsets[s+1]) of pts. */
+PCP_API int pcp_plane_fit(pcp_ctx* ctx, const void* pts, size_t stride, const int64_t* seg_offsets,
+                          size_t nseg, pcp_plan_segment* out);
+
+/* ---- voxel grid ------------------------------------------------------------------------------------
+ * VoxelGrid<PointXYZRGBA>::applyFilter (voxel_grid.h:811-1056, no field filter) incl. its numerics:
+ * truncating cell index, DBL_MIN max seed, float-rounded field sums in double, rgb re-pack.
+ * out_pts: capacity n records of `stride` bytes; *m receives the number of occupied cells; output is in
+ * ascending (k,j,i) cell order.  min_b/div_b (3 ints each), point_cell (n*3: cell of every input point,
+ * -1 for dropped points), cell_count (capacity n) are optional.  Non-finite points are always dropped. */
+PCP_API int pcp_voxel_grid(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, const double leaf[3],
+                           int downsample_all, void* out_pts, size_t* m, int32_t min_b[3], int32_t div_b[3],
+                           int32_t* point_cell, int32_t* cell_count);
+
+/* PointCloudHelper::remove_duplicate (point_cloud_helper.cpp:42-63): centre on the serial-order centroid
+ * (point_cloud_helper.h:192-230, reproduced bit-exactly), voxel grid with a float leaf, un-centre.
+ * In place: pts_inout holds *n_inout records on entry and the filtered cloud on return. */
+PCP_API int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf);
+
+/* compute3DCentroid (point_cloud_helper.h:192-230) and getMinMax3D (point_cloud_helper.h:59-90). */
+PCP_API int pcp_centroid(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double c[3], uint64_t* count);
+PCP_API int pcp_minmax(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double mn[3], double mx[3]);
+
+/* ---- synthetic clouds (bench / tests) ----------------------------------------------------
+ * Fills n PointXYZRGBA records (stride 48) of the named kind; point i is a pure function of
+ * (kind, n_total, seed, first + i).  kind: 0 uniform_cube, 1 strip, 2 forest, 3 city, 4 lattice.
+ * centred != 0 omits the UTM-scale world offset. */
+PCP_API int pcp_synth_cloud(pcp_ctx* ctx, int kind, uint64_t n_total, uint64_t first, uint64_t n, uint64_t seed,
+                            int centred, void* out_pts);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

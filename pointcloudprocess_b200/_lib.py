@@ -1,0 +1,89 @@
+"""ctypes binding of libpcp_cuda.so (include/pcp_cuda.h).  There is no CPU fallback: if the shared library
+is missing or no CUDA device is usable, every entry point raises."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpcp_cuda.so")
+
+# every symbol include/pcp_cuda.h declares (checked by tests/test_abi.py against the header text)
+SYMBOLS = [
+    "pcp_create", "pcp_destroy", "pcp_last_error", "pcp_set_stream", "pcp_synchronize", "pcp_device_count",
+    "pcp_version", "pcp_trim", "pcp_profile_enable", "pcp_profile_reset", "pcp_profile_get", "pcp_launch_count",
+    "pcp_dev_alloc", "pcp_dev_free", "pcp_host_alloc_pinned", "pcp_host_free_pinned", "pcp_memcpy",
+    "pcp_index_build", "pcp_index_free", "pcp_index_size", "pcp_index_cell_size", "pcp_knn", "pcp_radius_count",
+    "pcp_radius_fill", "pcp_features_knn", "pcp_features_radius", "pcp_plane_fit", "pcp_voxel_grid",
+    "pcp_remove_duplicate", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
+]
+
+
+class StageTime(C.Structure):
+    _fields_ = [("name", C.c_char * 48), ("ms", C.c_double), ("launches", C.c_int64), ("bytes", C.c_double)]
+
+
+class PcpError(RuntimeError):
+    def __init__(self, status, msg):
+        super().__init__("pcp status %d: %s" % (status, msg))
+        self.status = status
+
+
+_lib = None
+
+
+def load():
+    """Load the shared library (no CUDA call is made here)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise PcpError(-2, "libpcp_cuda.so is not built (run `python -m pointcloudprocess_b200.build` or "
+                           "__graft_entry__.build()); there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, sz, i32, i64, u32, u64, dbl = C.c_void_p, C.c_size_t, C.c_int, C.c_int64, C.c_uint32, C.c_uint64, C.c_double
+    pp = C.POINTER(C.c_void_p)
+    sig = {
+        "pcp_create": (i32, [pp, i32]),
+        "pcp_destroy": (None, [vp]),
+        "pcp_last_error": (C.c_char_p, [vp]),
+        "pcp_set_stream": (i32, [vp, vp]),
+        "pcp_synchronize": (i32, [vp]),
+        "pcp_device_count": (i32, []),
+        "pcp_version": (C.c_char_p, []),
+        "pcp_trim": (i32, [vp]),
+        "pcp_profile_enable": (i32, [vp, i32]),
+        "pcp_profile_reset": (i32, [vp]),
+        "pcp_profile_get": (i32, [vp, C.POINTER(StageTime), i32, C.POINTER(i32)]),
+        "pcp_launch_count": (i64, [vp]),
+        "pcp_dev_alloc": (i32, [vp, sz, pp]),
+        "pcp_dev_free": (i32, [vp, vp]),
+        "pcp_host_alloc_pinned": (i32, [vp, sz, pp]),
+        "pcp_host_free_pinned": (i32, [vp, vp]),
+        "pcp_memcpy": (i32, [vp, vp, vp, sz]),
+        "pcp_index_build": (i32, [vp, vp, sz, sz, dbl, pp]),
+        "pcp_index_free": (None, [vp]),
+        "pcp_index_size": (i64, [vp]),
+        "pcp_index_cell_size": (dbl, [vp]),
+        "pcp_knn": (i32, [vp, vp, sz, sz, i32, vp, vp, vp]),
+        "pcp_radius_count": (i32, [vp, vp, sz, sz, dbl, u32, vp]),
+        "pcp_radius_fill": (i32, [vp, vp, sz, sz, dbl, u32, vp, vp, vp]),
+        "pcp_features_knn": (i32, [vp, i32, vp, vp, vp, vp]),
+        "pcp_features_radius": (i32, [vp, dbl, u32, vp, vp, vp, vp]),
+        "pcp_plane_fit": (i32, [vp, vp, sz, vp, sz, vp]),
+        "pcp_voxel_grid": (i32, [vp, vp, sz, sz, vp, i32, vp, C.POINTER(sz), vp, vp, vp, vp]),
+        "pcp_remove_duplicate": (i32, [vp, vp, C.POINTER(sz), sz, C.c_float]),
+        "pcp_centroid": (i32, [vp, vp, sz, sz, vp, C.POINTER(u64)]),
+        "pcp_minmax": (i32, [vp, vp, sz, sz, vp, vp]),
+        "pcp_synth_cloud": (i32, [vp, i32, u64, u64, u64, u64, i32, vp]),
+    }
+    for name, (res, args) in sig.items():
+        f = getattr(L, name)  # AttributeError here = the .so does not export what the header declares
+        f.restype = res
+        f.argtypes = args
+    _lib = L
+    return L
+
+
+def check(ctx_handle, status):
+    if status != 0:
+        msg = load().pcp_last_error(ctx_handle)
+        raise PcpError(status, msg.decode("utf-8", "replace") if msg else "")

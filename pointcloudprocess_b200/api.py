@@ -1,0 +1,461 @@
+"""Host-side mirror of the reference's interface for the hot path, over the C ABI (include/pcp_cuda.h).
+
+Names, argument meaning and return conventions follow the reference classes:
+  KdTreeFLANN          kd_tree.h:772-903       setInputCloud / nearestKSearch / radiusSearch
+  VoxelGrid            voxel_grid.h:482-773    setInputCloud / setLeafSize / setDownsampleAllData / filter
+  CalculateFeature     calculate_feature.h:11-16
+  PointCloudHelper     point_cloud_helper.h:16-90,192-230   remove_duplicate / getMinMax3D / compute3DCentroid
+Clouds are numpy structured arrays of POINT_DTYPE (PointXYZRGBA, point_type.h:9-82) on the host, or
+DeviceArray handles for data that stays in HBM.  All compute happens in libpcp_cuda.so on the GPU.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+
+POINT_DTYPE = np.dtype(
+    {"names": ["x", "y", "z", "w", "rgba", "stamp_id"],
+     "formats": ["<f8", "<f8", "<f8", "<f8", "<u4", "<u4"],
+     "offsets": [0, 8, 16, 24, 32, 36], "itemsize": 48})
+PROP_DTYPE = np.dtype(
+    {"names": ["normal_x", "normal_y", "normal_z", "Distance", "curvature", "PointID", "SegmentID",
+               "dis_from_point_plane"],
+     "formats": ["<f4", "<f4", "<f4", "<f8", "<f8", "<i4", "<i4", "<f4"],
+     "offsets": [0, 4, 8, 16, 24, 32, 36, 40], "itemsize": 48})
+PLAN_DTYPE = np.dtype(
+    {"names": ["normal_x", "normal_y", "normal_z", "min_value", "curvature", "Distance", "eig"],
+     "formats": ["<f4", "<f4", "<f4", "<f4", "<f4", "<f4", ("<f8", (3,))],
+     "offsets": [0, 4, 8, 12, 16, 20, 24], "itemsize": 48})
+
+SYNTH_KINDS = {"uniform_cube": 0, "strip": 1, "forest": 2, "city": 3, "lattice": 4}
+
+
+def make_cloud(xyz, rgba=None, stamp_id=None):
+    xyz = np.asarray(xyz, dtype=np.float64)
+    c = np.zeros(xyz.shape[0], dtype=POINT_DTYPE)
+    c["x"], c["y"], c["z"], c["w"] = xyz[:, 0], xyz[:, 1], xyz[:, 2], 1.0
+    if rgba is not None:
+        c["rgba"] = rgba
+    if stamp_id is not None:
+        c["stamp_id"] = stamp_id
+    return c
+
+
+class DeviceArray:
+    """A device allocation owned by the library (pcp_dev_alloc)."""
+
+    def __init__(self, ctx, nbytes):
+        self.ctx, self.nbytes = ctx, int(nbytes)
+        p = C.c_void_p()
+        ctx._check(ctx.L.pcp_dev_alloc(ctx.h, max(self.nbytes, 1), C.byref(p)))
+        self.ptr = p.value
+
+    def free(self):
+        if self.ptr:
+            self.ctx.L.pcp_dev_free(self.ctx.h, self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def to_host(self, dtype, count=None):
+        dtype = np.dtype(dtype)
+        n = self.nbytes // dtype.itemsize if count is None else count
+        out = np.empty(n, dtype=dtype)
+        self.ctx.memcpy(out.ctypes.data, self.ptr, n * dtype.itemsize)
+        return out
+
+    def from_host(self, arr):
+        arr = np.ascontiguousarray(arr)
+        assert arr.nbytes <= self.nbytes
+        self.ctx.memcpy(self.ptr, arr.ctypes.data, arr.nbytes)
+
+
+def _ptr(a):
+    """numpy array / DeviceArray / int address / None -> c_void_p value"""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    if isinstance(a, DeviceArray):
+        return a.ptr
+    return int(a)
+
+
+def _pts(a):
+    """(pointer, count, stride) of a cloud given as POINT_DTYPE array, (n,>=3) float64 array or
+    (ptr, n, stride) tuple of a device buffer."""
+    if isinstance(a, tuple):
+        p, n, s = a
+        return _ptr(p), int(n), int(s), None
+    a = np.ascontiguousarray(a)
+    if a.dtype.names:
+        return a.ctypes.data, a.shape[0], a.dtype.itemsize, a
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    if a.ndim == 1:
+        a = a.reshape(1, -1)
+    assert a.shape[1] >= 3
+    return a.ctypes.data, a.shape[0], a.strides[0], a
+
+
+class Context:
+    """pcp_ctx: one per GPU."""
+
+    def __init__(self, device=0):
+        self.L = _lib.load()
+        h = C.c_void_p()
+        st = self.L.pcp_create(C.byref(h), int(device))
+        if st != 0:
+            msg = self.L.pcp_last_error(None)
+            raise _lib.PcpError(st, msg.decode() if msg else "")
+        self.h = h
+        self.device = device
+
+    def _check(self, st):
+        _lib.check(self.h, st)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.pcp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream):
+        self._check(self.L.pcp_set_stream(self.h, cuda_stream))
+
+    def synchronize(self):
+        self._check(self.L.pcp_synchronize(self.h))
+
+    def memcpy(self, dst, src, nbytes):
+        self._check(self.L.pcp_memcpy(self.h, _ptr(dst), _ptr(src), int(nbytes)))
+
+    def alloc(self, nbytes):
+        return DeviceArray(self, nbytes)
+
+    def pinned(self, nbytes, dtype=np.uint8):
+        """numpy view over cudaHostAlloc memory (freed with free_pinned)."""
+        p = C.c_void_p()
+        self._check(self.L.pcp_host_alloc_pinned(self.h, int(nbytes), C.byref(p)))
+        buf = (C.c_uint8 * int(nbytes)).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=np.uint8).view(dtype)
+        arr_ptr = p.value
+        return arr, arr_ptr
+
+    def free_pinned(self, ptr):
+        self._check(self.L.pcp_host_free_pinned(self.h, ptr))
+
+    def profile(self, on=True):
+        self._check(self.L.pcp_profile_enable(self.h, int(on)))
+
+    def profile_reset(self):
+        self._check(self.L.pcp_profile_reset(self.h))
+
+    def profile_get(self):
+        arr = (_lib.StageTime * 64)()
+        n = C.c_int(0)
+        self._check(self.L.pcp_profile_get(self.h, arr, 64, C.byref(n)))
+        return [{"name": arr[i].name.decode(), "ms": arr[i].ms, "launches": arr[i].launches, "bytes": arr[i].bytes}
+                for i in range(min(n.value, 64))]
+
+    def launch_count(self):
+        return int(self.L.pcp_launch_count(self.h))
+
+    def trim(self):
+        self._check(self.L.pcp_trim(self.h))
+
+    # ---- raw entry points (host or device pointers) ----
+    def synth_cloud(self, kind, n_total, first=0, n=None, seed=1, centred=False, out=None):
+        n = n_total - first if n is None else n
+        kind = SYNTH_KINDS[kind] if isinstance(kind, str) else kind
+        ret = None
+        if out is None:
+            ret = np.zeros(n, dtype=POINT_DTYPE)
+            out = ret
+        self._check(self.L.pcp_synth_cloud(self.h, kind, n_total, first, n, seed, int(centred), _ptr(out)))
+        return ret
+
+    def voxel_grid(self, cloud, leaf, downsample_all=True, out=None, want_cells=False):
+        p, n, s, keep = _pts(cloud)
+        leaf3 = np.array([leaf] * 3 if np.isscalar(leaf) else leaf, dtype=np.float64)
+        host_out = out is None
+        if host_out:
+            out = np.zeros(max(n, 1), dtype=POINT_DTYPE if s == 48 else np.dtype((np.void, s)))
+        m = C.c_size_t(0)
+        min_b = np.zeros(3, dtype=np.int32)
+        div_b = np.zeros(3, dtype=np.int32)
+        cell = np.zeros((max(n, 1), 3), dtype=np.int32) if want_cells else None
+        cnt = np.zeros(max(n, 1), dtype=np.int32) if want_cells else None
+        self._check(self.L.pcp_voxel_grid(self.h, p, n, s, leaf3.ctypes.data, int(downsample_all), _ptr(out),
+                                          C.byref(m), min_b.ctypes.data, div_b.ctypes.data, _ptr(cell), _ptr(cnt)))
+        res = {"m": m.value, "min_b": min_b, "div_b": div_b}
+        if host_out:
+            res["points"] = out[:m.value]
+        if want_cells:
+            res["point_cell"] = cell[:n]
+            res["cell_count"] = cnt[:m.value]
+        return res
+
+    def remove_duplicate(self, cloud, leaf):
+        """In place on a (ptr, n, stride) device tuple (returns m) or on a copy of a host array (returns array)."""
+        if isinstance(cloud, tuple):
+            p, n, s, _ = _pts(cloud)
+            nn = C.c_size_t(n)
+            self._check(self.L.pcp_remove_duplicate(self.h, p, C.byref(nn), s, C.c_float(leaf)))
+            return nn.value
+        a = np.array(cloud, copy=True)
+        nn = C.c_size_t(a.shape[0])
+        self._check(self.L.pcp_remove_duplicate(self.h, a.ctypes.data, C.byref(nn), a.dtype.itemsize, C.c_float(leaf)))
+        return a[:nn.value].copy()
+
+    def centroid(self, cloud):
+        p, n, s, keep = _pts(cloud)
+        c = np.zeros(3)
+        cnt = C.c_uint64(0)
+        self._check(self.L.pcp_centroid(self.h, p, n, s, c.ctypes.data, C.byref(cnt)))
+        return c, cnt.value
+
+    def minmax(self, cloud):
+        p, n, s, keep = _pts(cloud)
+        mn, mx = np.zeros(3), np.zeros(3)
+        self._check(self.L.pcp_minmax(self.h, p, n, s, mn.ctypes.data, mx.ctypes.data))
+        return mn, mx
+
+    def plane_fit(self, pts, seg_offsets):
+        p, n, s, keep = _pts(pts)
+        off = np.ascontiguousarray(seg_offsets, dtype=np.int64)
+        out = np.zeros(off.shape[0] - 1, dtype=PLAN_DTYPE)
+        self._check(self.L.pcp_plane_fit(self.h, p, s, off.ctypes.data, off.shape[0] - 1, out.ctypes.data))
+        return out
+
+
+class Index:
+    """pcp_index: the search structure built by KdTreeFLANN.setInputCloud."""
+
+    def __init__(self, ctx, cloud, cell_size=0.0):
+        self.ctx = ctx
+        p, n, s, keep = _pts(cloud)
+        self.n_orig = n
+        h = C.c_void_p()
+        ctx._check(ctx.L.pcp_index_build(ctx.h, p, n, s, float(cell_size), C.byref(h)))
+        self.h = h
+
+    def free(self):
+        if getattr(self, "h", None) and self.ctx.h:
+            self.ctx.L.pcp_index_free(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+    def size(self):
+        return int(self.ctx.L.pcp_index_size(self.h))
+
+    def cell_size(self):
+        return float(self.ctx.L.pcp_index_cell_size(self.h))
+
+    def knn(self, queries, k, want_d2=True):
+        p, nq, s, keep = _pts(queries)
+        idx = np.empty((nq, k), dtype=np.int32)
+        d2 = np.empty((nq, k), dtype=np.float64) if want_d2 else None
+        found = np.empty(nq, dtype=np.int32)
+        self.ctx._check(self.ctx.L.pcp_knn(self.h, p, nq, s, k, idx.ctypes.data, _ptr(d2), found.ctypes.data))
+        return idx, d2, found
+
+    def radius(self, queries, r, max_nn=0):
+        p, nq, s, keep = _pts(queries)
+        off = np.zeros(nq + 1, dtype=np.int64)
+        self.ctx._check(self.ctx.L.pcp_radius_count(self.h, p, nq, s, float(r), max_nn, off.ctypes.data))
+        idx = np.empty(off[-1], dtype=np.int32)
+        d2 = np.empty(off[-1], dtype=np.float64)
+        self.ctx._check(self.ctx.L.pcp_radius_fill(self.h, p, nq, s, float(r), max_nn, off.ctypes.data,
+                                                   idx.ctypes.data, d2.ctypes.data))
+        return off, idx, d2
+
+    def features_knn(self, k, props=None, eig=None, lps=None, knn_idx=None, want_eig=True, want_lps=True,
+                     want_idx=False):
+        """Host outputs are allocated unless device pointers are passed in."""
+        n = self.n_orig
+        ret = {}
+        if props is None:
+            props = ret["props"] = np.zeros(n, dtype=PROP_DTYPE)
+        if eig is None and want_eig:
+            eig = ret["eig"] = np.zeros((n, 3))
+        if lps is None and want_lps:
+            lps = ret["lps"] = np.zeros((n, 3), dtype=np.float32)
+        if knn_idx is None and want_idx:
+            knn_idx = ret["knn_idx"] = np.empty((n, k), dtype=np.int32)
+        self.ctx._check(self.ctx.L.pcp_features_knn(self.h, k, _ptr(props), _ptr(eig), _ptr(lps), _ptr(knn_idx)))
+        return ret
+
+    def features_radius(self, r, max_nn=0, props=None, eig=None, lps=None, counts=None, want_extra=True):
+        n = self.n_orig
+        ret = {}
+        if props is None:
+            props = ret["props"] = np.zeros(n, dtype=PROP_DTYPE)
+        if want_extra:
+            if eig is None:
+                eig = ret["eig"] = np.zeros((n, 3))
+            if lps is None:
+                lps = ret["lps"] = np.zeros((n, 3), dtype=np.float32)
+            if counts is None:
+                counts = ret["counts"] = np.zeros(n, dtype=np.int32)
+        self.ctx._check(self.ctx.L.pcp_features_radius(self.h, float(r), max_nn, _ptr(props), _ptr(eig), _ptr(lps),
+                                                       _ptr(counts)))
+        return ret
+
+
+# ---- reference-shaped classes ------------------------------------------------------------------------
+_default_ctx = None
+
+
+def default_context():
+    global _default_ctx
+    if _default_ctx is None:
+        _default_ctx = Context(0)
+    return _default_ctx
+
+
+class PointCloud:
+    """point_cloud.h:54-535: points + width/height/is_dense."""
+
+    def __init__(self, points=None):
+        self.points = np.zeros(0, dtype=POINT_DTYPE) if points is None else points
+        self.height = 1
+        self.is_dense = True
+
+    @property
+    def width(self):
+        return len(self.points)
+
+    def size(self):
+        return len(self.points)
+
+    def push_back(self, x, y, z, rgba=0, stamp_id=0):
+        p = np.zeros(1, dtype=POINT_DTYPE)
+        p["x"], p["y"], p["z"], p["w"], p["rgba"], p["stamp_id"] = x, y, z, 1.0, rgba, stamp_id
+        self.points = np.concatenate([self.points, p])
+
+
+class KdTreeFLANN:
+    def __init__(self, ctx=None, sorted=True):
+        self.ctx = ctx or default_context()
+        self.index = None
+
+    def setInputCloud(self, cloud):
+        pts = cloud.points if isinstance(cloud, PointCloud) else cloud
+        self.index = Index(self.ctx, pts)
+
+    def nearestKSearch(self, point, k):
+        """-> (count, k_indices, k_sqr_distances); k is clamped to the number of valid points (kd_tree.h:820)."""
+        q = np.array([[point["x"], point["y"], point["z"]]]) if hasattr(point, "dtype") and point.dtype.names \
+            else np.asarray(point, dtype=np.float64).reshape(1, -1)
+        kk = min(k, self.index.size())
+        if kk <= 0:
+            return 0, np.zeros(0, np.int32), np.zeros(0)
+        idx, d2, found = self.index.knn(q, kk)
+        return int(found[0]), idx[0, :found[0]].copy(), d2[0, :found[0]].copy()
+
+    def radiusSearch(self, point, radius, max_nn=0):
+        q = np.array([[point["x"], point["y"], point["z"]]]) if hasattr(point, "dtype") and point.dtype.names \
+            else np.asarray(point, dtype=np.float64).reshape(1, -1)
+        off, idx, d2 = self.index.radius(q, radius, max_nn)
+        return int(off[1]), idx, d2
+
+
+class VoxelGrid:
+    def __init__(self, ctx=None):
+        self.ctx = ctx or default_context()
+        self.input = None
+        self.leaf = None
+        self.downsample_all_data = True  # voxel_grid.h:499
+        self.min_b = self.div_b = None
+
+    def setInputCloud(self, cloud):
+        self.input = cloud
+
+    def setLeafSize(self, lx, ly, lz):
+        self.leaf = (float(lx), float(ly), float(lz))
+
+    def setDownsampleAllData(self, flag):
+        self.downsample_all_data = bool(flag)
+
+    def getMinBoxCoordinates(self):
+        return self.min_b
+
+    def getNrDivisions(self):
+        return self.div_b
+
+    def filter(self):
+        out = PointCloud()
+        if self.input is None:  # voxel_grid.h:815-821
+            print("[applyFilter] No input dataset given")
+            return out
+        pts = self.input.points if isinstance(self.input, PointCloud) else self.input
+        r = self.ctx.voxel_grid(pts, self.leaf, self.downsample_all_data)
+        self.min_b, self.div_b = r["min_b"], r["div_b"]
+        out.points = r["points"].copy()
+        return out
+
+
+class CalculateFeature:
+    def __init__(self, ctx=None):
+        self.ctx = ctx or default_context()
+
+    def calculate_plan_parameter_h_points(self, cloud):
+        pts = cloud.points if isinstance(cloud, PointCloud) else cloud
+        n = len(pts)
+        return self.ctx.plane_fit(pts, [0, n])[0]
+
+    def calculate_plan_parameter(self, cloud, radius=None, k=20):
+        """calculate_feature.h:15 (declared, never defined in the reference): kNN(k) plane fit per point,
+        or radius neighbourhoods when `radius` is given."""
+        pts = cloud.points if isinstance(cloud, PointCloud) else cloud
+        ix = Index(self.ctx, pts)
+        try:
+            if radius is None:
+                return ix.features_knn(k, want_eig=False, want_lps=False)["props"]
+            return ix.features_radius(radius, want_extra=False)["props"]
+        finally:
+            ix.free()
+
+    def calculate_plan_parameter_rpca(self, cloud, radius, pr=0.99, epi=0.5):
+        """Signature of calculate_feature.cpp:208; like the reference it ignores `radius` and uses k = 20
+        (:233).  The randomised hypothesis loop is not reproduced (it is not reproducible run to run in the
+        reference either, :210,:249); this is the deterministic plain-PCA result on the 20 neighbours."""
+        return self.calculate_plan_parameter(cloud, None, 20)
+
+
+class PointCloudHelper:
+    @staticmethod
+    def remove_duplicate(cloud, voxel_grid_size, min_num=None, ctx=None):
+        ctx = ctx or default_context()
+        pts = cloud.points if isinstance(cloud, PointCloud) else cloud
+        out = ctx.remove_duplicate(pts, np.float32(voxel_grid_size))
+        if min_num is not None and len(out) < min_num:  # point_cloud_helper.cpp:65-73
+            out = pts
+        if isinstance(cloud, PointCloud):
+            cloud.points = out
+            return cloud
+        return out
+
+    @staticmethod
+    def getMinMax3D(cloud, ctx=None):
+        ctx = ctx or default_context()
+        return ctx.minmax(cloud.points if isinstance(cloud, PointCloud) else cloud)
+
+    @staticmethod
+    def compute3DCentroid(cloud, ctx=None):
+        ctx = ctx or default_context()
+        return ctx.centroid(cloud.points if isinstance(cloud, PointCloud) else cloud)

@@ -1,0 +1,146 @@
+// common.cuh -- context, stream-ordered arena, host/device pointer staging, stage timing.
+// Internal to libpcp_cuda.so; the public surface is include/pcp_cuda.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/pcp_cuda.h"
+
+#define PCP_SM_COUNT_B200 148
+
+struct pcp_stage_rec {
+    std::string name;
+    double ms = 0;
+    int64_t launches = 0;
+    double bytes = 0;
+};
+
+struct pcp_ctx {
+    int device = 0;
+    int sm_count = PCP_SM_COUNT_B200;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    cudaMemPool_t pool = nullptr;
+    std::string err;
+    std::mutex mu;
+    bool profile = false;
+    std::vector<pcp_stage_rec> stages;
+    int64_t launches = 0;
+    // pending stage events (resolved lazily at pcp_profile_get / next sync)
+    struct pending_ev {
+        int stage;
+        cudaEvent_t a, b;
+    };
+    std::vector<pending_ev> pending;
+    std::vector<cudaEvent_t> ev_free;
+};
+
+int pcp_fail(pcp_ctx* ctx, int code, const char* fmt, ...);
+void pcp_set_global_error(const char* msg);
+
+#define PCP_CUDA_TRY(ctx, expr)                                                                              \
+    do {                                                                                                     \
+        cudaError_t _e = (expr);                                                                             \
+        if (_e != cudaSuccess)                                                                               \
+            return pcp_fail((ctx), PCP_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),     \
+                            __FILE__, __LINE__);                                                             \
+    } while (0)
+
+#define PCP_TRY(expr)                                                                                        \
+    do {                                                                                                     \
+        int _s = (expr);                                                                                     \
+        if (_s != PCP_OK) return _s;                                                                         \
+    } while (0)
+
+// after a kernel launch
+#define PCP_LAUNCH_CHECK(ctx)                                                                                \
+    do {                                                                                                     \
+        (ctx)->launches++;                                                                                   \
+        PCP_CUDA_TRY((ctx), cudaGetLastError());                                                             \
+    } while (0)
+
+// ---- stream-ordered arena ----------------------------------------------------------------------------
+int pcp_arena_alloc(pcp_ctx* ctx, size_t bytes, void** out);
+void pcp_arena_free(pcp_ctx* ctx, void* p);
+
+// RAII device buffer from the arena (freed stream-ordered at scope exit)
+template <typename T> struct DevBuf {
+    pcp_ctx* ctx = nullptr;
+    T* p = nullptr;
+    size_t n = 0;
+    DevBuf() {}
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    ~DevBuf() { release(); }
+    int alloc(pcp_ctx* c, size_t count)
+    {
+        release();
+        ctx = c;
+        n = count;
+        void* q = nullptr;
+        int s = pcp_arena_alloc(c, (count ? count : 1) * sizeof(T), &q);
+        p = static_cast<T*>(q);
+        return s;
+    }
+    void release()
+    {
+        if (p) pcp_arena_free(ctx, p);
+        p = nullptr;
+        n = 0;
+    }
+    T* detach()
+    {
+        T* q = p;
+        p = nullptr;
+        return q;
+    }
+};
+
+// ---- pointer staging -----------------------------------------------------------------------------------
+enum pcp_ptr_kind { PCP_PTR_HOST = 0, PCP_PTR_DEVICE = 1, PCP_PTR_BAD = 2 };
+pcp_ptr_kind pcp_classify(pcp_ctx* ctx, const void* p);
+
+// Input that must be readable on the device: device pointers pass through, host data is copied in.
+struct InStage {
+    pcp_ctx* ctx = nullptr;
+    const void* dptr = nullptr;
+    void* owned = nullptr;
+    ~InStage()
+    {
+        if (owned) pcp_arena_free(ctx, owned);
+    }
+    int open(pcp_ctx* c, const void* p, size_t bytes);
+};
+
+// Output written on the device: device pointers are written in place, host outputs get a device
+// scratch that commit() copies back (synchronises the stream).
+struct OutStage {
+    pcp_ctx* ctx = nullptr;
+    void* user = nullptr;
+    void* dptr = nullptr;
+    void* owned = nullptr;
+    size_t bytes = 0;
+    ~OutStage()
+    {
+        if (owned) pcp_arena_free(ctx, owned);
+    }
+    int open(pcp_ctx* c, void* p, size_t nbytes, bool preload = false);
+    int commit(size_t nbytes_override = (size_t)-1);
+};
+
+// ---- stage timing --------------------------------------------------------------------------------------
+struct StageTimer {
+    pcp_ctx* ctx;
+    int stage = -1;
+    cudaEvent_t a = nullptr, b = nullptr;
+    StageTimer(pcp_ctx* c, const char* name, double bytes = 0);
+    ~StageTimer();
+};
+void pcp_profile_resolve(pcp_ctx* ctx);
+
+static inline unsigned pcp_blocks_for(size_t n, unsigned threads) { return (unsigned)((n + threads - 1) / threads); }

@@ -1,0 +1,389 @@
+// index.cu -- builds the Morton-sorted multi-level grid (see index.cuh).  Replaces
+// KdTreeFLANN::setInputCloud / convertCloudToArray (kd_tree.h:772-798, 928-956): non-finite points are
+// dropped, every record keeps its ORIGINAL cloud index (index_mapping_).
+#include "index.cuh"
+#include "reduce.cuh"
+#include "sort.cuh"
+#include <cfloat>
+#include <cmath>
+
+namespace {
+
+__global__ void __launch_bounds__(256) morton_key_kernel(const char* __restrict__ pts, size_t n, size_t stride,
+                                                         pcp_grid g, unsigned long long* __restrict__ keys,
+                                                         uint32_t* __restrict__ vals)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double* p = reinterpret_cast<const double*>(pts + i * stride);
+    double x = p[0], y = p[1], z = p[2];
+    unsigned long long key = PCP_EMPTY_KEY;
+    if (isfinite(x) && isfinite(y) && isfinite(z)) {
+        int cx = min(max(pcp_cell_coord(x, g.org[0], g.inv_h, g.dims[0]), 0), g.dims[0] - 1);
+        int cy = min(max(pcp_cell_coord(y, g.org[1], g.inv_h, g.dims[1]), 0), g.dims[1] - 1);
+        int cz = min(max(pcp_cell_coord(z, g.org[2], g.inv_h, g.dims[2]), 0), g.dims[2] - 1);
+        key = pcp_morton(cx, cy, cz);
+    }
+    keys[i] = key;
+    vals[i] = (uint32_t)i;
+}
+
+__global__ void __launch_bounds__(256) gather_rec_kernel(const char* __restrict__ pts, size_t stride,
+                                                         const uint32_t* __restrict__ vals, size_t nv,
+                                                         pcp_rec* __restrict__ rec)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= nv) return;
+    uint32_t o = vals[i];
+    const double* p = reinterpret_cast<const double*>(pts + (size_t)o * stride);
+    pcp_rec r;
+    r.x = p[0];
+    r.y = p[1];
+    r.z = p[2];
+    r.idx = (long long)o;
+    rec[i] = r;
+}
+
+__global__ void __launch_bounds__(256) cell_flag_kernel(const unsigned long long* __restrict__ keys, size_t nv,
+                                                        uint32_t* __restrict__ flag)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= nv) return;
+    flag[i] = (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(256) cell_fill_kernel(const unsigned long long* __restrict__ keys,
+                                                        const uint32_t* __restrict__ flag,
+                                                        const uint32_t* __restrict__ scan, size_t nv,
+                                                        unsigned long long* __restrict__ ckey,
+                                                        uint32_t* __restrict__ cstart, uint32_t* __restrict__ ncell_out)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= nv) return;
+    if (flag[i]) {
+        ckey[scan[i]] = keys[i];
+        cstart[scan[i]] = (uint32_t)i;
+    }
+    if (i == nv - 1) {
+        uint32_t m = scan[i] + flag[i];
+        cstart[m] = (uint32_t)nv;
+        *ncell_out = m;
+    }
+}
+
+// point-weighted occupancy histogram: bin floor(log2(count)) += count
+__global__ void __launch_bounds__(256) occupancy_kernel(const uint32_t* __restrict__ cstart, uint32_t ncell,
+                                                        unsigned long long* __restrict__ bins)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncell) return;
+    uint32_t cnt = cstart[c + 1] - cstart[c];
+    int b = 31 - __clz(cnt);
+    atomicAdd(&bins[b], (unsigned long long)cnt);
+}
+
+__global__ void __launch_bounds__(256) hash_insert_kernel(const unsigned long long* __restrict__ ckey,
+                                                          const uint32_t* __restrict__ cstart, uint32_t ncell,
+                                                          pcp_hslot* __restrict__ htab, uint32_t hmask)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncell) return;
+    unsigned long long key = ckey[c];
+    uint32_t s = pcp_hash64(key) & hmask;
+    while (true) {
+        unsigned long long prev = atomicCAS(&htab[s].key, PCP_EMPTY_KEY, key);
+        if (prev == PCP_EMPTY_KEY) {
+            htab[s].start = cstart[c];
+            htab[s].count = cstart[c + 1] - cstart[c];
+            return;
+        }
+        s = (s + 1) & hmask;
+    }
+}
+
+__global__ void __launch_bounds__(256) item_count_kernel(const uint32_t* __restrict__ cstart, uint32_t ncell,
+                                                         uint32_t* __restrict__ nchunk)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncell) return;
+    nchunk[c] = (cstart[c + 1] - cstart[c] + 31) >> 5;
+}
+
+__global__ void __launch_bounds__(256) item_fill_kernel(const uint32_t* __restrict__ cstart,
+                                                        const uint32_t* __restrict__ nchunk,
+                                                        const uint32_t* __restrict__ off, uint32_t ncell,
+                                                        uint32_t* __restrict__ item_cell,
+                                                        uint32_t* __restrict__ item_first, uint32_t* __restrict__ nitem)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncell) return;
+    uint32_t o = off[c], k = nchunk[c], s = cstart[c];
+    for (uint32_t j = 0; j < k; j++) {
+        item_cell[o + j] = c;
+        item_first[o + j] = s + 32 * j;
+    }
+    if (c == ncell - 1) *nitem = o + k;
+}
+
+int ilog2_ceil(int v)
+{
+    int b = 0;
+    while ((1 << b) < v) b++;
+    return b;
+}
+
+void grid_from_h(pcp_grid& g, const pcp_bbox& bb, double h)
+{
+    double ext[3];
+    double emax = 0;
+    for (int d = 0; d < 3; d++) {
+        ext[d] = bb.mx[d] - bb.mn[d];
+        if (!(ext[d] >= 0)) ext[d] = 0;
+        emax = fmax(emax, ext[d]);
+    }
+    // at most 2^21 cells per axis (63-bit Morton codes)
+    double hmin = emax / 2097150.0;
+    if (!(h > hmin)) h = hmin > 0 ? hmin : 1.0;
+    int dmax = 1;
+    for (int d = 0; d < 3; d++) {
+        g.org[d] = bb.mn[d];
+        g.dims[d] = (int)(ext[d] / h) + 1;
+        dmax = g.dims[d] > dmax ? g.dims[d] : dmax;
+    }
+    g.h = h;
+    g.inv_h = 1.0 / h;
+    g.nbits = ilog2_ceil(dmax);
+    if (g.nbits < 1) g.nbits = 1;
+    g.top_level = g.nbits; // at level nbits every coordinate >> level is 0
+}
+
+} // namespace
+
+static void index_release(pcp_index* ix)
+{
+    if (!ix) return;
+    pcp_ctx* c = ix->ctx;
+    pcp_arena_free(c, ix->rec);
+    pcp_arena_free(c, ix->ckey);
+    pcp_arena_free(c, ix->cstart);
+    pcp_arena_free(c, ix->htab);
+    pcp_arena_free(c, ix->item_cell);
+    pcp_arena_free(c, ix->item_first);
+    delete ix;
+}
+
+int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, double cell_size, pcp_index** out)
+{
+    *out = nullptr;
+    if (n > (size_t)0x7fffffff) return pcp_fail(ctx, PCP_ERR_RANGE, "index: more than 2^31-1 points");
+    pcp_index* ix = new pcp_index();
+    ix->ctx = ctx;
+    ix->n_orig = n;
+    pcp_bbox bb;
+    memset(&bb, 0, sizeof(bb));
+    if (n) {
+        StageTimer t(ctx, "index.bbox", 24.0 * n);
+        int s = pcp_bbox_host(ctx, dpts, n, stride, &bb);
+        if (s != PCP_OK) {
+            delete ix;
+            return s;
+        }
+    }
+    ix->n = (size_t)bb.count;
+    size_t nv = ix->n;
+    if (nv == 0) {
+        memset(&ix->grid, 0, sizeof(ix->grid));
+        ix->grid.h = ix->grid.inv_h = 1.0;
+        *out = ix;
+        return PCP_OK;
+    }
+    // initial guess: points on a surface spanning the two largest extents, ~16 points per cell
+    double e[3] = {bb.mx[0] - bb.mn[0], bb.mx[1] - bb.mn[1], bb.mx[2] - bb.mn[2]};
+    double a = fmax(e[0] * e[1], fmax(e[0] * e[2], e[1] * e[2]));
+    double h = cell_size > 0 ? cell_size : sqrt(16.0 * a / (double)nv);
+    if (!(h > 0) || !std::isfinite(h)) h = 1.0;
+
+    DevBuf<unsigned long long> k0, k1, bins;
+    DevBuf<uint32_t> v0, v1, flag, scan, ncell_dev;
+    int st = PCP_OK;
+#define IX_TRY(expr)                                                                                         \
+    do {                                                                                                     \
+        st = (expr);                                                                                         \
+        if (st != PCP_OK) {                                                                                  \
+            index_release(ix);                                                                               \
+            return st;                                                                                       \
+        }                                                                                                    \
+    } while (0)
+#define IX_CUDA(expr)                                                                                        \
+    do {                                                                                                     \
+        cudaError_t _e = (expr);                                                                             \
+        if (_e != cudaSuccess) {                                                                             \
+            index_release(ix);                                                                               \
+            return pcp_fail(ctx, PCP_ERR_CUDA, "%s failed: %s", #expr, cudaGetErrorString(_e));              \
+        }                                                                                                    \
+    } while (0)
+    IX_TRY(k0.alloc(ctx, n));
+    IX_TRY(k1.alloc(ctx, n));
+    IX_TRY(v0.alloc(ctx, n));
+    IX_TRY(v1.alloc(ctx, n));
+    IX_TRY(flag.alloc(ctx, nv));
+    IX_TRY(scan.alloc(ctx, nv));
+    IX_TRY(ncell_dev.alloc(ctx, 2));
+    IX_TRY(bins.alloc(ctx, 32));
+    unsigned long long *keys = k0.p, *keys_alt = k1.p;
+    uint32_t *vals = v0.p, *vals_alt = v1.p;
+    uint32_t ncell = 0;
+    const int max_iter = cell_size > 0 ? 1 : 6;
+    for (int iter = 0; iter < max_iter; iter++) {
+        grid_from_h(ix->grid, bb, h);
+        h = ix->grid.h;
+        keys = k0.p, keys_alt = k1.p, vals = v0.p, vals_alt = v1.p;
+        {
+            StageTimer t(ctx, "index.keys", 24.0 * n);
+            morton_key_kernel<<<pcp_blocks_for(n, 256), 256, 0, ctx->stream>>>(static_cast<const char*>(dpts), n,
+                                                                             stride, ix->grid, keys, vals);
+            ctx->launches++;
+            IX_CUDA(cudaGetLastError());
+        }
+        {
+            StageTimer t(ctx, "index.sort");
+            int bits = 3 * ix->grid.nbits + (nv < n ? 1 : 0);
+            if (nv < n && bits < 64) bits = 64; // the all-ones key of dropped points must sort last
+            IX_TRY(pcp_sort_pairs_u64(ctx, &keys, &keys_alt, &vals, &vals_alt, n, bits > 64 ? 64 : bits));
+        }
+        {
+            StageTimer t(ctx, "index.cells");
+            cell_flag_kernel<<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(keys, nv, flag.p);
+            ctx->launches++;
+            IX_CUDA(cudaGetLastError());
+            IX_TRY(pcp_exclusive_scan_u32(ctx, flag.p, scan.p, nv));
+            // ncell = scan[nv-1] + flag[nv-1]
+            uint32_t tail[2];
+            IX_CUDA(cudaMemcpyAsync(&tail[0], scan.p + (nv - 1), 4, cudaMemcpyDeviceToHost, ctx->stream));
+            IX_CUDA(cudaMemcpyAsync(&tail[1], flag.p + (nv - 1), 4, cudaMemcpyDeviceToHost, ctx->stream));
+            IX_CUDA(cudaStreamSynchronize(ctx->stream));
+            ncell = tail[0] + tail[1];
+        }
+        pcp_arena_free(ctx, ix->ckey);
+        pcp_arena_free(ctx, ix->cstart);
+        ix->ckey = nullptr;
+        ix->cstart = nullptr;
+        void* q = nullptr;
+        IX_TRY(pcp_arena_alloc(ctx, (size_t)ncell * 8, &q));
+        ix->ckey = (unsigned long long*)q;
+        IX_TRY(pcp_arena_alloc(ctx, ((size_t)ncell + 1) * 4, &q));
+        ix->cstart = (uint32_t*)q;
+        {
+            StageTimer t(ctx, "index.cells");
+            cell_fill_kernel<<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(keys, flag.p, scan.p, nv, ix->ckey,
+                                                                             ix->cstart, ncell_dev.p);
+            ctx->launches++;
+            IX_CUDA(cudaGetLastError());
+        }
+        ix->ncell = ncell;
+        if (iter + 1 >= max_iter) break;
+        // data-driven cell size: aim the point-weighted median occupancy at ~16 points per cell
+        unsigned long long hb[32];
+        IX_CUDA(cudaMemsetAsync(bins.p, 0, 32 * 8, ctx->stream));
+        occupancy_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->cstart, ncell, bins.p);
+        ctx->launches++;
+        IX_CUDA(cudaGetLastError());
+        IX_CUDA(cudaMemcpyAsync(hb, bins.p, 32 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        IX_CUDA(cudaStreamSynchronize(ctx->stream));
+        unsigned long long acc = 0;
+        int mb = 0;
+        for (int b = 0; b < 32; b++) {
+            acc += hb[b];
+            if (2 * acc >= nv) {
+                mb = b;
+                break;
+            }
+        }
+        double occ = 1.5 * (double)(1u << mb); // centre of [2^b, 2^(b+1))
+        if (nv <= 64) break;                    // tiny clouds: any grid works
+        if (mb == 0) {
+            h *= 2.5;
+        } else if (occ < 10.0 || occ >= 40.0) {
+            h *= pow(16.0 / occ, 1.0 / 2.5);
+        } else {
+            break;
+        }
+    }
+    void* q = nullptr;
+    IX_TRY(pcp_arena_alloc(ctx, nv * sizeof(pcp_rec), &q));
+    ix->rec = (pcp_rec*)q;
+    {
+        StageTimer t(ctx, "index.gather", 56.0 * nv);
+        gather_rec_kernel<<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(static_cast<const char*>(dpts), stride,
+                                                                          vals, nv, ix->rec);
+        ctx->launches++;
+        IX_CUDA(cudaGetLastError());
+    }
+    {
+        StageTimer t(ctx, "index.hash");
+        uint32_t cap = 64;
+        while (cap < 2u * ncell && cap < 0x80000000u) cap <<= 1;
+        ix->hmask = cap - 1;
+        IX_TRY(pcp_arena_alloc(ctx, (size_t)cap * sizeof(pcp_hslot), &q));
+        ix->htab = (pcp_hslot*)q;
+        IX_CUDA(cudaMemsetAsync(ix->htab, 0xff, (size_t)cap * sizeof(pcp_hslot), ctx->stream));
+        hash_insert_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->ckey, ix->cstart, ncell, ix->htab,
+                                                                              ix->hmask);
+        ctx->launches++;
+        IX_CUDA(cudaGetLastError());
+    }
+    {
+        StageTimer t(ctx, "index.items");
+        DevBuf<uint32_t> nchunk, off;
+        IX_TRY(nchunk.alloc(ctx, ncell));
+        IX_TRY(off.alloc(ctx, ncell));
+        item_count_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->cstart, ncell, nchunk.p);
+        ctx->launches++;
+        IX_CUDA(cudaGetLastError());
+        IX_TRY(pcp_exclusive_scan_u32(ctx, nchunk.p, off.p, ncell));
+        // nitem <= ncell + nv/32
+        size_t cap_items = (size_t)ncell + nv / 32 + 1;
+        IX_TRY(pcp_arena_alloc(ctx, cap_items * 4, &q));
+        ix->item_cell = (uint32_t*)q;
+        IX_TRY(pcp_arena_alloc(ctx, cap_items * 4, &q));
+        ix->item_first = (uint32_t*)q;
+        item_fill_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->cstart, nchunk.p, off.p, ncell,
+                                                                            ix->item_cell, ix->item_first,
+                                                                            ncell_dev.p + 1);
+        ctx->launches++;
+        IX_CUDA(cudaGetLastError());
+        uint32_t ni = 0;
+        IX_CUDA(cudaMemcpyAsync(&ni, ncell_dev.p + 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        IX_CUDA(cudaStreamSynchronize(ctx->stream));
+        ix->nitem = ni;
+    }
+#undef IX_TRY
+#undef IX_CUDA
+    *out = ix;
+    return PCP_OK;
+}
+
+extern "C" {
+
+int pcp_index_build(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double cell_size, pcp_index** out)
+{
+    if (!ctx || !out || stride < 24 || (n && !pts)) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_index_build: bad argument");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    InStage in;
+    PCP_TRY(in.open(ctx, pts, n * stride));
+    return pcp_index_build_device(ctx, in.dptr, n, stride, cell_size, out);
+}
+
+void pcp_index_free(pcp_index* index)
+{
+    if (!index) return;
+    std::lock_guard<std::mutex> lock(index->ctx->mu);
+    cudaSetDevice(index->ctx->device);
+    index_release(index);
+}
+
+int64_t pcp_index_size(const pcp_index* index) { return index ? (int64_t)index->n : 0; }
+double pcp_index_cell_size(const pcp_index* index) { return index ? index->grid.h : 0.0; }
+
+} // extern "C"

@@ -1,0 +1,214 @@
+// knn.cu -- host side of the neighbour-search entry points of include/pcp_cuda.h:
+// pcp_features_knn (the calculate_plan_parameter path, calculate_feature.h:15) and pcp_knn
+// (KdTreeFLANN::nearestKSearch, kd_tree.h:814-845).
+#include "knn_warp.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) props_fallback_kernel(void* props, double* eig3, float* lps3, int32_t* knn_idx,
+                                                             int k, size_t n)
+{
+    size_t j = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    pcp_plane pl;
+    pcp_store_props(props, j, false, pl);
+    pcp_store_extra(eig3, lps3, j, false, pl);
+    if (knn_idx)
+        for (int e = 0; e < k; e++) knn_idx[j * k + e] = -1;
+}
+
+__global__ void __launch_bounds__(256) knn_export_kernel(const pcp_rec* __restrict__ rec,
+                                                         const uint32_t* __restrict__ pos, size_t total, int k,
+                                                         int32_t* __restrict__ idx, int32_t* __restrict__ found)
+{
+    size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (t >= total) return;
+    uint32_t p = pos[t];
+    idx[t] = p == 0xffffffffu ? -1 : (int32_t)rec[p].idx;
+    if (found && (t % k) == 0) {
+        int c = 0;
+        for (int e = 0; e < k; e++) c += pos[t + e] != 0xffffffffu;
+        found[t / k] = c;
+    }
+}
+
+template <int KPL> int launch_wknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint32_t expected)
+{
+    int blocks = ctx->sm_count * 4;
+    if (expected && (expected + 3) / 4 < (uint32_t)blocks) blocks = (int)((expected + 3) / 4);
+    if (blocks < 1) blocks = 1;
+    knn_warp_kernel<KPL><<<blocks, 128, 0, ctx->stream>>>(P);
+    PCP_LAUNCH_CHECK(ctx);
+    return PCP_OK;
+}
+
+int run_wknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint32_t expected)
+{
+    if (P.k <= 32) return launch_wknn<1>(ctx, P, expected);
+    if (P.k <= 64) return launch_wknn<2>(ctx, P, expected);
+    if (P.k <= 128) return launch_wknn<4>(ctx, P, expected);
+    return pcp_fail(ctx, PCP_ERR_RANGE, "kNN: k > 128 is not supported");
+}
+
+} // namespace
+
+extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double* eig3, float* lps3, int32_t* knn_idx)
+{
+    if (!ix || !props || k < 1) return pcp_fail(ix ? ix->ctx : nullptr, PCP_ERR_INVALID, "pcp_features_knn: bad argument");
+    pcp_ctx* ctx = ix->ctx;
+    if (k > 128) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_features_knn: k > 128 is not supported");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    const size_t n0 = ix->n_orig, nv = ix->n;
+    if (n0 == 0) return PCP_OK;
+    OutStage o_props, o_eig, o_lps, o_idx;
+    PCP_TRY(o_props.open(ctx, props, n0 * 48));
+    PCP_TRY(o_eig.open(ctx, eig3, n0 * 24));
+    PCP_TRY(o_lps.open(ctx, lps3, n0 * 12));
+    PCP_TRY(o_idx.open(ctx, knn_idx, n0 * (size_t)k * 4));
+    const int kk = (int)(nv < (size_t)k ? nv : (size_t)k);
+    if (nv < n0 || kk == 0) {
+        props_fallback_kernel<<<pcp_blocks_for(n0, 256), 256, 0, ctx->stream>>>(
+            o_props.dptr, (double*)o_eig.dptr, (float*)o_lps.dptr, (int32_t*)o_idx.dptr, k, n0);
+        PCP_LAUNCH_CHECK(ctx);
+    }
+    if (nv > 0 && kk > 0) {
+        DevBuf<uint32_t> fail_list, counters;
+        PCP_TRY(fail_list.alloc(ctx, nv));
+        PCP_TRY(counters.alloc(ctx, 2));
+        PCP_CUDA_TRY(ctx, cudaMemsetAsync(counters.p, 0, 8, ctx->stream));
+        uint32_t nfail = 0;
+        if (kk <= 64) {
+            pcp_knn_params P;
+            P.rec = ix->rec;
+            P.htab = ix->htab;
+            P.hmask = ix->hmask;
+            P.ckey = ix->ckey;
+            P.cstart = ix->cstart;
+            P.ncell = ix->ncell;
+            P.item_cell = ix->item_cell;
+            P.item_first = ix->item_first;
+            P.nitem = ix->nitem;
+            P.g = ix->grid;
+            P.k = k;
+            P.kk = kk;
+            P.cap = kk + 12;
+            P.props = o_props.dptr;
+            P.eig3 = (double*)o_eig.dptr;
+            P.lps3 = (float*)o_lps.dptr;
+            P.knn_idx = (int32_t*)o_idx.dptr;
+            P.fail_list = fail_list.p;
+            P.fail_count = counters.p;
+            size_t smem = PCP_KNN_WARPS * ((size_t)PCP_KNN_NB * 32 * 4 + (size_t)P.cap * 32 * 12);
+            PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_cell_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            {
+                StageTimer t(ctx, "knn.cell_kernel", 72.0 * nv);
+                knn_cell_kernel<<<pcp_blocks_for(ix->nitem, PCP_KNN_WARPS), 32 * PCP_KNN_WARPS, smem, ctx->stream>>>(P);
+                PCP_LAUNCH_CHECK(ctx);
+            }
+            PCP_CUDA_TRY(ctx, cudaMemcpyAsync(&nfail, counters.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+            PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+        } else {
+            // k too large for the cell kernel's shared-memory lists: every query takes the warp kernel
+            nfail = (uint32_t)nv;
+            // qlist = identity over sorted positions
+            // (reuse fail_list; filled by a trivial kernel below)
+        }
+        if (nfail) {
+            DevBuf<uint32_t> nbr;
+            PCP_TRY(nbr.alloc(ctx, (size_t)nfail * k));
+            pcp_wknn_params W;
+            memset(&W, 0, sizeof(W));
+            W.rec = ix->rec;
+            W.ckey = ix->ckey;
+            W.cstart = ix->cstart;
+            W.ncell = ix->ncell;
+            W.g = ix->grid;
+            W.k = k;
+            W.kk = kk;
+            W.qcount = nfail;
+            W.out_pos = nbr.p;
+            W.work_counter = counters.p + 1;
+            DevBuf<uint32_t> ident;
+            if (kk > 64) {
+                // identity query list with start level 0
+                PCP_TRY(ident.alloc(ctx, nv));
+                std::vector<uint32_t> h(nv);
+                for (size_t i = 0; i < nv; i++) h[i] = (uint32_t)i;
+                PCP_CUDA_TRY(ctx, cudaMemcpyAsync(ident.p, h.data(), nv * 4, cudaMemcpyHostToDevice, ctx->stream));
+                PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+                PCP_CUDA_TRY(ctx, cudaMemcpyAsync(counters.p, &nfail, 4, cudaMemcpyHostToDevice, ctx->stream));
+                W.qlist = ident.p;
+            } else {
+                W.qlist = fail_list.p;
+            }
+            {
+                StageTimer t(ctx, "knn.warp_kernel");
+                PCP_TRY(run_wknn(ctx, W, nfail));
+            }
+            {
+                StageTimer t(ctx, "knn.fallback_features");
+                features_from_list_kernel<<<pcp_blocks_for(nfail, 128), 128, 0, ctx->stream>>>(
+                    ix->rec, W.qlist, counters.p, nbr.p, k, kk, o_props.dptr, (double*)o_eig.dptr,
+                    (float*)o_lps.dptr, (int32_t*)o_idx.dptr);
+                PCP_LAUNCH_CHECK(ctx);
+            }
+        }
+    }
+    PCP_TRY(o_props.commit());
+    PCP_TRY(o_eig.commit());
+    PCP_TRY(o_lps.commit());
+    PCP_TRY(o_idx.commit());
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}
+
+extern "C" int pcp_knn(const pcp_index* ix, const void* q, size_t nq, size_t qstride, int k, int32_t* idx, double* d2,
+                       int32_t* found)
+{
+    if (!ix || k < 1 || qstride < 24 || (nq && (!q || !idx)))
+        return pcp_fail(ix ? ix->ctx : nullptr, PCP_ERR_INVALID, "pcp_knn: bad argument");
+    pcp_ctx* ctx = ix->ctx;
+    if (k > 128) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_knn: k > 128 is not supported");
+    if (nq > 0xfffffff0ull) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_knn: too many queries in one call");
+    if (nq == 0) return PCP_OK;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    InStage in;
+    OutStage o_idx, o_d2, o_found;
+    PCP_TRY(in.open(ctx, q, nq * qstride));
+    PCP_TRY(o_idx.open(ctx, idx, nq * (size_t)k * 4));
+    PCP_TRY(o_d2.open(ctx, d2, nq * (size_t)k * 8));
+    PCP_TRY(o_found.open(ctx, found, nq * 4));
+    DevBuf<uint32_t> pos, counter;
+    PCP_TRY(pos.alloc(ctx, nq * (size_t)k));
+    PCP_TRY(counter.alloc(ctx, 1));
+    PCP_CUDA_TRY(ctx, cudaMemsetAsync(counter.p, 0, 4, ctx->stream));
+    pcp_wknn_params W;
+    memset(&W, 0, sizeof(W));
+    W.rec = ix->rec;
+    W.ckey = ix->ckey;
+    W.cstart = ix->cstart;
+    W.ncell = ix->ncell;
+    W.g = ix->grid;
+    W.k = k;
+    W.kk = (int)(ix->n < (size_t)k ? ix->n : (size_t)k);
+    W.qcount = (uint32_t)nq;
+    W.qpts = static_cast<const char*>(in.dptr);
+    W.qstride = qstride;
+    W.out_pos = pos.p;
+    W.out_d2 = (double*)o_d2.dptr;
+    W.work_counter = counter.p;
+    {
+        StageTimer t(ctx, "knn.query_kernel");
+        PCP_TRY(run_wknn(ctx, W, (uint32_t)nq));
+        knn_export_kernel<<<pcp_blocks_for(nq * (size_t)k, 256), 256, 0, ctx->stream>>>(
+            ix->rec, pos.p, nq * (size_t)k, k, (int32_t*)o_idx.dptr, (int32_t*)o_found.dptr);
+        PCP_LAUNCH_CHECK(ctx);
+    }
+    PCP_TRY(o_idx.commit());
+    PCP_TRY(o_d2.commit());
+    PCP_TRY(o_found.commit());
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}

@@ -1,0 +1,212 @@
+// knn_warp.cuh -- warp-per-query exact kNN with level escalation: KdTreeFLANN::nearestKSearch
+// (kd_tree.h:814-845) for arbitrary query points, and the fall-back for queries the cell kernel could not
+// prove exact.  The 32 lanes stream the points of the 3x3x3 block of level-l cells (coalesced 32-byte
+// records), keep the best candidates as a warp-distributed sorted list (entry e lives in lane e%32, slot
+// e/32) and insert with ballot + shuffle; ordering is (d2, original index).  If the k-th distance is not
+// provably inside the block the query moves one level up (cell edge doubles) and rescans.
+#pragma once
+#include "knn_cell.cuh"
+
+struct pcp_wknn_params {
+    const pcp_rec* rec;
+    const unsigned long long* ckey;
+    const uint32_t* cstart;
+    uint32_t ncell;
+    pcp_grid g;
+    int k, kk;
+    // queries: either sorted positions (qlist, with count in *qcount_dev or qcount) or external points
+    const uint32_t* qlist;
+    const uint32_t* qcount_dev;
+    uint32_t qcount;
+    const char* qpts;
+    size_t qstride;
+    // outputs, row r = query ordinal in the list: kk sorted positions (and squared distances)
+    uint32_t* out_pos; // [nq][k]
+    double* out_d2;    // [nq][k] or NULL
+    uint32_t* work_counter;
+};
+
+template <int KPL> struct pcp_wlist {
+    double d[KPL];
+    int idx[KPL];
+    uint32_t pos[KPL];
+};
+
+__device__ __forceinline__ bool pcp_less(double d, int i, double e, int j) { return d < e || (d == e && i < j); }
+
+template <int KPL>
+__device__ __forceinline__ void pcp_wlist_insert(pcp_wlist<KPL>& L, int lane, double xd, int xi, uint32_t xp)
+{
+    int p = 0;
+#pragma unroll
+    for (int s = 0; s < KPL; s++) p += __popc(__ballot_sync(0xffffffffu, pcp_less(L.d[s], L.idx[s], xd, xi)));
+#pragma unroll
+    for (int s = KPL - 1; s >= 0; s--) {
+        double pd = __shfl_up_sync(0xffffffffu, L.d[s], 1);
+        int pi = __shfl_up_sync(0xffffffffu, L.idx[s], 1);
+        uint32_t pp = __shfl_up_sync(0xffffffffu, L.pos[s], 1);
+        if (s > 0) {
+            double cd = __shfl_sync(0xffffffffu, L.d[s - 1], 31);
+            int ci = __shfl_sync(0xffffffffu, L.idx[s - 1], 31);
+            uint32_t cp = __shfl_sync(0xffffffffu, L.pos[s - 1], 31);
+            if (lane == 0) pd = cd, pi = ci, pp = cp;
+        }
+        const int e = s * 32 + lane;
+        if (e > p) {
+            L.d[s] = pd;
+            L.idx[s] = pi;
+            L.pos[s] = pp;
+        } else if (e == p) {
+            L.d[s] = xd;
+            L.idx[s] = xi;
+            L.pos[s] = xp;
+        }
+    }
+}
+
+template <int KPL> __device__ __forceinline__ void pcp_wlist_kth(const pcp_wlist<KPL>& L, int kk, double& kd, int& ki)
+{
+    const int e = kk - 1;
+    double d = L.d[0];
+    int i = L.idx[0];
+#pragma unroll
+    for (int s = 1; s < KPL; s++)
+        if ((e >> 5) == s) d = L.d[s], i = L.idx[s];
+    kd = __shfl_sync(0xffffffffu, d, e & 31);
+    ki = __shfl_sync(0xffffffffu, i, e & 31);
+}
+
+template <int KPL> static __global__ void __launch_bounds__(128) knn_warp_kernel(pcp_wknn_params P)
+{
+    const int lane = threadIdx.x & 31;
+    const uint32_t nq = P.qcount_dev ? *P.qcount_dev : P.qcount;
+    while (true) {
+        uint32_t qi = 0;
+        if (lane == 0) qi = atomicAdd(P.work_counter, 1u);
+        qi = __shfl_sync(0xffffffffu, qi, 0);
+        if (qi >= nq) return;
+        double qx, qy, qz;
+        int level = 0;
+        if (P.qlist) {
+            uint32_t code = __ldg(P.qlist + qi);
+            level = (code & 0x80000000u) ? 1 : 0;
+            const pcp_rec q = pcp_load_rec(P.rec, code & 0x7fffffffu);
+            qx = q.x, qy = q.y, qz = q.z;
+        } else {
+            const double* qp = reinterpret_cast<const double*>(P.qpts + (size_t)qi * P.qstride);
+            qx = qp[0], qy = qp[1], qz = qp[2];
+        }
+        pcp_wlist<KPL> L;
+        int found = 0;
+        const bool finite_q = isfinite(qx) && isfinite(qy) && isfinite(qz);
+        if (finite_q && P.kk > 0) {
+            // base-cell coordinates of the query, clamped into the grid
+            const int bx = min(max(pcp_cell_coord(qx, P.g.org[0], P.g.inv_h, 0), 0), P.g.dims[0] - 1);
+            const int by = min(max(pcp_cell_coord(qy, P.g.org[1], P.g.inv_h, 0), 0), P.g.dims[1] - 1);
+            const int bz = min(max(pcp_cell_coord(qz, P.g.org[2], P.g.inv_h, 0), 0), P.g.dims[2] - 1);
+            if (level > P.g.top_level) level = P.g.top_level;
+            for (; level <= P.g.top_level; level++) {
+#pragma unroll
+                for (int s = 0; s < KPL; s++) L.d[s] = DBL_MAX, L.idx[s] = 0x7fffffff, L.pos[s] = 0xffffffffu;
+                const int cx = bx >> level, cy = by >> level, cz = bz >> level;
+                uint32_t lo = 0, hi = 0;
+                if (lane < 27) {
+                    int dx, dy, dz;
+                    pcp_nb_offset(lane, dx, dy, dz);
+                    const int nx = cx + dx, ny = cy + dy, nz = cz + dz;
+                    const int mx = (P.g.dims[0] - 1) >> level, my = (P.g.dims[1] - 1) >> level,
+                              mz = (P.g.dims[2] - 1) >> level;
+                    if (nx >= 0 && ny >= 0 && nz >= 0 && nx <= mx && ny <= my && nz <= mz)
+                        pcp_level_range(P.ckey, P.cstart, P.ncell, level, nx, ny, nz, lo, hi);
+                }
+                double kd = DBL_MAX;
+                int ki = 0x7fffffff;
+                for (int nb = 0; nb < 27; nb++) {
+                    const uint32_t s0 = __shfl_sync(0xffffffffu, lo, nb);
+                    const uint32_t s1 = __shfl_sync(0xffffffffu, hi, nb);
+                    for (uint32_t t0 = s0; t0 < s1; t0 += 32) {
+                        const uint32_t t = t0 + lane;
+                        double d2 = DBL_MAX;
+                        int ci = 0x7fffffff;
+                        if (t < s1) {
+                            const pcp_rec r = pcp_load_rec(P.rec, t);
+                            d2 = pcp_dist2(qx, qy, qz, r.x, r.y, r.z);
+                            ci = (int)r.idx;
+                        }
+                        unsigned qual = __ballot_sync(0xffffffffu, t < s1 && pcp_less(d2, ci, kd, ki));
+                        while (qual) {
+                            const int src = __ffs(qual) - 1;
+                            qual &= qual - 1;
+                            const double xd = __shfl_sync(0xffffffffu, d2, src);
+                            const int xi = __shfl_sync(0xffffffffu, ci, src);
+                            if (!pcp_less(xd, xi, kd, ki)) continue; // threshold moved since the ballot
+                            pcp_wlist_insert<KPL>(L, lane, xd, xi, t0 + src);
+                            pcp_wlist_kth<KPL>(L, P.kk, kd, ki);
+                        }
+                    }
+                }
+                const double g2 = pcp_guarantee2(P.g, level, cx, cy, cz, qx, qy, qz);
+                if (level == P.g.top_level || (kd < DBL_MAX && kd < g2)) break;
+            }
+            found = P.kk;
+        }
+        // write the list: entry e -> out[qi*k + e]
+#pragma unroll
+        for (int s = 0; s < KPL; s++) {
+            const int e = s * 32 + lane;
+            if (e < P.k) {
+                const bool have = e < found && L.d[s] < DBL_MAX;
+                P.out_pos[(size_t)qi * P.k + e] = have ? L.pos[s] : 0xffffffffu;
+                if (P.out_d2) P.out_d2[(size_t)qi * P.k + e] = have ? L.d[s] : __longlong_as_double(0x7ff0000000000000ll);
+            }
+        }
+    }
+}
+
+// thread per fall-back query: neighbour positions -> plane fit -> LAS_POINT_PROPERTY
+static __global__ void __launch_bounds__(128) features_from_list_kernel(const pcp_rec* __restrict__ rec,
+                                                                 const uint32_t* __restrict__ qlist,
+                                                                 const uint32_t* __restrict__ qcount_dev,
+                                                                 const uint32_t* __restrict__ nbr_pos, int k, int kk,
+                                                                 void* props, double* eig3, float* lps3,
+                                                                 int32_t* knn_idx)
+{
+    const uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= *qcount_dev) return;
+    const uint32_t qpos = qlist[qi] & 0x7fffffffu;
+    const size_t jq = (size_t)rec[qpos].idx;
+    const uint32_t* row = nbr_pos + (size_t)qi * k;
+    int N = 0;
+    for (int e = 0; e < kk; e++)
+        if (row[e] != 0xffffffffu) N++;
+    if (knn_idx)
+        for (int e = 0; e < k; e++) knn_idx[jq * k + e] = e < N ? (int32_t)rec[row[e]].idx : -1;
+    pcp_plane pl;
+    const bool fitted = N > 3;
+    if (fitted) {
+        double XAve = 0.0, YAve = 0.0, ZAve = 0.0;
+        for (int e = 0; e < N; e++) {
+            const pcp_rec r = pcp_load_rec(rec, row[e]);
+            XAve += r.x;
+            YAve += r.y;
+            ZAve += r.z;
+        }
+        XAve /= (double)N;
+        YAve /= (double)N;
+        ZAve /= (double)N;
+        double s00 = 0, s01 = 0, s02 = 0, s11 = 0, s12 = 0, s22 = 0;
+        for (int e = 0; e < N; e++) {
+            const pcp_rec r = pcp_load_rec(rec, row[e]);
+            const double X = r.x - XAve, Y = r.y - YAve, Z = r.z - ZAve;
+            s00 += X * X;
+            s01 += X * Y;
+            s02 += X * Z;
+            s11 += Y * Y;
+            s12 += Y * Z;
+            s22 += Z * Z;
+        }
+        pcp_plane_from_scatter(s00, s01, s02, s11, s12, s22, XAve, YAve, ZAve, pl);
+    }
+    pcp_store_props(props, jq, fitted, pl);
+    pcp_store_extra(eig3, lps3, jq, fitted, pl);
+}

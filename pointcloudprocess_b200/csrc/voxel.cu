@@ -1,0 +1,354 @@
+// voxel.cu -- VoxelGrid<PointXYZRGBA>::applyFilter (voxel_grid.h:811-1056) as sort + segmented reduce,
+// and PointCloudHelper::remove_duplicate (point_cloud_helper.cpp:42-63) around it.
+//
+// Numerics kept from the reference: cell index by truncation of double(p*inv_leaf) - min_b
+// (voxel_grid.h:936-938), min_b/max_b by truncation of the bounding box (:835-840) with the DBL_MIN max
+// seed (point_cloud_helper.h:65), every field rounded through float before the double sum
+// (concatenate.h:153), division by the count (:1034), static_cast write-back (concatenate.h:118) and the
+// rgb re-pack (:1045-1050).  Cell keys are 64-bit (the reference's int idx overflows on large grids).
+// Inside a cell points are summed in ascending point index (stable LSD sort of (key, index)).
+#include "reduce.cuh"
+#include "sort.cuh"
+#include <cfloat>
+
+namespace {
+
+struct VoxParams {
+    double inv[3];
+    int min_b[3];
+    int div_b[3];
+};
+
+template <typename KeyT>
+__global__ void __launch_bounds__(256) voxel_key_kernel(const char* __restrict__ pts, size_t n, size_t stride,
+                                                        VoxParams P, KeyT* __restrict__ keys,
+                                                        uint32_t* __restrict__ vals, int32_t* __restrict__ point_cell)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double* p = reinterpret_cast<const double*>(pts + i * stride);
+    double x = p[0], y = p[1], z = p[2];
+    KeyT key = ~(KeyT)0; // dropped points sort to the end
+    int c0 = -1, c1 = -1, c2 = -1;
+    if (isfinite(x) && isfinite(y) && isfinite(z)) {
+        c0 = (int)__dsub_rn(__dmul_rn(x, P.inv[0]), (double)P.min_b[0]);
+        c1 = (int)__dsub_rn(__dmul_rn(y, P.inv[1]), (double)P.min_b[1]);
+        c2 = (int)__dsub_rn(__dmul_rn(z, P.inv[2]), (double)P.min_b[2]);
+        unsigned long long k = (unsigned long long)c0 + (unsigned long long)c1 * (unsigned long long)P.div_b[0] +
+                               (unsigned long long)c2 * (unsigned long long)P.div_b[0] * (unsigned long long)P.div_b[1];
+        key = (KeyT)k;
+    }
+    keys[i] = key;
+    vals[i] = (uint32_t)i;
+    if (point_cell) {
+        point_cell[3 * i + 0] = c0;
+        point_cell[3 * i + 1] = c1;
+        point_cell[3 * i + 2] = c2;
+    }
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(256) head_flag_kernel(const KeyT* __restrict__ keys, size_t nv,
+                                                        uint32_t* __restrict__ flag)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= nv) return;
+    flag[i] = (i == 0 || keys[i] != keys[i - 1]) ? 1u : 0u;
+}
+
+// scan[] is the exclusive prefix sum of flag[]: a head at sorted position i opens cell scan[i].
+__global__ void __launch_bounds__(256) cell_start_kernel(const uint32_t* __restrict__ flag,
+                                                         const uint32_t* __restrict__ scan, size_t nv,
+                                                         uint32_t* __restrict__ cell_start, uint32_t* __restrict__ m_out)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= nv) return;
+    if (flag[i]) cell_start[scan[i]] = (uint32_t)i;
+    if (i == nv - 1) {
+        uint32_t m = scan[i] + flag[i];
+        cell_start[m] = (uint32_t)nv;
+        *m_out = m;
+    }
+}
+
+// One thread per occupied cell (N/M is ~1 for the reference's leaf sizes).
+__global__ void __launch_bounds__(128) voxel_centroid_kernel(const char* __restrict__ pts, size_t stride,
+                                                             const uint32_t* __restrict__ vals,
+                                                             const uint32_t* __restrict__ cell_start,
+                                                             const uint32_t* __restrict__ m_ptr, int downsample_all,
+                                                             char* __restrict__ out, size_t out_stride,
+                                                             int32_t* __restrict__ cell_count)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= *m_ptr) return;
+    uint32_t b = cell_start[c], e = cell_start[c + 1];
+    double s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (uint32_t t = b; t < e; t++) {
+        const char* rec = pts + (size_t)vals[t] * stride;
+        const double* p = reinterpret_cast<const double*>(rec);
+        double v[8];
+        if (downsample_all) {
+            uint32_t rgba = *reinterpret_cast<const uint32_t*>(rec + 32);
+            uint32_t stamp = *reinterpret_cast<const uint32_t*>(rec + 36);
+            v[0] = (double)(float)p[0];
+            v[1] = (double)(float)p[1];
+            v[2] = (double)(float)p[2];
+            v[3] = (double)(float)rgba;
+            v[4] = (double)(float)stamp;
+            v[5] = (double)((rgba >> 16) & 0xffu);
+            v[6] = (double)((rgba >> 8) & 0xffu);
+            v[7] = (double)(rgba & 0xffu);
+        } else {
+            v[0] = p[0], v[1] = p[1], v[2] = p[2];
+            v[3] = v[4] = v[5] = v[6] = v[7] = 0;
+        }
+        if (t == b) {
+#pragma unroll
+            for (int f = 0; f < 8; f++) s[f] = v[f];
+        } else {
+#pragma unroll
+            for (int f = 0; f < 8; f++) s[f] = __dadd_rn(s[f], v[f]);
+        }
+    }
+    double cnt = (double)(e - b);
+#pragma unroll
+    for (int f = 0; f < 8; f++) s[f] = __ddiv_rn(s[f], cnt);
+    char* o = out + (size_t)c * out_stride;
+    double* od = reinterpret_cast<double*>(o);
+    od[0] = s[0];
+    od[1] = s[1];
+    od[2] = s[2];
+    if (out_stride >= 32) od[3] = 1.0;
+    if (out_stride >= 40) {
+        uint32_t rgb = 0, stamp = 0;
+        if (downsample_all) {
+            float r = (float)s[5], g = (float)s[6], bl = (float)s[7];
+            rgb = (uint32_t)(((int)r << 16) | ((int)g << 8) | (int)bl);
+            stamp = (uint32_t)s[4]; // cvt.rzi.u32.f64 == static_cast<uint32_t> for in-range values
+        }
+        *reinterpret_cast<uint32_t*>(o + 32) = rgb;
+        *reinterpret_cast<uint32_t*>(o + 36) = stamp;
+    }
+    if (out_stride >= 48) *reinterpret_cast<uint64_t*>(o + 40) = 0ull;
+    if (cell_count) cell_count[c] = (int32_t)(e - b);
+}
+
+__global__ void __launch_bounds__(256) shift_kernel(char* __restrict__ pts, size_t n, size_t stride, const double* c3,
+                                                    const unsigned long long* cnt, int sign)
+{
+    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double* p = reinterpret_cast<double*>(pts + i * stride);
+    double x = p[0], y = p[1], z = p[2];
+    if (!(isfinite(x) && isfinite(y) && isfinite(z))) return; // transformPointCloud skips them (:116-124)
+    double dn = (double)*cnt;
+    double cx = __ddiv_rn(c3[0], dn), cy = __ddiv_rn(c3[1], dn), cz = __ddiv_rn(c3[2], dn);
+    if (sign < 0) cx = -cx, cy = -cy, cz = -cz;
+    p[0] = __dadd_rn(x, cx);
+    p[1] = __dadd_rn(y, cy);
+    p[2] = __dadd_rn(z, cz);
+}
+
+int ceil_log2_u128(double cells)
+{
+    int b = 0;
+    double v = 1.0;
+    while (v < cells && b < 64) v *= 2.0, b++;
+    return b;
+}
+
+} // namespace
+
+// Device-resident core.  dpts: device cloud; dout: device output (capacity n records).
+// m_host receives M (synchronises).  d_point_cell / d_cell_count may be NULL.
+int pcp_voxel_grid_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, const double leaf[3],
+                          int downsample_all, void* dout, size_t out_stride, size_t* m_host, int32_t min_b[3],
+                          int32_t div_b[3], int32_t* d_point_cell, int32_t* d_cell_count)
+{
+    *m_host = 0;
+    if (n == 0) return PCP_OK;
+    if (n > (size_t)0x7fffffff) return pcp_fail(ctx, PCP_ERR_RANGE, "voxel grid: more than 2^31-1 points");
+    pcp_bbox bb;
+    {
+        StageTimer t(ctx, "voxel.bbox", 24.0 * n);
+        PCP_TRY(pcp_bbox_host(ctx, dpts, n, stride, &bb));
+    }
+    if (bb.count == 0) return PCP_OK;
+    VoxParams P;
+    double cells = 1.0;
+    for (int d = 0; d < 3; d++) {
+        if (!(leaf[d] > 0)) return pcp_fail(ctx, PCP_ERR_INVALID, "voxel grid: leaf size must be positive");
+        P.inv[d] = 1.0 / leaf[d];
+        double mx = bb.mx[d] > DBL_MIN ? bb.mx[d] : DBL_MIN; // sic, point_cloud_helper.h:65
+        double lo = bb.mn[d] * P.inv[d], hi = mx * P.inv[d];
+        if (!(fabs(lo) < 2147483000.0) || !(fabs(hi) < 2147483000.0))
+            return pcp_fail(ctx, PCP_ERR_RANGE, "voxel grid: leaf too small, cell index exceeds int range");
+        P.min_b[d] = (int)lo;
+        int max_b = (int)hi;
+        P.div_b[d] = max_b - P.min_b[d] + 1;
+        cells *= (double)P.div_b[d];
+        if (min_b) min_b[d] = P.min_b[d];
+        if (div_b) div_b[d] = P.div_b[d];
+    }
+    int bits = ceil_log2_u128(cells);
+    if (bits > 63) return pcp_fail(ctx, PCP_ERR_RANGE, "voxel grid: more than 2^63 cells");
+    size_t nv = (size_t)bb.count;
+    DevBuf<uint32_t> v0, v1, flag, scan, cell_start, m_dev;
+    PCP_TRY(v0.alloc(ctx, n));
+    PCP_TRY(v1.alloc(ctx, n));
+    uint32_t *vals = v0.p, *vals_alt = v1.p;
+    unsigned nb = pcp_blocks_for(n, 256);
+    PCP_TRY(flag.alloc(ctx, nv));
+    PCP_TRY(scan.alloc(ctx, nv));
+    // dropped (non-finite) points carry an all-ones key: sort one extra bit when there are any
+    int sort_bits = (nv < n) ? (bits < 63 ? bits + 1 : 64) : bits;
+    if (sort_bits <= 32 && !(nv < n && bits == 32)) {
+        DevBuf<uint32_t> k0, k1;
+        PCP_TRY(k0.alloc(ctx, n));
+        PCP_TRY(k1.alloc(ctx, n));
+        uint32_t *keys = k0.p, *keys_alt = k1.p;
+        {
+            StageTimer t(ctx, "voxel.keys", 24.0 * n);
+            voxel_key_kernel<uint32_t><<<nb, 256, 0, ctx->stream>>>(static_cast<const char*>(dpts), n, stride, P, keys,
+                                                                   vals, d_point_cell);
+            PCP_LAUNCH_CHECK(ctx);
+        }
+        {
+            StageTimer t(ctx, "voxel.sort");
+            PCP_TRY(pcp_sort_pairs_u32(ctx, &keys, &keys_alt, &vals, &vals_alt, n, nv < n ? 32 : sort_bits));
+        }
+        StageTimer t(ctx, "voxel.segments");
+        head_flag_kernel<uint32_t><<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(keys, nv, flag.p);
+        PCP_LAUNCH_CHECK(ctx);
+    } else {
+        DevBuf<unsigned long long> k0, k1;
+        PCP_TRY(k0.alloc(ctx, n));
+        PCP_TRY(k1.alloc(ctx, n));
+        unsigned long long *keys = k0.p, *keys_alt = k1.p;
+        {
+            StageTimer t(ctx, "voxel.keys", 24.0 * n);
+            voxel_key_kernel<unsigned long long><<<nb, 256, 0, ctx->stream>>>(static_cast<const char*>(dpts), n, stride, P, keys,
+                                                                   vals, d_point_cell);
+            PCP_LAUNCH_CHECK(ctx);
+        }
+        {
+            StageTimer t(ctx, "voxel.sort");
+            PCP_TRY(pcp_sort_pairs_u64(ctx, &keys, &keys_alt, &vals, &vals_alt, n, nv < n ? 64 : sort_bits));
+        }
+        StageTimer t(ctx, "voxel.segments");
+        head_flag_kernel<unsigned long long><<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(keys, nv, flag.p);
+        PCP_LAUNCH_CHECK(ctx);
+    }
+    {
+        StageTimer t(ctx, "voxel.segments");
+        PCP_TRY(pcp_exclusive_scan_u32(ctx, flag.p, scan.p, nv));
+        PCP_TRY(cell_start.alloc(ctx, nv + 1));
+        PCP_TRY(m_dev.alloc(ctx, 1));
+        cell_start_kernel<<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(flag.p, scan.p, nv, cell_start.p, m_dev.p);
+        PCP_LAUNCH_CHECK(ctx);
+    }
+    {
+        StageTimer t(ctx, "voxel.centroids", 32.0 * n);
+        // grid sized for the worst case M == nv; threads beyond *m_ptr exit
+        voxel_centroid_kernel<<<pcp_blocks_for(nv, 128), 128, 0, ctx->stream>>>(
+            static_cast<const char*>(dpts), stride, vals, cell_start.p, m_dev.p, downsample_all,
+            static_cast<char*>(dout), out_stride, d_cell_count);
+        PCP_LAUNCH_CHECK(ctx);
+    }
+    uint32_t m = 0;
+    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(&m, m_dev.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    *m_host = m;
+    return PCP_OK;
+}
+
+extern "C" int pcp_voxel_grid(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, const double leaf[3],
+                              int downsample_all, void* out_pts, size_t* m, int32_t min_b[3], int32_t div_b[3],
+                              int32_t* point_cell, int32_t* cell_count)
+{
+    if (!ctx || !m || !leaf || stride < 24 || (n && (!pts || !out_pts)))
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_voxel_grid: bad argument");
+    if (downsample_all && stride < 40)
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_voxel_grid: downsample_all needs rgba/stamp_id (stride >= 40)");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    InStage in;
+    OutStage out, pc, cc;
+    PCP_TRY(in.open(ctx, pts, n * stride));
+    PCP_TRY(out.open(ctx, out_pts, n * stride));
+    PCP_TRY(pc.open(ctx, point_cell, n * 12));
+    PCP_TRY(cc.open(ctx, cell_count, n * 4));
+    size_t mm = 0;
+    PCP_TRY(pcp_voxel_grid_device(ctx, in.dptr, n, stride, leaf, downsample_all, out.dptr, stride, &mm, min_b, div_b,
+                                  static_cast<int32_t*>(pc.dptr), static_cast<int32_t*>(cc.dptr)));
+    *m = mm;
+    PCP_TRY(out.commit(mm * stride));
+    PCP_TRY(pc.commit());
+    PCP_TRY(cc.commit(mm * 4));
+    return PCP_OK;
+}
+
+extern "C" int pcp_centroid(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double c[3], uint64_t* count)
+{
+    if (!ctx || !c || stride < 24) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_centroid: bad argument");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    InStage in;
+    PCP_TRY(in.open(ctx, pts, n * stride));
+    DevBuf<double> s3;
+    PCP_TRY(s3.alloc(ctx, 3));
+    pcp_bbox bb;
+    PCP_TRY(pcp_serial_sum_device(ctx, in.dptr, n, stride, s3.p));
+    PCP_TRY(pcp_bbox_host(ctx, in.dptr, n, stride, &bb));
+    double h[3];
+    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(h, s3.p, 24, cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    double dn = (double)bb.count;
+    for (int d = 0; d < 3; d++) c[d] = bb.count ? h[d] / dn : 0.0;
+    if (count) *count = bb.count;
+    return PCP_OK;
+}
+
+extern "C" int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf)
+{
+    if (!ctx || !n_inout || stride < 40 || (*n_inout && !pts_inout))
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_remove_duplicate: bad argument");
+    size_t n = *n_inout;
+    if (n == 0) return PCP_OK;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    OutStage io; // in-place: host clouds are staged in, filtered on the device, staged back
+    PCP_TRY(io.open(ctx, pts_inout, n * stride, true));
+    char* d = static_cast<char*>(io.dptr);
+    DevBuf<char> tmp; // cloud_temp2 (point_cloud_helper.cpp:49-50)
+    DevBuf<double> s3;
+    DevBuf<pcp_bbox> bb;
+    PCP_TRY(tmp.alloc(ctx, n * stride));
+    PCP_TRY(s3.alloc(ctx, 3));
+    PCP_TRY(bb.alloc(ctx, 1));
+    {
+        StageTimer t(ctx, "dedup.centroid", 24.0 * n);
+        PCP_TRY(pcp_serial_sum_device(ctx, d, n, stride, s3.p));
+        PCP_TRY(pcp_bbox_device(ctx, d, n, stride, bb.p));
+    }
+    const unsigned long long* cnt = &bb.p->count;
+    {
+        StageTimer t(ctx, "dedup.centre", 48.0 * n);
+        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(tmp.p, d, n * stride, cudaMemcpyDeviceToDevice, ctx->stream));
+        shift_kernel<<<pcp_blocks_for(n, 256), 256, 0, ctx->stream>>>(tmp.p, n, stride, s3.p, cnt, -1);
+        PCP_LAUNCH_CHECK(ctx);
+    }
+    double l = (double)leaf; // const float -> setLeafSize(double,double,double), point_cloud_helper.cpp:57
+    double leaf3[3] = {l, l, l};
+    size_t m = 0;
+    PCP_TRY(pcp_voxel_grid_device(ctx, tmp.p, n, stride, leaf3, 1, d, stride, &m, nullptr, nullptr, nullptr, nullptr));
+    if (m) {
+        StageTimer t(ctx, "dedup.uncentre", 48.0 * m);
+        shift_kernel<<<pcp_blocks_for(m, 256), 256, 0, ctx->stream>>>(d, m, stride, s3.p, cnt, +1);
+        PCP_LAUNCH_CHECK(ctx);
+    }
+    *n_inout = m;
+    PCP_TRY(io.commit(m * stride));
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}

@@ -1,0 +1,268 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on the same inputs.
+Bars: kNN index sets, squared distances, voxel cells/counts/order bit-exact; features within the
+north-star tolerances (<= 1e-5 relative on eigenvalues, <= 1e-4 rad on normals) -- and, because both sides
+run the same non-fused arithmetic in the same order, in fact bit-identical, which is asserted too."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+UTM = np.array([483189.100569, 3371741.645173, 430.094726])
+
+
+def cloud_uniform(n, seed, offset=True, side=10.0):
+    rng = np.random.default_rng(seed)
+    xyz = rng.uniform(0, side, size=(n, 3)) + (UTM if offset else 0.0)
+    import pointcloudprocess_b200 as pcp
+    c = pcp.make_cloud(xyz, rgba=rng.integers(0, 1 << 24, n, dtype=np.uint32), stamp_id=np.arange(n) % 10)
+    return c
+
+
+def assert_clouds_equal(a, b):
+    """Field-wise bit equality (numpy does not preserve the padding bytes of a structured copy)."""
+    assert len(a) == len(b)
+    for f in ("x", "y", "z", "w", "rgba", "stamp_id"):
+        assert a[f].tobytes() == b[f].tobytes(), f
+
+
+def assert_props_equal(got, ref):
+    for f in ("normal_x", "normal_y", "normal_z", "Distance", "curvature", "PointID"):
+        assert np.array_equal(got[f], ref[f], equal_nan=True), f
+
+
+def check_features_tolerance(got_props, got_eig, ref_props, ref_eig):
+    fitted = ref_eig[:, 0] > 0
+    rel = np.abs(got_eig[fitted] - ref_eig[fitted]) / np.maximum(np.abs(ref_eig[fitted][:, :1]), 1e-300)
+    assert rel.max(initial=0.0) <= 1e-5  # eigenvalues, relative to lambda1
+    n1 = np.stack([got_props[f] for f in ("normal_x", "normal_y", "normal_z")], 1).astype(np.float64)[fitted]
+    n2 = np.stack([ref_props[f] for f in ("normal_x", "normal_y", "normal_z")], 1).astype(np.float64)[fitted]
+    # sign-canonicalised angle
+    cosang = np.abs(np.sum(n1 * n2, 1)) / np.maximum(np.linalg.norm(n1, axis=1) * np.linalg.norm(n2, axis=1), 1e-300)
+    # isotropic neighbourhoods (lambda2 ~ lambda3) have no defined normal: exclude near-degenerate ones
+    sep = (ref_eig[fitted][:, 1] - ref_eig[fitted][:, 2]) / ref_eig[fitted][:, 0] > 1e-6
+    ang = np.arccos(np.clip(cosang[sep], -1, 1))
+    assert ang.max(initial=0.0) <= 1e-4
+
+
+# ---- the reference's own (derivable) known answers: main_test.cpp:126-188 ---------------------------------
+def test_kd_tree_known_answer(ctx):
+    import pointcloudprocess_b200 as pcp
+    cloud = pcp.PointCloud()
+    cloud.points = pcp.make_cloud(np.array([[0.1 * i] * 3 for i in range(100)]))
+    k = pcp.KdTreeFLANN(ctx)
+    k.setInputCloud(cloud)
+    n, index, dis2 = k.nearestKSearch(np.array([0.0, 0.0, 0.0]), 10)
+    assert n == 10
+    assert list(index) == list(range(10))
+    exp = []
+    for i in range(10):
+        d = (0.1 * i) - 0.0
+        exp.append((d * d + d * d) + d * d)
+    assert list(dis2) == exp
+
+
+def test_voxel_grid_known_answer(ctx):
+    import pointcloudprocess_b200 as pcp
+    pts = [[float(i)] * 3 for i in range(10)] + [[0.1 * i] * 3 for i in range(100)]
+    cloud = pcp.PointCloud(pcp.make_cloud(np.array(pts)))
+    vg = pcp.VoxelGrid(ctx)
+    vg.setInputCloud(cloud)
+    vg.setLeafSize(1, 1, 1)
+    out = vg.filter()
+    assert out.size() == 10
+    for c in range(10):
+        vals = [np.float32(c)] + [np.float32(0.1 * i) for i in range(10 * c, 10 * c + 10)]
+        exp = sum(float(v) for v in vals) / 11.0
+        assert out.points["x"][c] == exp and out.points["y"][c] == exp and out.points["z"][c] == exp
+    assert (out.points["rgba"] == 0).all() and (out.points["stamp_id"] == 0).all()
+
+
+# ---- kNN ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,k,offset", [(100, 10, False), (1000, 20, True), (10000, 20, True), (20000, 32, True),
+                                        (5000, 50, False), (3000, 1, True), (300, 100, True)])
+def test_knn_matches_oracle(ctx, orc, n, k, offset):
+    import pointcloudprocess_b200 as pcp
+    cloud = cloud_uniform(n, 7 + n, offset)
+    ix = pcp.Index(ctx, cloud)
+    rng = np.random.default_rng(1)
+    # members and non-members (some outside the bounding box) as queries
+    q = np.concatenate([np.stack([cloud["x"], cloud["y"], cloud["z"]], 1)[:500],
+                        rng.uniform(-3, 13, size=(200, 3)) + (UTM if offset else 0.0)])
+    idx, d2, found = ix.knn(q, k)
+    ridx, rd2, rfound = orc.knn_brute(cloud, q, k)
+    assert np.array_equal(found, rfound)
+    assert np.array_equal(idx, ridx)
+    assert np.array_equal(d2, rd2)
+    ix.free()
+
+
+def test_knn_small_and_degenerate(ctx, orc):
+    import pointcloudprocess_b200 as pcp
+    for n in (1, 2, 3, 4, 5, 19, 20, 21):
+        cloud = cloud_uniform(n, 100 + n, True)
+        ix = pcp.Index(ctx, cloud)
+        idx, d2, found = ix.knn(cloud, 20)
+        ridx, rd2, rfound = orc.knn_brute(cloud, cloud, 20)
+        assert np.array_equal(found, rfound) and np.array_equal(idx, ridx) and np.array_equal(d2, rd2)
+        got = ix.features_knn(20, want_idx=True)
+        props, eig, lps, kidx = orc.features_knn(cloud, 20, want_idx=True)
+        assert np.array_equal(got["knn_idx"], kidx)
+        assert_props_equal(got["props"], props)
+        ix.free()
+    # all points identical (zero scatter -> NaN curvature on both sides)
+    cloud = pcp.make_cloud(np.tile(UTM, (50, 1)))
+    ix = pcp.Index(ctx, cloud)
+    got = ix.features_knn(20, want_idx=True)
+    props, eig, lps, kidx = orc.features_knn(cloud, 20, want_idx=True)
+    assert np.array_equal(got["knn_idx"], kidx)
+    assert_props_equal(got["props"], props)
+    ix.free()
+
+
+def test_knn_with_nan_points_remaps_indices(ctx, orc):
+    import pointcloudprocess_b200 as pcp
+    cloud = cloud_uniform(5000, 9, True)
+    bad = np.random.default_rng(3).choice(5000, 50, replace=False)
+    cloud["x"][bad[:20]] = np.nan
+    cloud["y"][bad[20:35]] = np.inf
+    cloud["z"][bad[35:]] = -np.inf
+    ix = pcp.Index(ctx, cloud)
+    assert ix.size() == 4950
+    got = ix.features_knn(20, want_idx=True)
+    props, eig, lps, kidx = orc.features_knn(cloud, 20, want_idx=True)
+    assert np.array_equal(got["knn_idx"], kidx)
+    assert_props_equal(got["props"], props)
+    assert np.array_equal(got["eig"], eig)
+    ix.free()
+
+
+def test_knn_lattice_ties_follow_index_order(ctx, orc):
+    import pointcloudprocess_b200 as pcp
+    cloud = ctx.synth_cloud("lattice", 4096, seed=8, centred=True)
+    ix = pcp.Index(ctx, cloud)
+    got = ix.features_knn(20, want_idx=True)
+    props, eig, lps, kidx = orc.features_knn(cloud, 20, want_idx=True)
+    assert orc.KdTree(cloud).boundary_ties(cloud, 20) > 0  # the case really has rank-k ties
+    assert np.array_equal(got["knn_idx"], kidx)
+    assert_props_equal(got["props"], props)
+    idx, d2, found = ix.knn(cloud, 20)
+    ridx, rd2, _ = orc.knn_brute(cloud, cloud, 20)
+    assert np.array_equal(idx, ridx) and np.array_equal(d2, rd2)
+    ix.free()
+
+
+# ---- features ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind,n,k", [("strip", 50000, 20), ("forest", 50000, 20), ("city", 100000, 20),
+                                      ("city", 60000, 32), ("uniform_cube", 30000, 10), ("strip", 30000, 50)])
+def test_features_knn_match_oracle(ctx, orc, kind, n, k):
+    import pointcloudprocess_b200 as pcp
+    cloud = ctx.synth_cloud(kind, n, seed=21)
+    ix = pcp.Index(ctx, cloud)
+    got = ix.features_knn(k, want_idx=True)
+    props, eig, lps, kidx = orc.features_knn(cloud, k, want_idx=True)
+    assert np.array_equal(got["knn_idx"], kidx)
+    check_features_tolerance(got["props"], got["eig"], props, eig)
+    assert_props_equal(got["props"], props)            # bit-identical, beyond the required tolerance
+    assert np.array_equal(got["eig"], eig, equal_nan=True)
+    assert np.array_equal(got["lps"], lps, equal_nan=True)
+    ix.free()
+
+
+def test_plane_fit_segments(ctx, orc):
+    rng = np.random.default_rng(5)
+    sizes = [3, 4, 13, 20, 50, 1000]
+    pts = np.concatenate([rng.normal(size=(s, 3)) * [5, 2, 0.01] + UTM for s in sizes])
+    off = np.concatenate([[0], np.cumsum(sizes)])
+    got = ctx.plane_fit(pts, off)
+    for s in range(len(sizes)):
+        ref = orc.plane_fit(pts[off[s]:off[s + 1]])
+        assert got[s].tobytes() == ref.tobytes()
+
+
+# ---- radius ----------------------------------------------------------------------------------------------
+def test_radius_search_matches_oracle(ctx, orc):
+    import pointcloudprocess_b200 as pcp
+    cloud = ctx.synth_cloud("forest", 40000, seed=3)
+    ix = pcp.Index(ctx, cloud)
+    t = orc.KdTree(cloud)
+    q = cloud[:2000]
+    for r, max_nn in ((0.5, 0), (0.25, 0), (1.0, 7), (0.0, 0)):
+        off, idx, d2 = ix.radius(q, r, max_nn)
+        roff, ridx, rd2 = t.radius(q, r, max_nn)
+        assert np.array_equal(off, roff)
+        assert np.array_equal(idx, ridx)
+        assert np.array_equal(d2, rd2)
+    ix.free()
+
+
+def test_features_radius_match_oracle(ctx, orc):
+    import pointcloudprocess_b200 as pcp
+    cloud = ctx.synth_cloud("forest", 40000, seed=4)
+    ix = pcp.Index(ctx, cloud)
+    got = ix.features_radius(0.5)
+    props, eig, lps, counts = orc.features_radius(cloud, 0.5)
+    assert np.array_equal(got["counts"], counts)          # neighbour sets are exact
+    check_features_tolerance(got["props"], got["eig"], props, eig)
+    ix.free()
+
+
+# ---- voxel grid -------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("kind,n,leaf,centred", [("strip", 100000, 0.05, True), ("strip", 100000, 0.04, True),
+                                                 ("city", 200000, 0.02, True), ("forest", 50000, 1.0, True),
+                                                 ("uniform_cube", 20000, 0.5, False)])
+def test_voxel_grid_matches_oracle(ctx, orc, kind, n, leaf, centred):
+    cloud = ctx.synth_cloud(kind, n, seed=2, centred=centred)
+    if centred:  # straddle zero like remove_duplicate's centred clouds, incl. negative coordinates
+        for f in "xyz":
+            cloud[f] -= np.median(cloud[f])
+    got = ctx.voxel_grid(cloud, leaf, want_cells=True)
+    ref = orc.voxel_grid(cloud, leaf)
+    assert got["m"] == len(ref["points"])
+    assert np.array_equal(got["min_b"], ref["min_b"]) and np.array_equal(got["div_b"], ref["div_b"])
+    assert np.array_equal(got["point_cell"], ref["point_cell"])
+    assert np.array_equal(got["cell_count"], ref["cell_count"])
+    assert_clouds_equal(got["points"], ref["points"])  # centroids, rgb repack, stamp_id, order
+
+
+def test_voxel_grid_xyz_only_and_nan(ctx, orc):
+    cloud = ctx.synth_cloud("strip", 30000, seed=6, centred=True)
+    cloud["x"][::97] = np.nan
+    got = ctx.voxel_grid(cloud, 0.1, downsample_all=False, want_cells=True)
+    ref = orc.voxel_grid(cloud, 0.1, downsample_all=False, is_dense=False)
+    assert got["m"] == len(ref["points"])
+    assert np.array_equal(got["point_cell"], ref["point_cell"])
+    assert np.array_equal(got["points"]["x"], ref["points"]["x"])
+    assert np.array_equal(got["points"]["y"], ref["points"]["y"])
+    assert np.array_equal(got["points"]["z"], ref["points"]["z"])
+    # all-negative axis: the DBL_MIN max seed of getMinMax3D (point_cloud_helper.h:65)
+    cloud = ctx.synth_cloud("uniform_cube", 5000, seed=6, centred=True)
+    cloud["y"] -= 100.0
+    got = ctx.voxel_grid(cloud, 0.25, want_cells=True)
+    ref = orc.voxel_grid(cloud, 0.25)
+    assert np.array_equal(got["div_b"], ref["div_b"])
+    assert_clouds_equal(got["points"], ref["points"])
+    mn, mx = ctx.minmax(cloud)
+    rmn, rmx = orc.minmax(cloud)
+    assert np.array_equal(mn, rmn) and np.array_equal(mx, rmx)
+
+
+def test_empty_inputs(ctx):
+    import pointcloudprocess_b200 as pcp
+    empty = np.zeros(0, dtype=pcp.POINT_DTYPE)
+    assert ctx.voxel_grid(empty, 0.1)["m"] == 0
+    ix = pcp.Index(ctx, empty)
+    assert ix.size() == 0
+    idx, d2, found = ix.knn(np.zeros((3, 3)), 5)
+    assert (idx == -1).all() and (found == 0).all()
+    assert len(ix.features_knn(20)["props"]) == 0
+    ix.free()
+
+
+@pytest.mark.parametrize("kind,n,leaf", [("strip", 200000, 0.04), ("city", 100000, 0.02), ("forest", 50000, 0.05)])
+def test_remove_duplicate_matches_oracle(ctx, orc, kind, n, leaf):
+    cloud = ctx.synth_cloud(kind, n, seed=12)  # UTM-scale coordinates: centring matters
+    got = ctx.remove_duplicate(cloud, leaf)
+    ref, centre = orc.remove_duplicate(cloud, leaf)
+    c, cnt = ctx.centroid(cloud)
+    assert np.array_equal(c, centre)  # serial-order sum reproduced bit-exactly
+    assert_clouds_equal(got, ref)
