@@ -96,6 +96,8 @@ PCP_API int pcp_dev_free(pcp_ctx* ctx, void* dptr);
 PCP_API int pcp_host_alloc_pinned(pcp_ctx* ctx, size_t bytes, void** hptr);
 PCP_API int pcp_host_free_pinned(pcp_ctx* ctx, void* hptr);
 PCP_API int pcp_memcpy(pcp_ctx* ctx, void* dst, const void* src, size_t bytes); /* any direction, synchronous */
+/* Same, ordered on the context's stream without waiting (host memory should be pinned to overlap). */
+PCP_API int pcp_memcpy_async(pcp_ctx* ctx, void* dst, const void* src, size_t bytes);
 
 /* ---- search structure ------------------------------------------------------------------------------
  * Replaces KdTreeFLANN<PointT>::setInputCloud + convertCloudToArray (kd_tree.h:772-798, 928-956):

@@ -138,6 +138,9 @@ class Context:
     def memcpy(self, dst, src, nbytes):
         self._check(self.L.pcp_memcpy(self.h, _ptr(dst), _ptr(src), int(nbytes)))
 
+    def memcpy_async(self, dst, src, nbytes):
+        self._check(self.L.pcp_memcpy_async(self.h, _ptr(dst), _ptr(src), int(nbytes)))
+
     def alloc(self, nbytes):
         return DeviceArray(self, nbytes)
 

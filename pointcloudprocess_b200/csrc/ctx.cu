@@ -305,4 +305,12 @@ int pcp_memcpy(pcp_ctx* ctx, void* dst, const void* src, size_t bytes)
     return PCP_OK;
 }
 
+int pcp_memcpy_async(pcp_ctx* ctx, void* dst, const void* src, size_t bytes)
+{
+    if (!ctx) return PCP_ERR_INVALID;
+    if (!bytes) return PCP_OK;
+    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, ctx->stream));
+    return PCP_OK;
+}
+
 } // extern "C"
