@@ -143,7 +143,7 @@ extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double*
                 W.qlist = fail_list.p;
             }
             {
-                StageTimer t(ctx, "knn.warp_kernel");
+                StageTimer t(ctx, "knn.warp_kernel", 72.0 * nfail); // bytes/72 = queries that fell back
                 PCP_TRY(run_wknn(ctx, W, nfail));
             }
             {

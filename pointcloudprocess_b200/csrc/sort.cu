@@ -54,3 +54,4 @@ template <typename T> static int excl_scan(pcp_ctx* ctx, const T* in, T* out, si
 }
 int pcp_exclusive_scan_u32(pcp_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n) { return excl_scan(ctx, in, out, n); }
 int pcp_exclusive_scan_u64(pcp_ctx* ctx, const unsigned long long* in, unsigned long long* out, size_t n) { return excl_scan(ctx, in, out, n); }
+int pcp_exclusive_scan_f64(pcp_ctx* ctx, const double* in, double* out, size_t n) { return excl_scan(ctx, in, out, n); }

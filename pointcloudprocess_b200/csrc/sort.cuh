@@ -12,3 +12,5 @@ int pcp_sort_pairs_u32(pcp_ctx* ctx, uint32_t** keys, uint32_t** keys_alt, uint3
 // exclusive prefix sum of n uint32 into n+1 outputs is done by callers via pcp_exclusive_scan_u32
 int pcp_exclusive_scan_u32(pcp_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n);
 int pcp_exclusive_scan_u64(pcp_ctx* ctx, const unsigned long long* in, unsigned long long* out, size_t n);
+// plain (non-reproducible-order) prefix sum of doubles: only used for predictions, never for results
+int pcp_exclusive_scan_f64(pcp_ctx* ctx, const double* in, double* out, size_t n);

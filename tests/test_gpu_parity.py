@@ -266,3 +266,53 @@ def test_remove_duplicate_matches_oracle(ctx, orc, kind, n, leaf):
     c, cnt = ctx.centroid(cloud)
     assert np.array_equal(c, centre)  # serial-order sum reproduced bit-exactly
     assert_clouds_equal(got, ref)
+
+
+# ---- serial-order centroid (compute3DCentroid, point_cloud_helper.h:192-230) -----------------------------------
+def _centroid_cases():
+    rng = np.random.default_rng(77)
+    n = 300_000
+    cases = {}
+    cases["utm"] = rng.uniform(0, 50, size=(n, 3)) + UTM
+    cases["centred_mixed_sign"] = rng.normal(size=(n, 3)) * [30.0, 5.0, 0.5]
+    cases["negative"] = -(rng.uniform(0, 50, size=(n, 3)) + UTM)
+    # round-half-even ties: once the running sum passes 2^62 its ulp is 2^10 and every odd multiple of 2^9 ties
+    t = 2.0 ** 45 + 2.0 ** 9 * rng.integers(0, 64, size=(n, 3))
+    cases["ties"] = t
+    cases["ties_negative"] = -t
+    sw = t.copy()
+    sw[n // 2:] *= -1.0  # climbs through the binades, then back down through them
+    cases["ties_up_then_down"] = sw
+    cases["huge_dynamic_range"] = rng.normal(size=(n, 3)) * 10.0 ** rng.integers(-12, 12, size=(n, 3))
+    cases["tiny_then_big"] = np.concatenate([rng.uniform(0, 1e-9, size=(n // 2, 3)), rng.uniform(0, 1e9, size=(n // 2, 3))])
+    z = rng.uniform(-1, 1, size=(n, 3))
+    z[::3] = 0.0
+    cases["zeros_and_cancellation"] = z
+    return cases
+
+
+@pytest.mark.parametrize("name", list(_centroid_cases().keys()))
+def test_serial_centroid_bit_exact(ctx, orc, name):
+    xyz = _centroid_cases()[name]
+    c, cnt = ctx.centroid(xyz)
+    rc, rcnt = orc.centroid(xyz, is_dense=False)
+    assert cnt == rcnt
+    assert c.tobytes() == rc.tobytes(), (name, c, rc)
+
+
+def test_serial_centroid_nan_and_sizes(ctx, orc):
+    rng = np.random.default_rng(78)
+    for n in (1, 31, 255, 257, 16383, 16384, 16385, 70000, 262144 + 5):
+        xyz = rng.uniform(0, 50, size=(n, 3)) + UTM
+        if n > 100:
+            xyz[rng.choice(n, n // 50, replace=False), rng.integers(0, 3, n // 50)] = np.nan
+        c, cnt = ctx.centroid(xyz)
+        rc, rcnt = orc.centroid(xyz, is_dense=False)
+        assert cnt == rcnt and c.tobytes() == rc.tobytes(), n
+
+
+def test_serial_centroid_full_size(ctx, orc):
+    cloud = ctx.synth_cloud("city", 5_000_000, seed=5)
+    c, cnt = ctx.centroid(cloud)
+    rc, rcnt = orc.centroid(cloud)
+    assert cnt == rcnt and c.tobytes() == rc.tobytes()
