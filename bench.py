@@ -10,7 +10,7 @@ shard (200 M / 8): weak scaling.
   value  : points that received features per second, inputs resident in HBM, device timed (CUDA events)
   e2e    : same through the C ABI with HOST buffers (pinned), H2D of the cloud and D2H of the
            LAS_POINT_PROPERTY records inside the timed region
-  roofline: dominant kernel (knn_cell_kernel): 72 B/point algorithmic bytes / its CUDA-event duration
+  roofline: dominant kernel (knn_fast_kernel): 72 B/point algorithmic bytes / its CUDA-event duration
   cpu_baseline: the oracle (CPU restatement of the reference path) on a bounded sample, host cores
 
 `--impl reference` times the oracle on the host cores only (rank 0), never touching the CUDA library.
@@ -280,16 +280,16 @@ def run_gpu(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md 6.65 TB/s)"
-    kst = [s for s in stages if s["name"] == "knn.cell_kernel"]
+    kst = [s for s in stages if s["name"] == "knn.fast_kernel"]
     if kst and kst[0]["ms"] > 0:
         s = kst[0]
         achieved = s["bytes"] / (s["ms"] * 1e-3) / 1e9
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "knn_cell_traffic.json"))).get("dram_bytes_per_launch")
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "knn_fast_traffic.json"))).get("dram_bytes_per_launch")
         except Exception:
             pass
-        roof = {"bound": "hbm", "kernel": "knn_cell_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        roof = {"bound": "hbm", "kernel": "knn_fast_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms_per_launch": s["ms"] / s["launches"], "algorithmic_bytes_per_launch": s["bytes"] / s["launches"],
                 "kernel_share_of_step": s["ms"] / (ms_total if world == 1 else e0.elapsed_time(e1))}
@@ -325,6 +325,7 @@ def run_gpu(args):
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "ms_per_step": e2e_ms},
                 "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof, "cpu_baseline": cpu,
+                "fallback_queries_per_step": sum(s["bytes"] for s in stages if s["name"] == "knn.warp_kernel") / 72.0 / args.steps,
                 "stages_ms_per_step": {s["name"]: round(s["ms"] / args.steps, 4) for s in stages}}
         print(json.dumps(line), flush=True)
     job.close()

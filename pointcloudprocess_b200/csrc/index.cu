@@ -30,7 +30,8 @@ __global__ void __launch_bounds__(256) morton_key_kernel(const char* __restrict_
 
 __global__ void __launch_bounds__(256) gather_rec_kernel(const char* __restrict__ pts, size_t stride,
                                                          const uint32_t* __restrict__ vals, size_t nv,
-                                                         pcp_rec* __restrict__ rec)
+                                                         pcp_rec* __restrict__ rec, float4* __restrict__ fpt,
+                                                         double ox, double oy, double oz)
 {
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= nv) return;
@@ -42,6 +43,7 @@ __global__ void __launch_bounds__(256) gather_rec_kernel(const char* __restrict_
     r.z = p[2];
     r.idx = (long long)o;
     rec[i] = r;
+    fpt[i] = make_float4((float)(r.x - ox), (float)(r.y - oy), (float)(r.z - oz), 0.f);
 }
 
 __global__ void __launch_bounds__(256) cell_flag_kernel(const unsigned long long* __restrict__ keys, size_t nv,
@@ -98,6 +100,58 @@ __global__ void __launch_bounds__(256) hash_insert_kernel(const unsigned long lo
             return;
         }
         s = (s + 1) & hmask;
+    }
+}
+
+// ---- level table: every cell of levels 0..PCP_HLEVELS-1 as a run of base cells ----
+__device__ __forceinline__ bool lvl_differs(const unsigned long long* __restrict__ ckey, uint32_t a, uint32_t b, int l)
+{
+    return (ckey[a] >> (3 * l)) != (ckey[b] >> (3 * l));
+}
+
+__global__ void __launch_bounds__(256) lhash_count_kernel(const unsigned long long* __restrict__ ckey, uint32_t ncell,
+                                                          unsigned long long* __restrict__ total)
+{
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned n = 0;
+    if (c < ncell)
+        for (int l = 0; l < PCP_HLEVELS; l++) n += (c == 0 || lvl_differs(ckey, c - 1, c, l)) ? 1u : 0u;
+    n = __reduce_add_sync(0xffffffffu, n);
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(total, (unsigned long long)n);
+}
+
+__global__ void __launch_bounds__(256) lhash_heads_kernel(const unsigned long long* __restrict__ ckey, uint32_t ncell,
+                                                          pcp_hslot* __restrict__ tab, uint32_t mask)
+{
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncell) return;
+    for (int l = 0; l < PCP_HLEVELS; l++) {
+        if (!(c == 0 || lvl_differs(ckey, c - 1, c, l))) continue;
+        const unsigned long long key = PCP_LKEY(l, ckey[c] >> (3 * l));
+        uint32_t s = pcp_hash64(key) & mask;
+        while (true) {
+            const unsigned long long prev = atomicCAS(&tab[s].key, PCP_EMPTY_KEY, key);
+            if (prev == PCP_EMPTY_KEY) {
+                tab[s].start = c;
+                tab[s].count = 0;
+                break;
+            }
+            s = (s + 1) & mask;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256) lhash_tails_kernel(const unsigned long long* __restrict__ ckey, uint32_t ncell,
+                                                          pcp_hslot* __restrict__ tab, uint32_t mask)
+{
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncell) return;
+    for (int l = 0; l < PCP_HLEVELS; l++) {
+        if (!(c == ncell - 1 || lvl_differs(ckey, c, c + 1, l))) continue;
+        const unsigned long long key = PCP_LKEY(l, ckey[c] >> (3 * l));
+        uint32_t s = pcp_hash64(key) & mask;
+        while (tab[s].key != key) s = (s + 1) & mask;
+        tab[s].count = c + 1 - tab[s].start;
     }
 }
 
@@ -164,9 +218,11 @@ static void index_release(pcp_index* ix)
     if (!ix) return;
     pcp_ctx* c = ix->ctx;
     pcp_arena_free(c, ix->rec);
+    pcp_arena_free(c, ix->fpt);
     pcp_arena_free(c, ix->ckey);
     pcp_arena_free(c, ix->cstart);
     pcp_arena_free(c, ix->htab);
+    pcp_arena_free(c, ix->ltab);
     pcp_arena_free(c, ix->item_cell);
     pcp_arena_free(c, ix->item_first);
     delete ix;
@@ -312,10 +368,22 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
     void* q = nullptr;
     IX_TRY(pcp_arena_alloc(ctx, nv * sizeof(pcp_rec), &q));
     ix->rec = (pcp_rec*)q;
+    IX_TRY(pcp_arena_alloc(ctx, nv * sizeof(float4), &q));
+    ix->fpt = (float4*)q;
     {
-        StageTimer t(ctx, "index.gather", 56.0 * nv);
+        // |float - true| <= half an ulp of the largest origin-relative coordinate, plus the rounding of the
+        // double subtraction p - origin
+        double emax = 0, cmax = 0;
+        for (int d = 0; d < 3; d++) {
+            emax = fmax(emax, bb.mx[d] - bb.mn[d]);
+            cmax = fmax(cmax, fmax(fabs(bb.mx[d]), fabs(bb.mn[d])));
+        }
+        ix->eps0 = emax * 5.97e-8 + cmax * 2.3e-16;
+        ix->epsd = cmax * 2.3e-16;
+        StageTimer t(ctx, "index.gather", 72.0 * nv);
         gather_rec_kernel<<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(static_cast<const char*>(dpts), stride,
-                                                                          vals, nv, ix->rec);
+                                                                          vals, nv, ix->rec, ix->fpt, ix->grid.org[0],
+                                                                          ix->grid.org[1], ix->grid.org[2]);
         ctx->launches++;
         IX_CUDA(cudaGetLastError());
     }
@@ -329,6 +397,30 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
         IX_CUDA(cudaMemsetAsync(ix->htab, 0xff, (size_t)cap * sizeof(pcp_hslot), ctx->stream));
         hash_insert_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->ckey, ix->cstart, ncell, ix->htab,
                                                                               ix->hmask);
+        ctx->launches++;
+        IX_CUDA(cudaGetLastError());
+    }
+    {
+        StageTimer t(ctx, "index.levels");
+        DevBuf<unsigned long long> tot;
+        IX_TRY(tot.alloc(ctx, 1));
+        IX_CUDA(cudaMemsetAsync(tot.p, 0, 8, ctx->stream));
+        lhash_count_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->ckey, ncell, tot.p);
+        ctx->launches++;
+        IX_CUDA(cudaGetLastError());
+        unsigned long long ne = 0;
+        IX_CUDA(cudaMemcpyAsync(&ne, tot.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        IX_CUDA(cudaStreamSynchronize(ctx->stream));
+        uint32_t cap = 64;
+        while ((unsigned long long)cap < 2ull * ne && cap < 0x80000000u) cap <<= 1;
+        ix->lmask = cap - 1;
+        IX_TRY(pcp_arena_alloc(ctx, (size_t)cap * sizeof(pcp_hslot), &q));
+        ix->ltab = (pcp_hslot*)q;
+        IX_CUDA(cudaMemsetAsync(ix->ltab, 0xff, (size_t)cap * sizeof(pcp_hslot), ctx->stream));
+        lhash_heads_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->ckey, ncell, ix->ltab, ix->lmask);
+        ctx->launches++;
+        IX_CUDA(cudaGetLastError());
+        lhash_tails_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->ckey, ncell, ix->ltab, ix->lmask);
         ctx->launches++;
         IX_CUDA(cudaGetLastError());
     }

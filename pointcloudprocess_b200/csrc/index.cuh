@@ -35,11 +35,17 @@ struct pcp_index {
     size_t n = 0;       // valid (finite) points == total_nr_points_
     pcp_grid grid;
     pcp_rec* rec = nullptr;
+    float4* fpt = nullptr;  // (float)(p - grid origin) of the sorted points, for the FP32 candidate filter
+    double eps0 = 0;        // bound on the error of those floats (see knn_fast.cuh)
+    double epsd = 0;        // bound on the rounding error of a double subtraction p - origin
     unsigned long long* ckey = nullptr;
     uint32_t* cstart = nullptr;
     uint32_t ncell = 0;
     pcp_hslot* htab = nullptr;
     uint32_t hmask = 0;
+    // cells of levels 0..PCP_HLEVELS-1: key (level<<58 | Morton prefix) -> (first base cell, base cells)
+    pcp_hslot* ltab = nullptr;
+    uint32_t lmask = 0;
     // per-cell work items for the cell-cooperative kernels: item -> (cell, chunk of 32 queries)
     uint32_t* item_cell = nullptr;
     uint32_t* item_first = nullptr; // first sorted point of the chunk
@@ -47,6 +53,8 @@ struct pcp_index {
 };
 
 #define PCP_EMPTY_KEY 0xffffffffffffffffull
+#define PCP_HLEVELS 5
+#define PCP_LKEY(level, prefix) (((unsigned long long)(level) << 58) | (prefix))
 
 __host__ __device__ __forceinline__ unsigned long long pcp_spread3(unsigned long long v)
 {

@@ -2,6 +2,9 @@
 // pcp_features_knn (the calculate_plan_parameter path, calculate_feature.h:15) and pcp_knn
 // (KdTreeFLANN::nearestKSearch, kd_tree.h:814-845).
 #include "knn_warp.cuh"
+#include "knn_far.cuh"
+#include <climits>
+#include <cstdlib>
 
 namespace {
 
@@ -42,6 +45,49 @@ template <int KPL> int launch_wknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint3
     return PCP_OK;
 }
 
+template <int CAP, int GS> int launch_fknn_t(pcp_ctx* ctx, const pcp_fknn_params& P)
+{
+    const size_t smem = PCP_FK_WARPS * pcp_fd_smem<CAP, GS>::bytes(P.k);
+    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_fast_kernel<CAP, GS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_fast_kernel<CAP, GS>, 32 * PCP_FK_WARPS, smem));
+    if (per_sm < 1) per_sm = 1;
+    // persistent warps: every resident slot of every SM is filled once, items come from the work counter
+    unsigned blocks = (unsigned)(ctx->sm_count * per_sm);
+    const unsigned need = pcp_blocks_for(P.nitem, PCP_FK_WARPS);
+    if (blocks > need) blocks = need;
+    knn_fast_kernel<CAP, GS><<<blocks, 32 * PCP_FK_WARPS, smem, ctx->stream>>>(P);
+    PCP_LAUNCH_CHECK(ctx);
+    return PCP_OK;
+}
+
+// list capacity CAP >= k plus room for the candidates of the boundary bucket
+int launch_fknn(pcp_ctx* ctx, const pcp_fknn_params& P)
+{
+    if (P.kk <= 24) return launch_fknn_t<32, 8>(ctx, P);
+    if (P.kk <= 52) return launch_fknn_t<64, 8>(ctx, P);
+    return launch_fknn_t<160, 8>(ctx, P);
+}
+
+template <int CAP> int launch_far_t(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)
+{
+    const size_t smem = PCP_FK_WARPS * pcp_far_smem<CAP>::bytes(P.k);
+    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_far_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_far_kernel<CAP>, 32 * PCP_FK_WARPS, smem));
+    if (per_sm < 1) per_sm = 1;
+    knn_far_kernel<CAP><<<ctx->sm_count * per_sm, 32 * PCP_FK_WARPS, smem, ctx->stream>>>(P, A);
+    PCP_LAUNCH_CHECK(ctx);
+    return PCP_OK;
+}
+
+int launch_far(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)
+{
+    if (P.kk <= 24) return launch_far_t<32>(ctx, P, A);
+    if (P.kk <= 52) return launch_far_t<64>(ctx, P, A);
+    return launch_far_t<160>(ctx, P, A);
+}
+
 int run_wknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint32_t expected)
 {
     if (P.k <= 32) return launch_wknn<1>(ctx, P, expected);
@@ -74,15 +120,22 @@ extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double*
     }
     if (nv > 0 && kk > 0) {
         DevBuf<uint32_t> fail_list, counters;
+        DevBuf<float> fail_u;
         PCP_TRY(fail_list.alloc(ctx, nv));
-        PCP_TRY(counters.alloc(ctx, 2));
-        PCP_CUDA_TRY(ctx, cudaMemsetAsync(counters.p, 0, 8, ctx->stream));
+        PCP_TRY(fail_u.alloc(ctx, nv));
+        DevBuf<uint32_t> fail2;
+        PCP_TRY(fail2.alloc(ctx, nv));
+        PCP_TRY(counters.alloc(ctx, 8));
+        PCP_CUDA_TRY(ctx, cudaMemsetAsync(counters.p, 0, 32, ctx->stream));
         uint32_t nfail = 0;
-        if (kk <= 64) {
-            pcp_knn_params P;
+        if (kk <= 128) {
+            pcp_fknn_params P;
             P.rec = ix->rec;
+            P.fpt = ix->fpt;
             P.htab = ix->htab;
             P.hmask = ix->hmask;
+            P.ltab = ix->ltab;
+            P.lmask = ix->lmask;
             P.ckey = ix->ckey;
             P.cstart = ix->cstart;
             P.ncell = ix->ncell;
@@ -92,22 +145,56 @@ extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double*
             P.g = ix->grid;
             P.k = k;
             P.kk = kk;
-            P.cap = kk + 12;
+            P.eps0 = ix->eps0;
+            P.epsd = ix->epsd;
+            P.query_limit = LLONG_MAX;
             P.props = o_props.dptr;
             P.eig3 = (double*)o_eig.dptr;
             P.lps3 = (float*)o_lps.dptr;
             P.knn_idx = (int32_t*)o_idx.dptr;
             P.fail_list = fail_list.p;
+            P.fail_u = fail_u.p;
             P.fail_count = counters.p;
-            size_t smem = PCP_KNN_WARPS * ((size_t)PCP_KNN_NB * 32 * 4 + (size_t)P.cap * 32 * 12);
-            PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_cell_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            {
-                StageTimer t(ctx, "knn.cell_kernel", 72.0 * nv);
-                knn_cell_kernel<<<pcp_blocks_for(ix->nitem, PCP_KNN_WARPS), 32 * PCP_KNN_WARPS, smem, ctx->stream>>>(P);
-                PCP_LAUNCH_CHECK(ctx);
+            P.work_counter = counters.p + 2;
+            P.dbg = nullptr;
+            DevBuf<unsigned long long> dbg;
+            const bool want_dbg = getenv("PCP_KNN_DEBUG") != nullptr;
+            if (want_dbg) {
+                PCP_TRY(dbg.alloc(ctx, 16));
+                PCP_CUDA_TRY(ctx, cudaMemsetAsync(dbg.p, 0, 16 * 8, ctx->stream));
+                P.dbg = dbg.p;
             }
-            PCP_CUDA_TRY(ctx, cudaMemcpyAsync(&nfail, counters.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+            {
+                StageTimer t(ctx, "knn.fast_kernel", 72.0 * nv);
+                PCP_TRY(launch_fknn(ctx, P));
+            }
+            if (want_dbg) {
+                unsigned long long h[16];
+                PCP_CUDA_TRY(ctx, cudaMemcpyAsync(h, dbg.p, 16 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+                PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+                fprintf(stderr, "[pcp knn] h=%.4f items=%llu staged=%llu queries=%llu cand/item=%.1f dense_items=%llu ok1=%llu ranged_second=%llu "
+                                "uncert=%llu overflow=%llu ranged_attempts=%llu ranged_cand/attempt=%.1f ranged_uncert=%llu\n", ix->grid.h,
+                        h[0], h[1], h[2], h[0] ? (double)h[3] / h[0] : 0.0, h[4], h[5], h[6], h[7], h[8], h[9],
+                        h[9] ? (double)h[10] / h[9] : 0.0, h[11]);
+            }
+            {
+                // everything the dense kernel left open: sparse cells, far neighbours, FP32 ambiguities
+                pcp_far_args A;
+                A.list = fail_list.p;
+                A.listU = fail_u.p;
+                A.count = counters.p;
+                A.work_counter = counters.p + 3;
+                A.fail_list = fail2.p;
+                A.fail_count = counters.p + 4;
+                StageTimer t(ctx, "knn.far_kernel");
+                PCP_TRY(launch_far(ctx, P, A));
+            }
+            uint32_t hc[5];
+            PCP_CUDA_TRY(ctx, cudaMemcpyAsync(hc, counters.p, 20, cudaMemcpyDeviceToHost, ctx->stream));
             PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+            nfail = hc[4];
+            if (want_dbg) fprintf(stderr, "[pcp knn] far queries=%u, streaming-kernel queries=%u\n", hc[0], hc[4]);
+            if (nfail) PCP_CUDA_TRY(ctx, cudaMemcpyAsync(counters.p, &hc[4], 4, cudaMemcpyHostToDevice, ctx->stream));
         } else {
             // k too large for the cell kernel's shared-memory lists: every query takes the warp kernel
             nfail = (uint32_t)nv;
@@ -130,7 +217,7 @@ extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double*
             W.out_pos = nbr.p;
             W.work_counter = counters.p + 1;
             DevBuf<uint32_t> ident;
-            if (kk > 64) {
+            if (kk > 128) {
                 // identity query list with start level 0
                 PCP_TRY(ident.alloc(ctx, nv));
                 std::vector<uint32_t> h(nv);
@@ -140,7 +227,7 @@ extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double*
                 PCP_CUDA_TRY(ctx, cudaMemcpyAsync(counters.p, &nfail, 4, cudaMemcpyHostToDevice, ctx->stream));
                 W.qlist = ident.p;
             } else {
-                W.qlist = fail_list.p;
+                W.qlist = fail2.p;
             }
             {
                 StageTimer t(ctx, "knn.warp_kernel", 72.0 * nfail); // bytes/72 = queries that fell back

@@ -1,0 +1,308 @@
+// knn_far.cuh -- exact kNN + features for the queries the dense kernel (knn_fast.cuh) could not settle:
+// points in sparse cells, queries whose k-th neighbour reaches beyond the 3x3x3 block of base cells, and
+// queries whose FP32 ordering was ambiguous.  One warp per query; an implicit-octree search over the
+// Morton-sorted cells with sphere pruning at base-cell granularity:
+//   level   the smallest level whose 3x3x3 block of level cells certifies the known upper bound U of the
+//           k-th squared distance (U comes from the dense kernel), or -- without a bound -- the smallest
+//           level whose block holds k points;
+//   bound   without U: the occupied base cells of the block are binned by their FARTHEST corner distance,
+//           weighted by their point count; the bucket at which the count reaches k bounds the k-th distance;
+//   prune   base cells whose NEAREST corner distance exceeds the bound are dropped; the survivors'
+//           point ranges form the candidate set (typically a few dozen cells);
+//   search  pcp_fk_search (knn_fast.cuh): FP32 histogram filter on coordinates relative to the query, exact
+//           FP64 distances and (d2, index) ranking of the short list, certification against the block faces.
+// If the exact k-th distance still reaches beyond the block, it becomes the new U and the level goes up.
+#pragma once
+#include "knn_fast.cuh"
+
+#define PCP_FAR_NSEL 256 // selected base cells per attempt
+
+template <int CAP> struct pcp_far_smem : pcp_fk_smem<CAP, 32> {
+    uint32_t* selpre;   // [NSEL]  exclusive prefix of the selected cells' point counts (0xffffffff beyond)
+    uint32_t* selstart; // [NSEL]  first point of the selected cell
+    static __host__ __device__ size_t bytes(int k) { return pcp_fk_smem<CAP, 32>::bytes(k) + PCP_FAR_NSEL * 8; }
+    __device__ pcp_far_smem(unsigned char* base, int k) : pcp_fk_smem<CAP, 32>(base, k)
+    {
+        selpre = reinterpret_cast<uint32_t*>(base + pcp_fk_smem<CAP, 32>::bytes(k));
+        selstart = selpre + PCP_FAR_NSEL;
+    }
+};
+
+// candidates = the points of the selected cells, staged CAND at a time as floats relative to the query
+struct pcp_far_src {
+    const pcp_rec* rec;
+    float4* cand;
+    const uint32_t* selpre;
+    const uint32_t* selstart;
+    uint32_t T;
+    double qx, qy, qz;
+    bool resident; // T <= CAND and already staged
+
+    __device__ __forceinline__ void stage(uint32_t c0, int lane) const
+    {
+        __syncwarp();
+#pragma unroll 1
+        for (int part = 0; part < PCP_FK_CAND / 128; part++) {
+            pcp_rec r[4];
+            uint32_t ps[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint32_t fl = c0 + part * 128 + lane + 32 * i;
+                int c = 0;
+#pragma unroll
+                for (int step = PCP_FAR_NSEL / 2; step; step >>= 1)
+                    if (selpre[c + step] <= fl) c += step;
+                ps[i] = selstart[c] + (fl - selpre[c]);
+                if (fl < T) r[i] = pcp_load_rec(rec, ps[i]);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                if (c0 + part * 128 + lane + 32 * i < T)
+                    cand[part * 128 + lane + 32 * i] = make_float4((float)(r[i].x - qx), (float)(r[i].y - qy),
+                                                                   (float)(r[i].z - qz), __uint_as_float(ps[i]));
+        }
+        __syncwarp();
+    }
+    template <class F> __device__ __forceinline__ void for_each(int lane, F f) const
+    {
+        for (uint32_t c0 = 0; c0 < T; c0 += PCP_FK_CAND) {
+            if (!resident) stage(c0, lane);
+            const int n = (int)min((uint32_t)PCP_FK_CAND, T - c0);
+            for (int f0 = 0; f0 < n; f0 += 32) {
+                const int i = f0 + lane;
+                const bool valid = i < n;
+                const float4 c = cand[valid ? i : 0];
+                f(valid, c.x, c.y, c.z, __float_as_uint(c.w));
+            }
+        }
+    }
+};
+
+// base-cell index range [ca, cb) of the level-`level` cell (cx,cy,cz) (binary search in the sorted cell keys)
+__device__ __forceinline__ void pcp_level_cells(const unsigned long long* __restrict__ ckey, uint32_t ncell, int level,
+                                                int cx, int cy, int cz, uint32_t& ca, uint32_t& cb)
+{
+    const unsigned long long pre = pcp_morton(cx, cy, cz);
+    const int sh = 3 * level;
+    const unsigned long long klo = sh >= 64 ? 0ull : (pre << sh);
+    const unsigned long long khi = sh >= 64 ? PCP_EMPTY_KEY : ((pre + 1) << sh);
+    uint32_t a = 0, b = ncell;
+    while (a < b) {
+        const uint32_t m = (a + b) >> 1;
+        if (__ldg(ckey + m) < klo) a = m + 1; else b = m;
+    }
+    ca = a;
+    b = ncell;
+    while (a < b) {
+        const uint32_t m = (a + b) >> 1;
+        if (__ldg(ckey + m) < khi) a = m + 1; else b = m;
+    }
+    cb = a;
+}
+
+// squared distance from q to the nearest / farthest point of base cell (ix,iy,iz), with outward margins
+__device__ __forceinline__ void pcp_cell_dist2(const pcp_grid& g, int ix, int iy, int iz, double qx, double qy, double qz,
+                                               float& mind2, float& maxd2)
+{
+    const double q[3] = {qx, qy, qz};
+    const int c[3] = {ix, iy, iz};
+    float mn = 0.f, mx = 0.f;
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        const float lo = (float)(g.org[a] + (double)c[a] * g.h - q[a]);
+        const float hi = (float)(g.org[a] + (double)(c[a] + 1) * g.h - q[a]);
+        const float dn = fmaxf(fmaxf(lo, -hi), 0.f);
+        const float dx = fmaxf(fabsf(lo), fabsf(hi));
+        mn = __fmaf_rn(dn, dn, mn);
+        mx = __fmaf_rn(dx, dx, mx);
+    }
+    mind2 = mn * 0.9999f;
+    maxd2 = mx * 1.0001f;
+}
+
+// first histogram bucket (64 buckets, 2 per lane) at which the cumulative count reaches kk, or 64
+__device__ __forceinline__ int pcp_hist_find32(const uint32_t* hist, int lane, uint32_t kk)
+{
+    const uint32_t h0 = hist[2 * lane], h1 = hist[2 * lane + 1];
+    uint32_t incl = h0 + h1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    const unsigned bal = __ballot_sync(0xffffffffu, incl >= kk);
+    if (!bal) return PCP_FK_NB;
+    const int L = __ffs(bal) - 1;
+    const uint32_t c0L = __shfl_sync(0xffffffffu, incl - h1, L);
+    return c0L >= kk ? 2 * L : 2 * L + 1;
+}
+
+struct pcp_far_args {
+    const uint32_t* list;    // sorted positions of the queries
+    const float* listU;      // upper bound of the k-th squared distance; +inf: none; -1: none, dense block
+    const uint32_t* count;   // number of entries (device)
+    uint32_t* work_counter;
+    uint32_t* fail_list;     // queries for the streaming FP64 kernel (list overflow)
+    uint32_t* fail_count;
+};
+
+template <int CAP>
+static __global__ void __launch_bounds__(32 * PCP_FK_WARPS) knn_far_kernel(pcp_fknn_params P, pcp_far_args A)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const pcp_far_smem<CAP> S(smem_raw + pcp_far_smem<CAP>::bytes(P.k) * warp, P.k);
+    S.sqpos[lane] = 0xffffffffu;
+    __syncwarp();
+    int fill = 0;
+    const uint32_t nq = *A.count;
+    const float e1 = (float)(2.0 * P.epsd) * 1.0001f;
+    const float INF = __int_as_float(0x7f800000);
+    while (true) {
+        uint32_t qi = 0;
+        if (lane == 0) qi = atomicAdd(A.work_counter, 1u);
+        qi = __shfl_sync(0xffffffffu, qi, 0);
+        if (qi >= nq) break;
+        const uint32_t qpos = __ldg(A.list + qi);
+        float U = __ldg(A.listU + qi);
+        const pcp_rec q = pcp_load_rec(P.rec, qpos);
+        const int bx = min(max(pcp_cell_coord(q.x, P.g.org[0], P.g.inv_h, 0), 0), P.g.dims[0] - 1);
+        const int by = min(max(pcp_cell_coord(q.y, P.g.org[1], P.g.inv_h, 0), 0), P.g.dims[1] - 1);
+        const int bz = min(max(pcp_cell_coord(q.z, P.g.org[2], P.g.inv_h, 0), 0), P.g.dims[2] - 1);
+        int level = (U == INF) ? 1 : 0;
+        if (U < 0.f) U = INF;
+        if (fill == 32) {
+            pcp_fk_flush(P, S, lane);
+            fill = 0;
+        }
+        const int slot = fill;
+        int st = PCP_FK_BEYOND;
+        for (; level <= P.g.top_level; level++) {
+            const int lx = bx >> level, ly = by >> level, lz = bz >> level;
+            const double g2 = pcp_guarantee2(P.g, level, lx, ly, lz, q.x, q.y, q.z);
+            if (U != INF && !((double)U < g2) && level < P.g.top_level) continue; // this block cannot certify U
+            // ---- the occupied base cells of the 27 level cells ----
+            uint32_t ca = 0, cb = 0;
+            if (lane < 27) {
+                int dx, dy, dz;
+                pcp_nb_offset(lane, dx, dy, dz);
+                const int nx = lx + dx, ny = ly + dy, nz = lz + dz;
+                const int mx = (P.g.dims[0] - 1) >> level, my = (P.g.dims[1] - 1) >> level, mz = (P.g.dims[2] - 1) >> level;
+                if (nx >= 0 && ny >= 0 && nz >= 0 && nx <= mx && ny <= my && nz <= mz) {
+                    if (level < PCP_HLEVELS) {
+                        uint32_t cn = 0;
+                        if (pcp_hash_find(P.ltab, P.lmask, PCP_LKEY(level, pcp_morton(nx, ny, nz)), ca, cn)) cb = ca + cn;
+                    } else {
+                        pcp_level_cells(P.ckey, P.ncell, level, nx, ny, nz, ca, cb);
+                    }
+                }
+            }
+            uint32_t cpre = cb - ca;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, cpre, o);
+                if (lane >= o) cpre += v;
+            }
+            const uint32_t NC = __shfl_sync(0xffffffffu, cpre, 31);
+            __syncwarp();
+            S.tab[lane] = lane < 27 ? cpre - (cb - ca) : 0xffffffffu;
+            S.tab[32 + lane] = ca;
+            __syncwarp();
+            float Ueff = U;
+            if (U == INF) {
+                uint32_t tl = (cb > ca) ? __ldg(P.cstart + cb) - __ldg(P.cstart + ca) : 0u;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) tl += __shfl_xor_sync(0xffffffffu, tl, o);
+                if (tl < (uint32_t)P.kk && level < P.g.top_level) continue;
+                // ---- bound: cells binned by farthest-corner distance, weighted by point count ----
+                const double H = ldexp(P.g.h, level);
+                const float topA = (float)(27.0 * H * H) * 1.001f;
+                const int key0 = (__float_as_int(topA) >> 21) - (PCP_FK_NB - 2);
+                S.hist[lane] = 0;
+                S.hist[lane + 32] = 0;
+                __syncwarp();
+                for (uint32_t c0 = 0; c0 < NC; c0 += 32) {
+                    const uint32_t fc = c0 + lane;
+                    if (fc < NC) {
+                        int t = 0;
+#pragma unroll
+                        for (int step = 16; step; step >>= 1)
+                            if (S.tab[t + step] <= fc) t += step;
+                        const uint32_t ci = S.tab[32 + t] + (fc - S.tab[t]);
+                        int ix, iy, iz;
+                        pcp_demorton(__ldg(P.ckey + ci), ix, iy, iz);
+                        float mn, mx;
+                        pcp_cell_dist2(P.g, ix, iy, iz, q.x, q.y, q.z, mn, mx);
+                        atomicAdd(&S.hist[pcp_fk_bucket(mx, key0)], __ldg(P.cstart + ci + 1) - __ldg(P.cstart + ci));
+                    }
+                }
+                __syncwarp();
+                const int bA = pcp_hist_find32(S.hist, lane, (uint32_t)P.kk);
+                Ueff = bA >= PCP_FK_NB - 1 ? topA : pcp_fk_edge(bA, key0);
+                __syncwarp();
+            }
+            // ---- prune: keep the base cells the sphere of radius sqrt(Ueff) touches ----
+            uint32_t nsel = 0;
+            __syncwarp();
+            for (int i = lane; i < PCP_FAR_NSEL; i += 32) S.selpre[i] = 0xffffffffu;
+            __syncwarp();
+            for (uint32_t c0 = 0; c0 < NC; c0 += 32) {
+                const uint32_t fc = c0 + lane;
+                bool sel = false;
+                uint32_t cs = 0, cc = 0;
+                if (fc < NC) {
+                    int t = 0;
+#pragma unroll
+                    for (int step = 16; step; step >>= 1)
+                        if (S.tab[t + step] <= fc) t += step;
+                    const uint32_t ci = S.tab[32 + t] + (fc - S.tab[t]);
+                    int ix, iy, iz;
+                    pcp_demorton(__ldg(P.ckey + ci), ix, iy, iz);
+                    float mn, mx;
+                    pcp_cell_dist2(P.g, ix, iy, iz, q.x, q.y, q.z, mn, mx);
+                    sel = mn <= Ueff;
+                    if (sel) cs = __ldg(P.cstart + ci), cc = __ldg(P.cstart + ci + 1) - cs;
+                }
+                const unsigned mask = __ballot_sync(0xffffffffu, sel);
+                const uint32_t at = nsel + __popc(mask & ((1u << lane) - 1u));
+                if (sel && at < PCP_FAR_NSEL) S.selstart[at] = cs, S.selpre[at] = cc;
+                nsel += __popc(mask);
+            }
+            __syncwarp();
+            if (nsel > PCP_FAR_NSEL) {
+                st = PCP_FK_OVERFLOW;
+                break;
+            }
+            // exclusive prefix of the counts
+            uint32_t T = 0;
+            for (uint32_t c0 = 0; c0 < nsel; c0 += 32) {
+                const uint32_t i = c0 + lane;
+                const uint32_t cnt = i < nsel ? S.selpre[i] : 0u;
+                uint32_t inc = cnt;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+                    if (lane >= o) inc += v;
+                }
+                if (i < nsel) S.selpre[i] = T + inc - cnt;
+                T += __shfl_sync(0xffffffffu, inc, 31);
+            }
+            __syncwarp();
+            pcp_far_src src{P.rec, S.cand, S.selpre, S.selstart, T, q.x, q.y, q.z, T <= PCP_FK_CAND};
+            if (src.resident) src.stage(0, lane);
+            double dk;
+            const float top = Ueff * 1.001f;
+            st = pcp_fk_search<32, CAP>(src, S, P.rec, lane, true, slot, P.kk, 0.f, 0.f, 0.f, q.x, q.y, q.z, top, g2, e1, dk);
+            if (st == PCP_FK_OK || st == PCP_FK_OVERFLOW) break;
+            if (st == PCP_FK_UNCERT) U = __double2float_ru(dk) * 1.000001f; // exact k-th of the scanned set: a true bound
+        }
+        if (st == PCP_FK_OK) {
+            S.sqpos[slot] = qpos;
+            fill++;
+        } else {
+            if (lane == 0) A.fail_list[atomicAdd(A.fail_count, 1u)] = qpos;
+        }
+    }
+    pcp_fk_flush(P, S, lane);
+}

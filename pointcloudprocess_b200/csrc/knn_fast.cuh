@@ -1,0 +1,639 @@
+// knn_fast.cuh -- the hot kernel: exact kNN(k) + plane-fit features in one pass over the Morton-sorted cloud.
+//
+// Persistent warps pull "items" (up to 32 consecutive queries of one base cell) from a global counter.
+//   stage    the FP32 copies of the points of the 3x3x3 block of cells around the item's cell are staged
+//            once per item in shared memory (all queries of the item share them);
+//   search   a query is handled by a group of G lanes (G = 8: four queries of the item in flight per warp;
+//            G = 32 for sparse cells and for the level escalation):
+//     pass 1   the lanes evaluate candidates in FP32 (coordinates relative to the grid origin) and bin the
+//              squared distances into a 64-bucket shared-memory histogram; a group scan finds the bucket b*
+//              at which the cumulative count reaches k;
+//     pass 2   candidates with d2 <= edge(b*+1) + 3*delta are compacted (ballot) into a short list, delta
+//              being a rigorous bound on the FP32 error, so the list provably contains the true k nearest;
+//     refine   the listed candidates get their exact FP64 squared distance (FLANN L2_Simple order, no FMA)
+//              and are ranked by (d2, original index); ranks < k are the answer, already in order;
+//     certify  edge(b*+1) + 2*delta must lie inside the distance from the query to the faces of the
+//              scanned block, otherwise the query moves up one level (cell edge doubles) and scans point
+//              ranges straight from global memory with the whole warp;
+//   features finished queries are parked in 32 shared-memory slots; when the slots are full every lane takes
+//            one query and runs calculate_plan_parameter_h_points (calculate_feature.cpp:119-206) on its k
+//            neighbours in ascending-distance order -- neighbour lists never leave the SM.
+// Queries that overflow the list (mass ties / duplicates) go to the streaming FP64 kernel in knn_warp.cuh.
+#pragma once
+#include "knn_cell.cuh"
+
+#define PCP_FK_NB 64      // histogram buckets (last one = beyond range)
+#define PCP_FK_CAND 256   // staged candidates per item
+#define PCP_FK_WARPS 4
+
+struct pcp_fknn_params {
+    const pcp_rec* rec;
+    const float4* fpt; // (float)(p - grid origin); w unused
+    const pcp_hslot* htab;
+    uint32_t hmask;
+    const pcp_hslot* ltab; // level table (index.cuh)
+    uint32_t lmask;
+    const unsigned long long* ckey;
+    const uint32_t* cstart;
+    uint32_t ncell;
+    const uint32_t* item_cell;
+    const uint32_t* item_first;
+    uint32_t nitem;
+    pcp_grid g;
+    int k, kk;
+    double eps0;           // bound on |float coordinate - true coordinate relative to the origin|
+    double epsd;           // bound on the rounding of a double subtraction p - origin
+    long long query_limit; // points with original index >= query_limit are candidates only (halo points)
+    void* props;
+    double* eig3;
+    float* lps3;
+    int32_t* knn_idx;
+    uint32_t* fail_list;     // far list: sorted positions ...
+    float* fail_u;           // ... and the known upper bound of the k-th squared distance (+inf: none)
+    uint32_t* fail_count;
+    uint32_t* work_counter;  // item dispenser
+    unsigned long long* dbg; // optional counters (PCP_KNN_DEBUG=1), NULL in production
+};
+
+#define PCP_FK_DBG(i, v)                                                                                     \
+    do {                                                                                                     \
+        if (P.dbg && lane == 0) atomicAdd(P.dbg + (i), (unsigned long long)(v));                             \
+    } while (0)
+
+// per-warp shared memory.  CAP = list capacity per query; the staged path runs 32/G queries at once, each
+// with its own histogram and list, the full-warp path uses set 0.
+template <int CAP, int GS> struct pcp_fk_smem {
+    static constexpr int NSET = 32 / GS;
+    float4* cand;    // [PCP_FK_CAND]
+    double* ld2;     // [NSET][CAP]
+    uint32_t* hist;  // [NSET][PCP_FK_NB]
+    uint32_t* lpos;  // [NSET][CAP]
+    int* lidx;       // [NSET][CAP]
+    uint32_t* nbr;   // [k][32]   neighbour positions of the parked queries
+    uint32_t* sqpos; // [32]      sorted position of the parked query (0xffffffff = empty slot)
+    uint32_t* tab;   // [64]      flat-index table of the 27 cell ranges: prefix[32], start[32]
+    static __host__ __device__ size_t bytes(int k)
+    {
+        return (size_t)PCP_FK_CAND * 16 + (size_t)NSET * CAP * 16 + (size_t)NSET * PCP_FK_NB * 4 + (size_t)32 * k * 4 + 128 + 256;
+    }
+    __device__ pcp_fk_smem(unsigned char* base, int k)
+    {
+        cand = reinterpret_cast<float4*>(base);
+        ld2 = reinterpret_cast<double*>(base + PCP_FK_CAND * 16);
+        hist = reinterpret_cast<uint32_t*>(base + PCP_FK_CAND * 16 + NSET * CAP * 8);
+        lpos = hist + NSET * PCP_FK_NB;
+        lidx = reinterpret_cast<int*>(lpos + NSET * CAP);
+        nbr = reinterpret_cast<uint32_t*>(lidx + NSET * CAP);
+        sqpos = nbr + 32 * k;
+        tab = sqpos + 32;
+    }
+};
+
+// candidate sources: every lane of the warp must call f(valid, x, y, z, pos) the same number of times
+template <int G> struct pcp_fk_staged {
+    const float4* cand;
+    int T;
+    template <class F> __device__ __forceinline__ void for_each(int gl, F f) const
+    {
+        for (int f0 = 0; f0 < T; f0 += G) {
+            const int i = f0 + gl;
+            const bool valid = i < T;
+            const float4 c = cand[valid ? i : 0];
+            f(valid, c.x, c.y, c.z, __float_as_uint(c.w));
+        }
+    }
+};
+
+// Full warp: the points of 27 cell ranges, flattened and staged through shared memory CAND at a time with
+// PCP_FK_CAND/32 independent loads in flight per lane (one memory latency per chunk instead of one per round).
+// tab[0..31] = exclusive prefix of the range sizes (0xffffffff beyond the 27th), tab[32..63] = range starts.
+struct pcp_fk_chunked {
+    const float4* fpt;
+    float4* cand;
+    const uint32_t* tab;
+    uint32_t T;
+    template <class F> __device__ __forceinline__ void for_each(int lane, F f) const
+    {
+        constexpr int R = PCP_FK_CAND / 32;
+        for (uint32_t c0 = 0; c0 < T; c0 += PCP_FK_CAND) {
+            __syncwarp();
+            float4 v[R];
+            uint32_t ps[R];
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                const uint32_t fl = c0 + lane + 32 * i;
+                int nb = 0;
+#pragma unroll
+                for (int step = 16; step; step >>= 1)
+                    if (tab[nb + step] <= fl) nb += step;
+                ps[i] = tab[32 + nb] + (fl - tab[nb]);
+                if (fl < T) v[i] = __ldg(fpt + ps[i]);
+            }
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                v[i].w = __uint_as_float(ps[i]);
+                if (c0 + lane + 32 * i < T) cand[lane + 32 * i] = v[i];
+            }
+            __syncwarp();
+            const int n = (int)min((uint32_t)PCP_FK_CAND, T - c0);
+            for (int f0 = 0; f0 < n; f0 += 32) {
+                const int i = f0 + lane;
+                const bool valid = i < n;
+                const float4 c = cand[valid ? i : 0];
+                f(valid, c.x, c.y, c.z, __float_as_uint(c.w));
+            }
+        }
+    }
+};
+
+// status of one search attempt
+#define PCP_FK_OK 0
+#define PCP_FK_BEYOND 1   // the k-th neighbour lies beyond the histogram range
+#define PCP_FK_UNCERT 2   // found, but not provably inside the scanned block
+#define PCP_FK_OVERFLOW 3 // more candidates than the list holds (ties / duplicates)
+#define PCP_FK_IDLE 4     // the group had no query
+
+// Logarithmic distance buckets, 4 per octave of d2, read straight off the float bits: no range to guess.
+// key(d2) = bits >> 21; bucket = clamp(key - (key(top) - 62), 0, 63); bucket 63 = beyond `top`.
+__device__ __forceinline__ int pcp_fk_bucket(float d2, int key0)
+{
+    return min(max((__float_as_int(d2) >> 21) - key0, 0), PCP_FK_NB - 1);
+}
+// exclusive upper edge of bucket b (b <= 62)
+__device__ __forceinline__ float pcp_fk_edge(int b, int key0) { return __int_as_float((key0 + b + 1) << 21); }
+
+// One search attempt (warp-collective; every group of G lanes works on its own query, or idles).
+// `top`: squared distance beyond which candidates are of no interest (they land in the last bucket).
+// On PCP_FK_OK the kk nearest (sorted positions) are in nbr[e*32 + slot], ascending by (d2, original index),
+// and the exact k-th squared distance is < g2.  On PCP_FK_UNCERT the list holds the kk nearest of the
+// scanned candidates and dk is their exact k-th squared distance: an upper bound of the true one.
+template <int G, int CAP, int GS, class Src>
+__device__ __forceinline__ int pcp_fk_search(const Src& src, const pcp_fk_smem<CAP, GS>& S, const pcp_rec* __restrict__ rec,
+                                             int lane, bool active, int slot, int kk, float qfx, float qfy, float qfz,
+                                             double qx, double qy, double qz, float top, double g2, float e1, double& dk)
+{
+    constexpr int SL = CAP / G;        // list entries per lane
+    constexpr int NBL = PCP_FK_NB / G; // histogram buckets per lane
+    const int gl = lane & (G - 1), gbase = lane & ~(G - 1), set = (G == 32) ? 0 : lane / G;
+    const unsigned gmask = (G == 32) ? 0xffffffffu : ((1u << G) - 1u);
+    uint32_t* hist = S.hist + set * PCP_FK_NB;
+    uint32_t* lpos = S.lpos + set * CAP;
+    int* lidx = S.lidx + set * CAP;
+    double* ld2 = S.ld2 + set * CAP;
+    const int key0 = (__float_as_int(top) >> 21) - (PCP_FK_NB - 2);
+#pragma unroll
+    for (int i = 0; i < NBL; i++) hist[gl + i * G] = 0;
+    __syncwarp();
+    // ---- pass 1: histogram ----
+    src.for_each(gl, [&](bool valid, float x, float y, float z, uint32_t) {
+        const float dx = qfx - x, dy = qfy - y, dz = qfz - z;
+        const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+        if (valid && active) atomicAdd(&hist[pcp_fk_bucket(d2, key0)], 1u);
+    });
+    __syncwarp();
+    // ---- scan: first bucket at which the cumulative count reaches kk ----
+    uint32_t hb[NBL];
+    if constexpr (NBL == 8) {
+        const uint4 a = *reinterpret_cast<const uint4*>(hist + gl * 8);
+        const uint4 b = *reinterpret_cast<const uint4*>(hist + gl * 8 + 4);
+        hb[0] = a.x, hb[1] = a.y, hb[2] = a.z, hb[3] = a.w, hb[4] = b.x, hb[5] = b.y, hb[6] = b.z, hb[7] = b.w;
+    } else {
+#pragma unroll
+        for (int i = 0; i < NBL; i++) hb[i] = hist[gl * NBL + i];
+    }
+    uint32_t tot = 0;
+#pragma unroll
+    for (int i = 0; i < NBL; i++) tot += hb[i];
+    uint32_t incl = tot;
+#pragma unroll
+    for (int o = 1; o < G; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o, G);
+        if (gl >= o) incl += v;
+    }
+    int st = active ? PCP_FK_OK : PCP_FK_IDLE;
+    const unsigned bal = (__ballot_sync(0xffffffffu, incl >= (uint32_t)kk) >> gbase) & gmask;
+    if (!bal && active) st = PCP_FK_BEYOND;
+    const int L = bal ? __ffs(bal) - 1 : 0;
+    int myb = PCP_FK_NB;
+    {
+        uint32_t c = incl - tot;
+#pragma unroll
+        for (int i = 0; i < NBL; i++) {
+            c += hb[i];
+            if (myb == PCP_FK_NB && c >= (uint32_t)kk) myb = gl * NBL + i;
+        }
+    }
+    const int bstar = __shfl_sync(0xffffffffu, myb, gbase + L);
+    if (st == PCP_FK_OK && bstar >= PCP_FK_NB - 1) st = PCP_FK_BEYOND;
+    // every true kk-nearest has FP32 d2 <= edge + 3*delta (delta: FP32 error bound at that distance)
+    const float edge = pcp_fk_edge(min(bstar, PCP_FK_NB - 2), key0);
+    const float delta = 4.0f * sqrtf(edge) * e1 + 4.0f * e1 * e1 + 1e-6f * edge;
+    const float thr = (edge + 3.0f * delta) * 1.000001f;
+    bool live = st == PCP_FK_OK;
+    // ---- pass 2: compact every candidate that can be among the kk nearest ----
+    uint32_t m = 0;
+    src.for_each(gl, [&](bool valid, float x, float y, float z, uint32_t pos) {
+        const float dx = qfx - x, dy = qfy - y, dz = qfz - z;
+        const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+        const bool in = live && valid && d2 <= thr;
+        const unsigned mask = (__ballot_sync(0xffffffffu, in) >> gbase) & gmask;
+        const uint32_t at = m + __popc(mask & ((1u << gl) - 1u));
+        if (in && at < (uint32_t)CAP) lpos[at] = pos;
+        m += __popc(mask);
+    });
+    if (live && m > (uint32_t)CAP) st = PCP_FK_OVERFLOW, live = false;
+    __syncwarp();
+    // ---- refine: exact squared distances, rank by (d2, original index) ----
+    double d2s[SL];
+    int ids[SL];
+    uint32_t ps[SL];
+#pragma unroll
+    for (int s = 0; s < SL; s++) {
+        const int e = s * G + gl;
+        d2s[s] = DBL_MAX, ids[s] = 0x7fffffff, ps[s] = 0;
+        if (live && e < (int)m) {
+            ps[s] = lpos[e];
+            const pcp_rec r = pcp_load_rec(rec, ps[s]);
+            d2s[s] = pcp_dist2(qx, qy, qz, r.x, r.y, r.z);
+            ids[s] = (int)r.idx;
+            ld2[e] = d2s[s];
+            lidx[e] = ids[s];
+        }
+    }
+    __syncwarp();
+    const uint32_t mmax = __reduce_max_sync(0xffffffffu, live ? m : 0u);
+    int rank[SL];
+#pragma unroll
+    for (int s = 0; s < SL; s++) rank[s] = 0;
+    for (uint32_t j = 0; j < mmax; j++) {
+        const bool have = j < m;
+        const double dj = ld2[have ? j : 0];
+        const int ij = lidx[have ? j : 0];
+#pragma unroll
+        for (int s = 0; s < SL; s++) rank[s] += (have && (dj < d2s[s] || (dj == d2s[s] && ij < ids[s]))) ? 1 : 0;
+    }
+    double dkl = -1.0;
+#pragma unroll
+    for (int s = 0; s < SL; s++)
+        if (live && s * G + gl < (int)m && rank[s] < kk) {
+            S.nbr[rank[s] * 32 + slot] = ps[s];
+            if (rank[s] == kk - 1) dkl = d2s[s];
+        }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) dkl = fmax(dkl, __shfl_xor_sync(0xffffffffu, dkl, o));
+    dk = dkl;
+    if (live && !(dkl < g2)) st = PCP_FK_UNCERT;
+    __syncwarp();
+    return st;
+}
+
+// features of the parked queries: lane = slot
+template <class SM> __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_params& P, const SM& S, int lane)
+{
+    __syncwarp();
+    const uint32_t qpos = S.sqpos[lane];
+    if (qpos != 0xffffffffu) {
+        const size_t jq = (size_t)P.rec[qpos].idx;
+        const int N = P.kk;
+        if (P.knn_idx) {
+            for (int e = 0; e < P.k; e++)
+                P.knn_idx[jq * P.k + e] = e < N ? (int32_t)P.rec[S.nbr[e * 32 + lane]].idx : -1;
+        }
+        pcp_plane pl;
+        const bool fitted = N > 3; // calculate_feature.cpp:238
+        if (fitted) {
+            double XAve = 0.0, YAve = 0.0, ZAve = 0.0;
+            for (int e = 0; e < N; e++) {
+                const pcp_rec r = pcp_load_rec(P.rec, S.nbr[e * 32 + lane]);
+                XAve += r.x;
+                YAve += r.y;
+                ZAve += r.z;
+            }
+            XAve /= (double)N;
+            YAve /= (double)N;
+            ZAve /= (double)N;
+            double s00 = 0, s01 = 0, s02 = 0, s11 = 0, s12 = 0, s22 = 0;
+            for (int e = 0; e < N; e++) {
+                const pcp_rec r = pcp_load_rec(P.rec, S.nbr[e * 32 + lane]);
+                const double X = r.x - XAve, Y = r.y - YAve, Z = r.z - ZAve;
+                s00 += X * X;
+                s01 += X * Y;
+                s02 += X * Z;
+                s11 += Y * Y;
+                s12 += Y * Z;
+                s22 += Z * Z;
+            }
+            pcp_plane_from_scatter(s00, s01, s02, s11, s12, s22, XAve, YAve, ZAve, pl);
+        }
+        pcp_store_props(P.props, jq, fitted, pl);
+        pcp_store_extra(P.eig3, P.lps3, jq, fitted, pl);
+    }
+    S.sqpos[lane] = 0xffffffffu;
+    __syncwarp();
+}
+
+// ---- the dense kernel ------------------------------------------------------------------------------------
+// FP32 only, coordinates relative to the item's cell origin (error ~1e-7 h, see pcp_fd_e1).  Queries whose FP32
+// ordering is not provably the exact one (two candidates closer in d2 than the error bound, or a k-th distance
+// too close to the certified radius) are not settled here: they go to the far list with their upper bound.
+template <int CAP, int GS> struct pcp_fd_smem {
+    static constexpr int NSET = 32 / GS;
+    float4* cand;    // [PCP_FK_CAND]  x, y, z relative to the cell origin, w = sorted position
+    uint32_t* hist;  // [NSET][PCP_FK_NB]
+    float* ld2;      // [NSET][CAP]
+    uint32_t* lpos;  // [NSET][CAP]
+    uint32_t* nbr;   // [k][32]
+    uint32_t* sqpos; // [32]
+    static __host__ __device__ size_t bytes(int k)
+    {
+        return (size_t)PCP_FK_CAND * 16 + (size_t)NSET * PCP_FK_NB * 4 + (size_t)NSET * CAP * 8 + (size_t)32 * k * 4 + 128;
+    }
+    __device__ pcp_fd_smem(unsigned char* base, int k)
+    {
+        cand = reinterpret_cast<float4*>(base);
+        hist = reinterpret_cast<uint32_t*>(base + PCP_FK_CAND * 16);
+        ld2 = reinterpret_cast<float*>(hist + NSET * PCP_FK_NB);
+        lpos = reinterpret_cast<uint32_t*>(ld2 + NSET * CAP);
+        nbr = lpos + NSET * CAP;
+        sqpos = nbr + 32 * k;
+    }
+};
+
+#define PCP_FD_OK 0
+#define PCP_FD_BEYOND 1 // fewer than kk candidates inside `top`, or list overflow: no bound known
+#define PCP_FD_AMBIG 2  // kk nearest found among the staged candidates but order / certification not provable in FP32
+#define PCP_FD_IDLE 4
+
+// Every group of G lanes searches the staged block for its own query.  dku: upper bound of the k-th squared
+// distance (valid for OK and AMBIG).
+template <int G, int CAP>
+__device__ __forceinline__ int pcp_fd_search(const float4* __restrict__ cand, int T, const pcp_fd_smem<CAP, G>& S, int lane,
+                                             bool active, int slot, int kk, float qfx, float qfy, float qfz, float top,
+                                             float g2, float e1, float& dku)
+{
+    constexpr int SL = CAP / G;
+    constexpr int NBL = PCP_FK_NB / G;
+    static_assert(NBL == 8 || NBL == 4, "pcp_fd_search: 8 or 16 lanes per query");
+    const int gl = lane & (G - 1), gbase = lane & ~(G - 1), set = (G == 32) ? 0 : lane / G;
+    const unsigned gmask = (G == 32) ? 0xffffffffu : ((1u << G) - 1u);
+    uint32_t* hist = S.hist + set * PCP_FK_NB;
+    float* ld2 = S.ld2 + set * CAP;
+    uint32_t* lpos = S.lpos + set * CAP;
+    const int key0 = (__float_as_int(top) >> 21) - (PCP_FK_NB - 2);
+#pragma unroll
+    for (int i = 0; i < NBL; i++) hist[gl + i * G] = 0;
+    __syncwarp();
+    // ---- pass 1: histogram of FP32 squared distances ----
+    for (int f0 = 0; f0 < T; f0 += G) {
+        const int i = f0 + gl;
+        const float4 c = cand[i < T ? i : 0];
+        const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
+        const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+        if (i < T && active) atomicAdd(&hist[pcp_fk_bucket(d2, key0)], 1u);
+    }
+    __syncwarp();
+    // ---- scan: bucket b* of the kk-th candidate; hist[b] becomes the write cursor (exclusive prefix) ----
+    uint32_t hb[NBL];
+    {
+        const uint4 a = *reinterpret_cast<const uint4*>(hist + gl * NBL);
+        hb[0] = a.x, hb[1] = a.y, hb[2] = a.z, hb[3] = a.w;
+        if constexpr (NBL == 8) {
+            const uint4 b = *reinterpret_cast<const uint4*>(hist + gl * 8 + 4);
+            hb[4] = b.x, hb[5] = b.y, hb[6] = b.z, hb[7] = b.w;
+        }
+    }
+    uint32_t tot = 0;
+#pragma unroll
+    for (int i = 0; i < NBL; i++) tot += hb[i];
+    uint32_t incl = tot;
+#pragma unroll
+    for (int o = 1; o < G; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o, G);
+        if (gl >= o) incl += v;
+    }
+    int st = active ? PCP_FD_OK : PCP_FD_IDLE;
+    const unsigned bal = (__ballot_sync(0xffffffffu, incl >= (uint32_t)kk) >> gbase) & gmask;
+    if (!bal && active) st = PCP_FD_BEYOND;
+    const int L = bal ? __ffs(bal) - 1 : 0;
+    int myb = PCP_FK_NB;
+    uint32_t mym = 0;
+    {
+        uint32_t c = incl - tot;
+        uint32_t ex[NBL];
+#pragma unroll
+        for (int i = 0; i < NBL; i++) {
+            ex[i] = c;
+            c += hb[i];
+            if (myb == PCP_FK_NB && c >= (uint32_t)kk) myb = gl * NBL + i, mym = c;
+        }
+        uint4 a;
+        a.x = ex[0], a.y = ex[1], a.z = ex[2], a.w = ex[3];
+        *reinterpret_cast<uint4*>(hist + gl * NBL) = a;
+        if constexpr (NBL == 8) {
+            uint4 b;
+            b.x = ex[4], b.y = ex[5], b.z = ex[6], b.w = ex[7];
+            *reinterpret_cast<uint4*>(hist + gl * 8 + 4) = b;
+        }
+    }
+    const int bstar = __shfl_sync(0xffffffffu, myb, gbase + L);
+    const uint32_t m = __shfl_sync(0xffffffffu, mym, gbase + L); // candidates in buckets <= b*
+    if (st == PCP_FD_OK && (bstar >= PCP_FK_NB - 1 || m > (uint32_t)CAP)) st = PCP_FD_BEYOND;
+    const bool live = st == PCP_FD_OK;
+    __syncwarp();
+    // ---- pass 2: scatter the candidates of buckets <= b* into the list, bucket by bucket ----
+    for (int f0 = 0; f0 < T; f0 += G) {
+        const int i = f0 + gl;
+        const float4 c = cand[i < T ? i : 0];
+        const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
+        const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+        const int b = pcp_fk_bucket(d2, key0);
+        if (live && i < T && b <= bstar) {
+            const uint32_t at = atomicAdd(&hist[b], 1u);
+            ld2[at] = d2;
+            lpos[at] = __float_as_uint(c.w);
+        }
+    }
+    __syncwarp();
+    // ---- rank inside the bucket (hist[b] is now the END of bucket b) ----
+    const float edge = pcp_fk_edge(min(bstar, PCP_FK_NB - 2), key0);
+    const float delta = 4.0f * sqrtf(edge) * e1 + 4.0f * e1 * e1 + 1e-6f * edge;
+    const float amb2 = 2.0f * delta;
+    bool ambig = false;
+    float dkl = -1.0f;
+#pragma unroll
+    for (int s = 0; s < SL; s++) {
+        const int e = s * G + gl;
+        if (live && e < (int)m) {
+            const float d = ld2[e];
+            const int b = pcp_fk_bucket(d, key0);
+            const uint32_t lo = b ? hist[b - 1] : 0u, hi = hist[b];
+            uint32_t r = lo;
+            // bucket edges: an entry this close to one may belong to the other side
+            if (b > 0 && d - pcp_fk_edge(b - 1, key0) <= amb2 && lo > 0) ambig = true;
+            if (b < bstar && pcp_fk_edge(b, key0) - d <= amb2) ambig = true;
+            for (uint32_t j = lo; j < hi; j++) {
+                const float dj = ld2[j];
+                r += dj < d ? 1u : 0u;
+                if (j != (uint32_t)e && fabsf(dj - d) <= amb2) ambig = true;
+            }
+            if (r < (uint32_t)kk) S.nbr[r * 32 + slot] = lpos[e];
+            if (r == (uint32_t)kk - 1u) dkl = d;
+        }
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) dkl = fmaxf(dkl, __shfl_xor_sync(0xffffffffu, dkl, o));
+    ambig = ((__ballot_sync(0xffffffffu, ambig) >> gbase) & gmask) != 0u;
+    // the k-th against bucket b*+1 and against the certified radius
+    dku = ((dkl >= 0.0f && !ambig) ? dkl : edge) + delta;
+    if (live) {
+        if (ambig || dkl < 0.0f || edge - dkl <= amb2 || !(dkl + amb2 < g2)) st = PCP_FD_AMBIG;
+    }
+    __syncwarp();
+    return st;
+}
+
+// CAP: list capacity per query (>= k + room for the boundary bucket); GS: lanes per query.
+// Settles every query whose k nearest provably lie inside the 3x3x3 block of base cells around its cell; the
+// others are appended to the "far" list with the best known upper bound of their k-th squared distance
+// (+inf if none) for knn_far_kernel.
+template <int CAP, int GS>
+static __global__ void __launch_bounds__(32 * PCP_FK_WARPS) knn_fast_kernel(pcp_fknn_params P)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    constexpr int NSET = 32 / GS;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const pcp_fd_smem<CAP, GS> S(smem_raw + pcp_fd_smem<CAP, GS>::bytes(P.k) * warp, P.k);
+    const int set = lane / GS;
+    S.sqpos[lane] = 0xffffffffu;
+    __syncwarp();
+    int fill = 0;
+    const double h0 = P.g.h;
+    // |float - true| of a block-relative coordinate difference: operands up to 2h and 3h in magnitude, each
+    // rounded once (2^-24 relative), plus the rounding of the double subtraction p - origin
+    const float e1 = (float)(8.0 * 5.97e-8 * h0 + 2.0 * P.epsd) * 1.0001f;
+    const float top0 = (float)(2.25 * h0 * h0); // nothing farther than 1.5 h can be certified at level 0
+    while (true) {
+        uint32_t item = 0;
+        if (lane == 0) item = atomicAdd(P.work_counter, 1u);
+        item = __shfl_sync(0xffffffffu, item, 0);
+        if (item >= P.nitem) break;
+        const uint32_t cell = __ldg(P.item_cell + item);
+        const uint32_t first = __ldg(P.item_first + item);
+        const uint32_t cend = __ldg(P.cstart + cell + 1);
+        const int nq = (int)min(32u, cend - first);
+        // lane j holds query j of the item (halo points are candidates only)
+        const pcp_rec myq = pcp_load_rec(P.rec, first + (lane < nq ? lane : 0));
+        const unsigned want = __ballot_sync(0xffffffffu, lane < nq && myq.idx < P.query_limit);
+        if (!want) continue;
+        const int nwant = __popc(want);
+        if (fill + nwant > 32) {
+            pcp_fk_flush(P, S, lane);
+            fill = 0;
+        }
+        int cx, cy, cz;
+        pcp_demorton(__ldg(P.ckey + cell), cx, cy, cz);
+        const double ox = P.g.org[0] + (double)cx * h0, oy = P.g.org[1] + (double)cy * h0, oz = P.g.org[2] + (double)cz * h0;
+        const float myfx = (float)(myq.x - ox), myfy = (float)(myq.y - oy), myfz = (float)(myq.z - oz);
+
+        // ---- the 27 neighbour cells (hash) and the staged candidate block ----
+        uint32_t nb_start = 0, nb_count = 0;
+        if (lane < 27) {
+            int dx, dy, dz;
+            pcp_nb_offset(lane, dx, dy, dz);
+            const int nx = cx + dx, ny = cy + dy, nz = cz + dz;
+            if (nx >= 0 && ny >= 0 && nz >= 0 && nx < P.g.dims[0] && ny < P.g.dims[1] && nz < P.g.dims[2])
+                if (!pcp_hash_find(P.htab, P.hmask, pcp_morton(nx, ny, nz), nb_start, nb_count)) nb_count = 0;
+        }
+        uint32_t pre = nb_count;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, pre, o);
+            if (lane >= o) pre += v;
+        }
+        const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
+        pre -= nb_count;
+        const bool staged = total <= PCP_FK_CAND && total >= (uint32_t)P.kk;
+        PCP_FK_DBG(0, 1);
+        PCP_FK_DBG(1, staged ? 1 : 0);
+        PCP_FK_DBG(2, nwant);
+        PCP_FK_DBG(3, total);
+        PCP_FK_DBG(4, total > PCP_FK_CAND);
+        unsigned okmask = 0;
+        // lane j: upper bound of query j's k-th squared distance (+inf: none; -1: none, block too dense to stage)
+        float myU = (total > PCP_FK_CAND) ? -1.0f : __int_as_float(0x7f800000);
+        if (staged) {
+            for (int nb = 0; nb < 27; nb++) {
+                const uint32_t c = __shfl_sync(0xffffffffu, nb_count, nb);
+                if (c == 0) continue;
+                const uint32_t s = __shfl_sync(0xffffffffu, nb_start, nb);
+                const uint32_t p = __shfl_sync(0xffffffffu, pre, nb);
+                for (uint32_t t = lane; t < c; t += 32) {
+                    const pcp_rec r = pcp_load_rec(P.rec, s + t);
+                    S.cand[p + t] = make_float4((float)(r.x - ox), (float)(r.y - oy), (float)(r.z - oz),
+                                                __uint_as_float(s + t));
+                }
+            }
+            __syncwarp();
+            for (unsigned rest = want; rest;) {
+                // group g takes the g-th remaining query
+                int jj = -1;
+#pragma unroll
+                for (int g = 0; g < NSET; g++) {
+                    const int b = rest ? __ffs(rest) - 1 : -1;
+                    if (g == set) jj = b;
+                    rest &= rest - 1; // 0 stays 0
+                }
+                const bool active = jj >= 0;
+                const int sj = active ? jj : 0;
+                const float qfx = __shfl_sync(0xffffffffu, myfx, sj), qfy = __shfl_sync(0xffffffffu, myfy, sj),
+                            qfz = __shfl_sync(0xffffffffu, myfz, sj);
+                // certified radius: distance from the query to the faces of the 3x3x3 block (faces on the grid
+                // boundary do not count), in cell-relative FP32 with a safety margin
+                float dout = 3.0e38f;
+                const float hf = (float)h0;
+                if (cx > 0) dout = fminf(dout, qfx + hf);
+                if (cx + 1 < P.g.dims[0]) dout = fminf(dout, 2.0f * hf - qfx);
+                if (cy > 0) dout = fminf(dout, qfy + hf);
+                if (cy + 1 < P.g.dims[1]) dout = fminf(dout, 2.0f * hf - qfy);
+                if (cz > 0) dout = fminf(dout, qfz + hf);
+                if (cz + 1 < P.g.dims[2]) dout = fminf(dout, 2.0f * hf - qfz);
+                dout = fmaxf(dout - (4.0f * e1 + 1e-6f * hf), 0.0f);
+                const float g2 = dout * dout * 0.999999f;
+                const int slot = fill + __popc(want & ((1u << sj) - 1u));
+                float dku;
+                const int st = pcp_fd_search<GS, CAP>(S.cand, (int)total, S, lane, active, slot, P.kk, qfx, qfy, qfz,
+                                                      top0, g2, e1, dku);
+                // collect the group results as query bits
+#pragma unroll
+                for (int g = 0; g < NSET; g++) {
+                    const int jg = __shfl_sync(0xffffffffu, jj, g * GS);
+                    const int sg = __shfl_sync(0xffffffffu, st, g * GS);
+                    const float dg = __shfl_sync(0xffffffffu, dku, g * GS);
+                    if (jg >= 0) {
+                        if (sg == PCP_FD_OK) okmask |= 1u << jg;
+                        if (sg == PCP_FD_AMBIG && lane == jg) myU = dg * 1.000001f;
+                    }
+                }
+            }
+            PCP_FK_DBG(5, __popc(okmask));
+        }
+        // ---- park the finished queries; the rest go to the far list ----
+        if ((okmask >> lane) & 1u) S.sqpos[fill + __popc(want & ((1u << lane) - 1u))] = first + lane;
+        fill += nwant;
+        {
+            const unsigned fm = want & ~okmask;
+            if (fm) {
+                uint32_t basei = 0;
+                if (lane == 0) basei = atomicAdd(P.fail_count, (uint32_t)__popc(fm));
+                basei = __shfl_sync(0xffffffffu, basei, 0);
+                if ((fm >> lane) & 1u) {
+                    const uint32_t at = basei + __popc(fm & ((1u << lane) - 1u));
+                    P.fail_list[at] = first + lane;
+                    P.fail_u[at] = myU;
+                }
+            }
+        }
+    }
+    pcp_fk_flush(P, S, lane);
+}
