@@ -155,6 +155,17 @@ __global__ void __launch_bounds__(256) lhash_tails_kernel(const unsigned long lo
     }
 }
 
+__global__ void __launch_bounds__(256) cinfo_kernel(const unsigned long long* __restrict__ ckey,
+                                                    const uint32_t* __restrict__ cstart, uint32_t ncell,
+                                                    uint4* __restrict__ cinfo)
+{
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncell) return;
+    int x, y, z;
+    pcp_demorton(ckey[c], x, y, z);
+    cinfo[c] = make_uint4((unsigned)x, (unsigned)y, (unsigned)z, cstart[c]);
+}
+
 __global__ void __launch_bounds__(256) item_count_kernel(const uint32_t* __restrict__ cstart, uint32_t ncell,
                                                          uint32_t* __restrict__ nchunk)
 {
@@ -223,6 +234,7 @@ static void index_release(pcp_index* ix)
     pcp_arena_free(c, ix->cstart);
     pcp_arena_free(c, ix->htab);
     pcp_arena_free(c, ix->ltab);
+    pcp_arena_free(c, ix->cinfo);
     pcp_arena_free(c, ix->item_cell);
     pcp_arena_free(c, ix->item_first);
     delete ix;
@@ -421,6 +433,11 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
         ctx->launches++;
         IX_CUDA(cudaGetLastError());
         lhash_tails_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->ckey, ncell, ix->ltab, ix->lmask);
+        ctx->launches++;
+        IX_CUDA(cudaGetLastError());
+        IX_TRY(pcp_arena_alloc(ctx, (size_t)ncell * sizeof(uint4), &q));
+        ix->cinfo = (uint4*)q;
+        cinfo_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->ckey, ix->cstart, ncell, ix->cinfo);
         ctx->launches++;
         IX_CUDA(cudaGetLastError());
     }

@@ -46,6 +46,7 @@ struct pcp_index {
     // cells of levels 0..PCP_HLEVELS-1: key (level<<58 | Morton prefix) -> (first base cell, base cells)
     pcp_hslot* ltab = nullptr;
     uint32_t lmask = 0;
+    uint4* cinfo = nullptr; // per base cell: integer coordinates x, y, z and the first point
     // per-cell work items for the cell-cooperative kernels: item -> (cell, chunk of 32 queries)
     uint32_t* item_cell = nullptr;
     uint32_t* item_first = nullptr; // first sorted point of the chunk

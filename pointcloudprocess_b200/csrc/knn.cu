@@ -83,8 +83,8 @@ template <int CAP> int launch_far_t(pcp_ctx* ctx, const pcp_fknn_params& P, cons
 
 int launch_far(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)
 {
-    if (P.kk <= 24) return launch_far_t<32>(ctx, P, A);
-    if (P.kk <= 52) return launch_far_t<64>(ctx, P, A);
+    if (P.kk <= 40) return launch_far_t<64>(ctx, P, A);
+    if (P.kk <= 100) return launch_far_t<128>(ctx, P, A);
     return launch_far_t<160>(ctx, P, A);
 }
 
@@ -136,6 +136,7 @@ extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double*
             P.hmask = ix->hmask;
             P.ltab = ix->ltab;
             P.lmask = ix->lmask;
+            P.cinfo = ix->cinfo;
             P.ckey = ix->ckey;
             P.cstart = ix->cstart;
             P.ncell = ix->ncell;

@@ -15,15 +15,21 @@
 #pragma once
 #include "knn_fast.cuh"
 
-#define PCP_FAR_NSEL 256 // selected base cells per attempt
+#define PCP_FAR_NSEL 128   // selected base cells per attempt
+#define PCP_FAR_CCACHE 256 // cells whose (nearest-corner distance, first point, count) are kept between passes
 
 template <int CAP> struct pcp_far_smem : pcp_fk_smem<CAP, 32> {
     uint32_t* selpre;   // [NSEL]  exclusive prefix of the selected cells' point counts (0xffffffff beyond)
     uint32_t* selstart; // [NSEL]  first point of the selected cell
-    static __host__ __device__ size_t bytes(int k) { return pcp_fk_smem<CAP, 32>::bytes(k) + PCP_FAR_NSEL * 8; }
+    float4* ccache;     // [CCACHE] nearest-corner d2, first point, count of the block's cells (pass A -> B)
+    static __host__ __device__ size_t bytes(int k)
+    {
+        return pcp_fk_smem<CAP, 32>::bytes(k) + PCP_FAR_NSEL * 8 + PCP_FAR_CCACHE * 16;
+    }
     __device__ pcp_far_smem(unsigned char* base, int k) : pcp_fk_smem<CAP, 32>(base, k)
     {
-        selpre = reinterpret_cast<uint32_t*>(base + pcp_fk_smem<CAP, 32>::bytes(k));
+        ccache = reinterpret_cast<float4*>(base + pcp_fk_smem<CAP, 32>::bytes(k));
+        selpre = reinterpret_cast<uint32_t*>(base + pcp_fk_smem<CAP, 32>::bytes(k) + PCP_FAR_CCACHE * 16);
         selstart = selpre + PCP_FAR_NSEL;
     }
 };
@@ -42,23 +48,26 @@ struct pcp_far_src {
     {
         __syncwarp();
 #pragma unroll 1
-        for (int part = 0; part < PCP_FK_CAND / 128; part++) {
-            pcp_rec r[4];
-            uint32_t ps[4];
+        for (int part = 0; part < PCP_FK_CAND / 64 && c0 + part * 64 < T; part++) {
+            pcp_rec r[2];
+            uint32_t ps[2];
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const uint32_t fl = c0 + part * 128 + lane + 32 * i;
-                int c = 0;
+            for (int i = 0; i < 2; i++) {
+                const uint32_t fl = c0 + part * 64 + lane + 32 * i;
+                ps[i] = 0;
+                if (fl < T) {
+                    int c = 0;
 #pragma unroll
-                for (int step = PCP_FAR_NSEL / 2; step; step >>= 1)
-                    if (selpre[c + step] <= fl) c += step;
-                ps[i] = selstart[c] + (fl - selpre[c]);
-                if (fl < T) r[i] = pcp_load_rec(rec, ps[i]);
+                    for (int step = PCP_FAR_NSEL / 2; step; step >>= 1)
+                        if (selpre[c + step] <= fl) c += step;
+                    ps[i] = selstart[c] + (fl - selpre[c]);
+                    r[i] = pcp_load_rec(rec, ps[i]);
+                }
             }
 #pragma unroll
-            for (int i = 0; i < 4; i++)
-                if (c0 + part * 128 + lane + 32 * i < T)
-                    cand[part * 128 + lane + 32 * i] = make_float4((float)(r[i].x - qx), (float)(r[i].y - qy),
+            for (int i = 0; i < 2; i++)
+                if (c0 + part * 64 + lane + 32 * i < T)
+                    cand[part * 64 + lane + 32 * i] = make_float4((float)(r[i].x - qx), (float)(r[i].y - qy),
                                                                    (float)(r[i].z - qz), __uint_as_float(ps[i]));
         }
         __syncwarp();
@@ -100,24 +109,25 @@ __device__ __forceinline__ void pcp_level_cells(const unsigned long long* __rest
     cb = a;
 }
 
-// squared distance from q to the nearest / farthest point of base cell (ix,iy,iz), with outward margins
-__device__ __forceinline__ void pcp_cell_dist2(const pcp_grid& g, int ix, int iy, int iz, double qx, double qy, double qz,
-                                               float& mind2, float& maxd2)
+// Query position in cell units: integer cell + fraction in [0,1) (float), so that a cell's offset from the
+// query is an exact integer difference minus the fraction.
+struct pcp_qcell {
+    int ix, iy, iz;
+    float fx, fy, fz;
+    float h;
+};
+// squared distance from q to the nearest / farthest point of base cell (cx,cy,cz), with outward margins
+__device__ __forceinline__ void pcp_cell_dist2(const pcp_qcell& Q, int cx, int cy, int cz, float& mind2, float& maxd2)
 {
-    const double q[3] = {qx, qy, qz};
-    const int c[3] = {ix, iy, iz};
-    float mn = 0.f, mx = 0.f;
-#pragma unroll
-    for (int a = 0; a < 3; a++) {
-        const float lo = (float)(g.org[a] + (double)c[a] * g.h - q[a]);
-        const float hi = (float)(g.org[a] + (double)(c[a] + 1) * g.h - q[a]);
-        const float dn = fmaxf(fmaxf(lo, -hi), 0.f);
-        const float dx = fmaxf(fabsf(lo), fabsf(hi));
-        mn = __fmaf_rn(dn, dn, mn);
-        mx = __fmaf_rn(dx, dx, mx);
-    }
-    mind2 = mn * 0.9999f;
-    maxd2 = mx * 1.0001f;
+    const float lo0 = ((float)(cx - Q.ix) - Q.fx) * Q.h, lo1 = ((float)(cy - Q.iy) - Q.fy) * Q.h,
+                lo2 = ((float)(cz - Q.iz) - Q.fz) * Q.h;
+    const float hi0 = lo0 + Q.h, hi1 = lo1 + Q.h, hi2 = lo2 + Q.h;
+    const float n0 = fmaxf(fmaxf(lo0, -hi0), 0.f), n1 = fmaxf(fmaxf(lo1, -hi1), 0.f), n2 = fmaxf(fmaxf(lo2, -hi2), 0.f);
+    const float x0 = fmaxf(fabsf(lo0), fabsf(hi0)), x1 = fmaxf(fabsf(lo1), fabsf(hi1)), x2 = fmaxf(fabsf(lo2), fabsf(hi2));
+    const float slack = 4e-6f * Q.h; // float rounding of lo/hi and of the cell assignment
+    const float m0 = fmaxf(n0 - slack, 0.f), m1 = fmaxf(n1 - slack, 0.f), m2 = fmaxf(n2 - slack, 0.f);
+    mind2 = __fmaf_rn(m2, m2, __fmaf_rn(m1, m1, m0 * m0)) * 0.99999f;
+    maxd2 = __fmaf_rn(x2 + slack, x2 + slack, __fmaf_rn(x1 + slack, x1 + slack, (x0 + slack) * (x0 + slack))) * 1.00001f;
 }
 
 // first histogram bucket (64 buckets, 2 per lane) at which the cumulative count reaches kk, or 64
@@ -147,7 +157,7 @@ struct pcp_far_args {
 };
 
 template <int CAP>
-static __global__ void __launch_bounds__(32 * PCP_FK_WARPS) knn_far_kernel(pcp_fknn_params P, pcp_far_args A)
+static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pcp_fknn_params P, pcp_far_args A)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
@@ -172,6 +182,14 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS) knn_far_kernel(pcp_f
         const int bz = min(max(pcp_cell_coord(q.z, P.g.org[2], P.g.inv_h, 0), 0), P.g.dims[2] - 1);
         int level = (U == INF) ? 1 : 0;
         if (U < 0.f) U = INF;
+        pcp_qcell Q;
+        {
+            const double tx = (q.x - P.g.org[0]) * P.g.inv_h, ty = (q.y - P.g.org[1]) * P.g.inv_h,
+                         tz = (q.z - P.g.org[2]) * P.g.inv_h;
+            Q.ix = bx, Q.iy = by, Q.iz = bz;
+            Q.fx = (float)(tx - (double)bx), Q.fy = (float)(ty - (double)by), Q.fz = (float)(tz - (double)bz);
+            Q.h = (float)P.g.h;
+        }
         if (fill == 32) {
             pcp_fk_flush(P, S, lane);
             fill = 0;
@@ -230,11 +248,12 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS) knn_far_kernel(pcp_f
                         for (int step = 16; step; step >>= 1)
                             if (S.tab[t + step] <= fc) t += step;
                         const uint32_t ci = S.tab[32 + t] + (fc - S.tab[t]);
-                        int ix, iy, iz;
-                        pcp_demorton(__ldg(P.ckey + ci), ix, iy, iz);
+                        const uint4 ce = __ldg(P.cinfo + ci);
+                        const uint32_t cnt = __ldg(P.cstart + ci + 1) - ce.w;
                         float mn, mx;
-                        pcp_cell_dist2(P.g, ix, iy, iz, q.x, q.y, q.z, mn, mx);
-                        atomicAdd(&S.hist[pcp_fk_bucket(mx, key0)], __ldg(P.cstart + ci + 1) - __ldg(P.cstart + ci));
+                        pcp_cell_dist2(Q, (int)ce.x, (int)ce.y, (int)ce.z, mn, mx);
+                        atomicAdd(&S.hist[pcp_fk_bucket(mx, key0)], cnt);
+                        if (fc < PCP_FAR_CCACHE) S.ccache[fc] = make_float4(mn, __uint_as_float(ce.w), __uint_as_float(cnt), 0.f);
                     }
                 }
                 __syncwarp();
@@ -247,22 +266,28 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS) knn_far_kernel(pcp_f
             __syncwarp();
             for (int i = lane; i < PCP_FAR_NSEL; i += 32) S.selpre[i] = 0xffffffffu;
             __syncwarp();
+            const bool cached = (U == INF); // pass A ran for this block and filled the cache
             for (uint32_t c0 = 0; c0 < NC; c0 += 32) {
                 const uint32_t fc = c0 + lane;
                 bool sel = false;
                 uint32_t cs = 0, cc = 0;
                 if (fc < NC) {
-                    int t = 0;
+                    if (cached && fc < PCP_FAR_CCACHE) {
+                        const float4 e = S.ccache[fc];
+                        sel = e.x <= Ueff;
+                        cs = __float_as_uint(e.y), cc = __float_as_uint(e.z);
+                    } else {
+                        int t = 0;
 #pragma unroll
-                    for (int step = 16; step; step >>= 1)
-                        if (S.tab[t + step] <= fc) t += step;
-                    const uint32_t ci = S.tab[32 + t] + (fc - S.tab[t]);
-                    int ix, iy, iz;
-                    pcp_demorton(__ldg(P.ckey + ci), ix, iy, iz);
-                    float mn, mx;
-                    pcp_cell_dist2(P.g, ix, iy, iz, q.x, q.y, q.z, mn, mx);
-                    sel = mn <= Ueff;
-                    if (sel) cs = __ldg(P.cstart + ci), cc = __ldg(P.cstart + ci + 1) - cs;
+                        for (int step = 16; step; step >>= 1)
+                            if (S.tab[t + step] <= fc) t += step;
+                        const uint32_t ci = S.tab[32 + t] + (fc - S.tab[t]);
+                        const uint4 ce = __ldg(P.cinfo + ci);
+                        float mn, mx;
+                        pcp_cell_dist2(Q, (int)ce.x, (int)ce.y, (int)ce.z, mn, mx);
+                        sel = mn <= Ueff;
+                        if (sel) cs = ce.w, cc = __ldg(P.cstart + ci + 1) - cs;
+                    }
                 }
                 const unsigned mask = __ballot_sync(0xffffffffu, sel);
                 const uint32_t at = nsel + __popc(mask & ((1u << lane) - 1u));

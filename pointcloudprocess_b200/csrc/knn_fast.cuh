@@ -25,6 +25,9 @@
 #define PCP_FK_NB 64      // histogram buckets (last one = beyond range)
 #define PCP_FK_CAND 256   // staged candidates per item
 #define PCP_FK_WARPS 4
+#ifndef PCP_FK_MINB
+#define PCP_FK_MINB 6
+#endif
 
 struct pcp_fknn_params {
     const pcp_rec* rec;
@@ -33,6 +36,7 @@ struct pcp_fknn_params {
     uint32_t hmask;
     const pcp_hslot* ltab; // level table (index.cuh)
     uint32_t lmask;
+    const uint4* cinfo;    // per base cell: x, y, z, first point
     const unsigned long long* ckey;
     const uint32_t* cstart;
     uint32_t ncell;
@@ -497,7 +501,7 @@ __device__ __forceinline__ int pcp_fd_search(const float4* __restrict__ cand, in
 // others are appended to the "far" list with the best known upper bound of their k-th squared distance
 // (+inf if none) for knn_far_kernel.
 template <int CAP, int GS>
-static __global__ void __launch_bounds__(32 * PCP_FK_WARPS) knn_fast_kernel(pcp_fknn_params P)
+static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fast_kernel(pcp_fknn_params P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int NSET = 32 / GS;
