@@ -225,8 +225,8 @@ def run_gpu(args):
     ctx.set_stream(stream.cuda_stream)
 
     n_shard = args.points
-    job = sharded.ShardedPipeline(ctx, rank, world, n_shard, seed=5, leaf=LEAF, k=K,
-                                  comm=(dist if world > 1 else None), torch=torch)
+    comm = sharded.DistComm(dist, torch, rank, world, torch.device("cuda", local)) if world > 1 else None
+    job = sharded.ShardedPipeline(ctx, rank, world, n_shard, seed=5, leaf=LEAF, k=K, comm=comm, torch=torch)
     job.generate()  # this rank's spatial shard, resident in HBM (untimed)
 
     def barrier():

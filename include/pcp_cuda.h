@@ -134,6 +134,12 @@ PCP_API int pcp_radius_fill(const pcp_index* index, const void* q, size_t nq, si
  * (l1-l2)/l1, (l2-l3)/l1, l3/l1), knn_idx (n*k) are optional (NULL). */
 PCP_API int pcp_features_knn(const pcp_index* index, int k, void* props, double* eig3, float* lps3,
                              int32_t* knn_idx);
+/* Same, for a shard of a larger cloud: only the points with original index < query_limit are
+ * queries (the rest -- halo points received from neighbouring shards -- are candidates only; query_limit < 0 =
+ * all), and kth_d2 (n floats, optional) receives an upper bound of every query's k-th squared distance, which
+ * tells the caller whether the neighbourhood can reach beyond the halo. */
+PCP_API int pcp_features_knn_ex(const pcp_index* index, int k, int64_t query_limit, void* props, double* eig3,
+                                float* lps3, int32_t* knn_idx, float* kth_d2);
 /* Same with radius neighbourhoods (strict d2 < r*r, max_nn as above); counts (n) optional. */
 PCP_API int pcp_features_radius(const pcp_index* index, double r, uint32_t max_nn, void* props, double* eig3,
                                 float* lps3, int32_t* counts);
@@ -157,6 +163,32 @@ PCP_API int pcp_voxel_grid(pcp_ctx* ctx, const void* pts, size_t n, size_t strid
  * (point_cloud_helper.h:192-230, reproduced bit-exactly), voxel grid with a float leaf, un-centre.
  * In place: pts_inout holds *n_inout records on entry and the filtered cloud on return. */
 PCP_API int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf);
+
+/* ---- sharding (one shard per GPU; the cut follows cloud_grid.cpp's tiles) --------------------
+ * remove_duplicate of a SHARD of a larger cloud: centred on the given centre (the whole cloud's serial-order
+ * centroid) and voxelised in the whole cloud's grid box (min_b / div_b of the centred whole cloud,
+ * voxel_grid.h:835-847), so that shards cut along voxel columns reproduce the single-device cells exactly. */
+PCP_API int pcp_remove_duplicate_centred(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf,
+                                         const double centre[3], const int32_t min_b[3], const int32_t div_b[3]);
+/* compute3DCentroid's serial-order sums continued over a chunk: sum3 (in/out) holds the running x,y,z sums of
+ * the points that precede the chunk, count (in/out, optional) the running number of finite points. */
+PCP_API int pcp_serial_sum(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double sum3[3], uint64_t* count);
+/* Histogram of voxel columns along `axis`: column = (int)((p + (-centre)) * (1/leaf) - min_b) as at
+ * voxel_grid.h:936; bin = (column - col0) / cols_per_bin clamped to [0, nbins); counts are ADDED to hist_inout. */
+PCP_API int pcp_column_histogram(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, int axis, float leaf,
+                                 double centre, int32_t min_b, int32_t col0, int32_t cols_per_bin, int32_t nbins,
+                                 uint64_t* hist_inout);
+/* Stable selection (input order kept) of the finite points with lo <= coordinate < hi / col_lo <= column < col_hi. */
+PCP_API int pcp_select_range(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, int axis, double lo, double hi,
+                             void* out_pts, size_t* m);
+PCP_API int pcp_select_columns(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, int axis, float leaf,
+                               double centre, int32_t min_b, int32_t col_lo, int32_t col_hi, void* out_pts, size_t* m);
+/* Exact features of queries whose neighbourhood spans shards: list l (of nlists <= 4) holds, for each of the nq
+ * queries, k candidate neighbours sorted by squared distance (xyz_lists [nlists][nq][k][3], d2_lists
+ * [nlists][nq][k], +inf padded).  The k nearest distinct candidates are merged and fitted
+ * (calculate_feature.cpp:119-206); results go to props[point_id[q]] (device arrays). */
+PCP_API int pcp_features_merge(pcp_ctx* ctx, size_t nq, int k, int nlists, const double* xyz_lists,
+                               const double* d2_lists, const int32_t* point_id, void* props, double* eig3, float* lps3);
 
 /* compute3DCentroid (point_cloud_helper.h:192-230) and getMinMax3D (point_cloud_helper.h:59-90). */
 PCP_API int pcp_centroid(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double c[3], uint64_t* count);

@@ -13,7 +13,8 @@ SYMBOLS = [
     "pcp_dev_alloc", "pcp_dev_free", "pcp_host_alloc_pinned", "pcp_host_free_pinned", "pcp_memcpy", "pcp_memcpy_async",
     "pcp_index_build", "pcp_index_free", "pcp_index_size", "pcp_index_cell_size", "pcp_knn", "pcp_radius_count",
     "pcp_radius_fill", "pcp_features_knn", "pcp_features_radius", "pcp_plane_fit", "pcp_voxel_grid",
-    "pcp_remove_duplicate", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
+    "pcp_remove_duplicate", "pcp_features_knn_ex", "pcp_remove_duplicate_centred", "pcp_serial_sum",
+    "pcp_column_histogram", "pcp_select_range", "pcp_select_columns", "pcp_features_merge", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
 ]
 
 
@@ -72,6 +73,13 @@ def load():
         "pcp_plane_fit": (i32, [vp, vp, sz, vp, sz, vp]),
         "pcp_voxel_grid": (i32, [vp, vp, sz, sz, vp, i32, vp, C.POINTER(sz), vp, vp, vp, vp]),
         "pcp_remove_duplicate": (i32, [vp, vp, C.POINTER(sz), sz, C.c_float]),
+        "pcp_features_knn_ex": (i32, [vp, i32, i64, vp, vp, vp, vp, vp]),
+        "pcp_remove_duplicate_centred": (i32, [vp, vp, C.POINTER(sz), sz, C.c_float, vp, vp, vp]),
+        "pcp_serial_sum": (i32, [vp, vp, sz, sz, vp, C.POINTER(u64)]),
+        "pcp_column_histogram": (i32, [vp, vp, sz, sz, i32, C.c_float, dbl, i32, i32, i32, i32, vp]),
+        "pcp_select_range": (i32, [vp, vp, sz, sz, i32, dbl, dbl, vp, C.POINTER(sz)]),
+        "pcp_select_columns": (i32, [vp, vp, sz, sz, i32, C.c_float, dbl, i32, i32, i32, vp, C.POINTER(sz)]),
+        "pcp_features_merge": (i32, [vp, sz, i32, i32, vp, vp, vp, vp, vp, vp]),
         "pcp_centroid": (i32, [vp, vp, sz, sz, vp, C.POINTER(u64)]),
         "pcp_minmax": (i32, [vp, vp, sz, sz, vp, vp]),
         "pcp_synth_cloud": (i32, [vp, i32, u64, u64, u64, u64, i32, vp]),

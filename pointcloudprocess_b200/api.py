@@ -219,6 +219,49 @@ class Context:
         self._check(self.L.pcp_remove_duplicate(self.h, a.ctypes.data, C.byref(nn), a.dtype.itemsize, C.c_float(leaf)))
         return a[:nn.value].copy()
 
+    # ---- sharding primitives ----
+    def remove_duplicate_centred(self, cloud, leaf, centre, min_b, div_b):
+        """In place on a (ptr, n, stride) device tuple; returns m."""
+        p, n, s, _ = _pts(cloud)
+        nn = C.c_size_t(n)
+        c = np.ascontiguousarray(centre, dtype=np.float64)
+        mb = np.ascontiguousarray(min_b, dtype=np.int32)
+        db = np.ascontiguousarray(div_b, dtype=np.int32)
+        self._check(self.L.pcp_remove_duplicate_centred(self.h, p, C.byref(nn), s, C.c_float(leaf), c.ctypes.data,
+                                                        mb.ctypes.data, db.ctypes.data))
+        return nn.value
+
+    def serial_sum(self, cloud, sum3, count):
+        """Continues compute3DCentroid's serial sums over a chunk; returns (sum3, count)."""
+        p, n, s, keep = _pts(cloud)
+        acc = np.array(sum3, dtype=np.float64)
+        cnt = C.c_uint64(int(count))
+        self._check(self.L.pcp_serial_sum(self.h, p, n, s, acc.ctypes.data, C.byref(cnt)))
+        return acc, cnt.value
+
+    def column_histogram(self, cloud, axis, leaf, centre, min_b, col0, cols_per_bin, hist):
+        p, n, s, keep = _pts(cloud)
+        assert hist.dtype == np.uint64 and hist.flags.c_contiguous
+        self._check(self.L.pcp_column_histogram(self.h, p, n, s, axis, C.c_float(leaf), float(centre), int(min_b),
+                                                int(col0), int(cols_per_bin), hist.shape[0], hist.ctypes.data))
+
+    def select_range(self, cloud, axis, lo, hi, out):
+        p, n, s, keep = _pts(cloud)
+        m = C.c_size_t(0)
+        self._check(self.L.pcp_select_range(self.h, p, n, s, axis, float(lo), float(hi), _ptr(out), C.byref(m)))
+        return m.value
+
+    def select_columns(self, cloud, axis, leaf, centre, min_b, col_lo, col_hi, out):
+        p, n, s, keep = _pts(cloud)
+        m = C.c_size_t(0)
+        self._check(self.L.pcp_select_columns(self.h, p, n, s, axis, C.c_float(leaf), float(centre), int(min_b),
+                                              int(col_lo), int(col_hi), _ptr(out), C.byref(m)))
+        return m.value
+
+    def features_merge(self, nq, k, nlists, xyz_lists, d2_lists, point_id, props, eig=None, lps=None):
+        self._check(self.L.pcp_features_merge(self.h, int(nq), int(k), int(nlists), _ptr(xyz_lists), _ptr(d2_lists),
+                                              _ptr(point_id), _ptr(props), _ptr(eig), _ptr(lps)))
+
     def centroid(self, cloud):
         p, n, s, keep = _pts(cloud)
         c = np.zeros(3)
@@ -286,8 +329,13 @@ class Index:
                                                    idx.ctypes.data, d2.ctypes.data))
         return off, idx, d2
 
+    def knn_device(self, q_ptr, nq, qstride, k, idx_ptr, d2_ptr):
+        """pcp_knn with caller-owned (device) buffers."""
+        self.ctx._check(self.ctx.L.pcp_knn(self.h, _ptr(q_ptr), int(nq), int(qstride), int(k), _ptr(idx_ptr),
+                                           _ptr(d2_ptr), None))
+
     def features_knn(self, k, props=None, eig=None, lps=None, knn_idx=None, want_eig=True, want_lps=True,
-                     want_idx=False):
+                     want_idx=False, query_limit=-1, kth_d2=None):
         """Host outputs are allocated unless device pointers are passed in."""
         n = self.n_orig
         ret = {}
@@ -299,7 +347,8 @@ class Index:
             lps = ret["lps"] = np.zeros((n, 3), dtype=np.float32)
         if knn_idx is None and want_idx:
             knn_idx = ret["knn_idx"] = np.empty((n, k), dtype=np.int32)
-        self.ctx._check(self.ctx.L.pcp_features_knn(self.h, k, _ptr(props), _ptr(eig), _ptr(lps), _ptr(knn_idx)))
+        self.ctx._check(self.ctx.L.pcp_features_knn_ex(self.h, k, int(query_limit), _ptr(props), _ptr(eig), _ptr(lps),
+                                                       _ptr(knn_idx), _ptr(kth_d2)))
         return ret
 
     def features_radius(self, r, max_nn=0, props=None, eig=None, lps=None, counts=None, want_extra=True):

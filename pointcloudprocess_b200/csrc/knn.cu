@@ -100,6 +100,12 @@ int run_wknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint32_t expected)
 
 extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double* eig3, float* lps3, int32_t* knn_idx)
 {
+    return pcp_features_knn_ex(ix, k, -1, props, eig3, lps3, knn_idx, nullptr);
+}
+
+extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_limit, void* props, double* eig3, float* lps3,
+                                   int32_t* knn_idx, float* kth_d2)
+{
     if (!ix || !props || k < 1) return pcp_fail(ix ? ix->ctx : nullptr, PCP_ERR_INVALID, "pcp_features_knn: bad argument");
     pcp_ctx* ctx = ix->ctx;
     if (k > 128) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_features_knn: k > 128 is not supported");
@@ -112,6 +118,10 @@ extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double*
     PCP_TRY(o_eig.open(ctx, eig3, n0 * 24));
     PCP_TRY(o_lps.open(ctx, lps3, n0 * 12));
     PCP_TRY(o_idx.open(ctx, knn_idx, n0 * (size_t)k * 4));
+    OutStage o_kth;
+    PCP_TRY(o_kth.open(ctx, kth_d2, n0 * 4));
+    if (o_kth.dptr) PCP_CUDA_TRY(ctx, cudaMemsetAsync(o_kth.dptr, 0, n0 * 4, ctx->stream));
+    const long long qlimit = query_limit < 0 ? LLONG_MAX : (long long)query_limit;
     const int kk = (int)(nv < (size_t)k ? nv : (size_t)k);
     if (nv < n0 || kk == 0) {
         props_fallback_kernel<<<pcp_blocks_for(n0, 256), 256, 0, ctx->stream>>>(
@@ -148,7 +158,8 @@ extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double*
             P.kk = kk;
             P.eps0 = ix->eps0;
             P.epsd = ix->epsd;
-            P.query_limit = LLONG_MAX;
+            P.query_limit = qlimit;
+            P.kth_d2 = (float*)o_kth.dptr;
             P.props = o_props.dptr;
             P.eig3 = (double*)o_eig.dptr;
             P.lps3 = (float*)o_lps.dptr;
@@ -238,7 +249,7 @@ extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double*
                 StageTimer t(ctx, "knn.fallback_features");
                 features_from_list_kernel<<<pcp_blocks_for(nfail, 128), 128, 0, ctx->stream>>>(
                     ix->rec, W.qlist, counters.p, nbr.p, k, kk, o_props.dptr, (double*)o_eig.dptr,
-                    (float*)o_lps.dptr, (int32_t*)o_idx.dptr);
+                    (float*)o_lps.dptr, (int32_t*)o_idx.dptr, (float*)o_kth.dptr);
                 PCP_LAUNCH_CHECK(ctx);
             }
         }
@@ -247,6 +258,7 @@ extern "C" int pcp_features_knn(const pcp_index* ix, int k, void* props, double*
     PCP_TRY(o_eig.commit());
     PCP_TRY(o_lps.commit());
     PCP_TRY(o_idx.commit());
+    PCP_TRY(o_kth.commit());
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return PCP_OK;
 }

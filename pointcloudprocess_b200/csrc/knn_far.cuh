@@ -319,11 +319,13 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
             double dk;
             const float top = Ueff * 1.001f;
             st = pcp_fk_search<32, CAP>(src, S, P.rec, lane, true, slot, P.kk, 0.f, 0.f, 0.f, q.x, q.y, q.z, top, g2, e1, dk);
+            if (st == PCP_FK_OK) U = __double2float_ru(dk);
             if (st == PCP_FK_OK || st == PCP_FK_OVERFLOW) break;
             if (st == PCP_FK_UNCERT) U = __double2float_ru(dk) * 1.000001f; // exact k-th of the scanned set: a true bound
         }
         if (st == PCP_FK_OK) {
             S.sqpos[slot] = qpos;
+            S.skd[slot] = U; // set below from the exact k-th distance of the successful attempt
             fill++;
         } else {
             if (lane == 0) A.fail_list[atomicAdd(A.fail_count, 1u)] = qpos;

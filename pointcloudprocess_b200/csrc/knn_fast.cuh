@@ -52,6 +52,7 @@ struct pcp_fknn_params {
     double* eig3;
     float* lps3;
     int32_t* knn_idx;
+    float* kth_d2;           // optional: upper bound of every query's k-th squared distance (shard boundary test)
     uint32_t* fail_list;     // far list: sorted positions ...
     float* fail_u;           // ... and the known upper bound of the k-th squared distance (+inf: none)
     uint32_t* fail_count;
@@ -76,9 +77,10 @@ template <int CAP, int GS> struct pcp_fk_smem {
     uint32_t* nbr;   // [k][32]   neighbour positions of the parked queries
     uint32_t* sqpos; // [32]      sorted position of the parked query (0xffffffff = empty slot)
     uint32_t* tab;   // [64]      flat-index table of the 27 cell ranges: prefix[32], start[32]
+    float* skd;      // [32]      k-th squared distance (upper bound) of the parked query
     static __host__ __device__ size_t bytes(int k)
     {
-        return (size_t)PCP_FK_CAND * 16 + (size_t)NSET * CAP * 16 + (size_t)NSET * PCP_FK_NB * 4 + (size_t)32 * k * 4 + 128 + 256;
+        return (size_t)PCP_FK_CAND * 16 + (size_t)NSET * CAP * 16 + (size_t)NSET * PCP_FK_NB * 4 + (size_t)32 * k * 4 + 128 + 256 + 128;
     }
     __device__ pcp_fk_smem(unsigned char* base, int k)
     {
@@ -90,6 +92,7 @@ template <int CAP, int GS> struct pcp_fk_smem {
         nbr = reinterpret_cast<uint32_t*>(lidx + NSET * CAP);
         sqpos = nbr + 32 * k;
         tab = sqpos + 32;
+        skd = reinterpret_cast<float*>(tab + 64);
     }
 };
 
@@ -331,6 +334,7 @@ template <class SM> __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_
         }
         pcp_store_props(P.props, jq, fitted, pl);
         pcp_store_extra(P.eig3, P.lps3, jq, fitted, pl);
+        if (P.kth_d2) P.kth_d2[jq] = S.skd[lane];
     }
     S.sqpos[lane] = 0xffffffffu;
     __syncwarp();
@@ -348,9 +352,10 @@ template <int CAP, int GS> struct pcp_fd_smem {
     uint32_t* lpos;  // [NSET][CAP]
     uint32_t* nbr;   // [k][32]
     uint32_t* sqpos; // [32]
+    float* skd;      // [32]
     static __host__ __device__ size_t bytes(int k)
     {
-        return (size_t)PCP_FK_CAND * 16 + (size_t)NSET * PCP_FK_NB * 4 + (size_t)NSET * CAP * 8 + (size_t)32 * k * 4 + 128;
+        return (size_t)PCP_FK_CAND * 16 + (size_t)NSET * PCP_FK_NB * 4 + (size_t)NSET * CAP * 8 + (size_t)32 * k * 4 + 256;
     }
     __device__ pcp_fd_smem(unsigned char* base, int k)
     {
@@ -360,6 +365,7 @@ template <int CAP, int GS> struct pcp_fd_smem {
         lpos = reinterpret_cast<uint32_t*>(ld2 + NSET * CAP);
         nbr = lpos + NSET * CAP;
         sqpos = nbr + 32 * k;
+        skd = reinterpret_cast<float*>(sqpos + 32);
     }
 };
 
@@ -616,14 +622,18 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
                     const float dg = __shfl_sync(0xffffffffu, dku, g * GS);
                     if (jg >= 0) {
                         if (sg == PCP_FD_OK) okmask |= 1u << jg;
-                        if (sg == PCP_FD_AMBIG && lane == jg) myU = dg * 1.000001f;
+                        if ((sg == PCP_FD_AMBIG || sg == PCP_FD_OK) && lane == jg) myU = dg * 1.000001f;
                     }
                 }
             }
             PCP_FK_DBG(5, __popc(okmask));
         }
         // ---- park the finished queries; the rest go to the far list ----
-        if ((okmask >> lane) & 1u) S.sqpos[fill + __popc(want & ((1u << lane) - 1u))] = first + lane;
+        if ((okmask >> lane) & 1u) {
+            const int sl = fill + __popc(want & ((1u << lane) - 1u));
+            S.sqpos[sl] = first + lane;
+            S.skd[sl] = myU;
+        }
         fill += nwant;
         {
             const unsigned fm = want & ~okmask;

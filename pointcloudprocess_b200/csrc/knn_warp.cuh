@@ -169,7 +169,7 @@ static __global__ void __launch_bounds__(128) features_from_list_kernel(const pc
                                                                  const uint32_t* __restrict__ qcount_dev,
                                                                  const uint32_t* __restrict__ nbr_pos, int k, int kk,
                                                                  void* props, double* eig3, float* lps3,
-                                                                 int32_t* knn_idx)
+                                                                 int32_t* knn_idx, float* kth_d2)
 {
     const uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
     if (qi >= *qcount_dev) return;
@@ -181,6 +181,10 @@ static __global__ void __launch_bounds__(128) features_from_list_kernel(const pc
         if (row[e] != 0xffffffffu) N++;
     if (knn_idx)
         for (int e = 0; e < k; e++) knn_idx[jq * k + e] = e < N ? (int32_t)rec[row[e]].idx : -1;
+    if (kth_d2 && N > 0) {
+        const pcp_rec q = pcp_load_rec(rec, qpos), r = pcp_load_rec(rec, row[N - 1]);
+        kth_d2[jq] = __double2float_ru(pcp_dist2(q.x, q.y, q.z, r.x, r.y, r.z));
+    }
     pcp_plane pl;
     const bool fitted = N > 3;
     if (fitted) {

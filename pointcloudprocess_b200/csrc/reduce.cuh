@@ -14,4 +14,4 @@ int pcp_bbox_host(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, pcp_b
 
 // Serial-order sum of x,y,z over the finite points (compute3DCentroid, point_cloud_helper.h:192-230),
 // bit-identical to the left-to-right double accumulation.  d_sum3: 3 doubles on the device.
-int pcp_serial_sum_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, double* d_sum3);
+int pcp_serial_sum_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, double* d_sum3, int carry = 0);

@@ -182,6 +182,7 @@ __device__ __forceinline__ int ss_pad(int i) { return i + (i >> 3); }
 
 __global__ void __launch_bounds__(128) ss_leaf_xfer_kernel(const char* __restrict__ pts, size_t n, size_t stride,
                                                            size_t nleaf, const double* __restrict__ lpre /*[3][nleaf]*/,
+                                                           const double* __restrict__ carry3 /*or NULL*/,
                                                            Xfer* __restrict__ out /*[3][nleaf]*/)
 {
     __shared__ double sm[4][3][SS_LEAF + SS_LEAF / 8];
@@ -201,7 +202,7 @@ __global__ void __launch_bounds__(128) ss_leaf_xfer_kernel(const char* __restric
         __syncwarp();
 #pragma unroll
         for (int axis = 0; axis < 3; axis++) {
-            const double pre = lpre[(size_t)axis * nleaf + leaf];
+            const double pre = lpre[(size_t)axis * nleaf + leaf] + (carry3 ? carry3[axis] : 0.0);
             const int e = exponent_of(pre);
             const bool usable = (pre != 0.0) && e > -900 && e < 1000;
             const double scale = usable ? pow2d(52 - e) : 1.0;
@@ -291,14 +292,15 @@ __global__ void __launch_bounds__(96) ss_walk_kernel(const char* __restrict__ pt
                                                      const Xfer* __restrict__ leafx, size_t nleaf,
                                                      const Xfer* __restrict__ groupx, size_t ngroup,
                                                      const Xfer* __restrict__ superx, size_t nsuper,
-                                                     double* __restrict__ out3, unsigned long long* __restrict__ stats)
+                                                     double* __restrict__ out3, int carry,
+                                                     unsigned long long* __restrict__ stats)
 {
     __shared__ Xfer bufS[3][32], bufG[3][32], bufL[3][32];
     const int axis = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const Xfer* lx = leafx + (size_t)axis * nleaf;
     const Xfer* gx = groupx + (size_t)axis * ngroup;
     const Xfer* sx = superx + (size_t)axis * nsuper;
-    double s = 0.0;
+    double s = carry ? out3[axis] : 0.0;
     unsigned long long replayed = 0;
     for (size_t s0 = 0; s0 < nsuper; s0 += 32) {
         ss_stage(sx, s0, nsuper, lane, bufS[axis]);
@@ -326,21 +328,22 @@ __global__ void __launch_bounds__(96) ss_walk_kernel(const char* __restrict__ pt
 
 // small clouds: one warp per axis, element by element
 __global__ void __launch_bounds__(96) ss_small_kernel(const char* __restrict__ pts, size_t n, size_t stride,
-                                                      double* __restrict__ out3)
+                                                      double* __restrict__ out3, int carry)
 {
     const int axis = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    double s = 0.0;
+    double s = carry ? out3[axis] : 0.0;
     ss_replay(pts, n, stride, 0, n, axis, lane, s);
     if (lane == 0) out3[axis] = s;
 }
 
 } // namespace
 
-int pcp_serial_sum_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, double* d_sum3)
+// carry != 0: d_sum3 holds the running sums of the points that precede this chunk (chunked / sharded clouds)
+int pcp_serial_sum_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, double* d_sum3, int carry)
 {
     const char* p = static_cast<const char*>(dpts);
     if (n < 16384) {
-        ss_small_kernel<<<1, 96, 0, ctx->stream>>>(p, n, stride, d_sum3);
+        ss_small_kernel<<<1, 96, 0, ctx->stream>>>(p, n, stride, d_sum3, carry);
         PCP_LAUNCH_CHECK(ctx);
         return PCP_OK;
     }
@@ -359,7 +362,7 @@ int pcp_serial_sum_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t strid
     ss_leaf_sum_kernel<<<blocks, 128, 0, ctx->stream>>>(p, n, stride, nleaf, lsum.p);
     PCP_LAUNCH_CHECK(ctx);
     for (int a = 0; a < 3; a++) PCP_TRY(pcp_exclusive_scan_f64(ctx, lsum.p + a * nleaf, lpre.p + a * nleaf, nleaf));
-    ss_leaf_xfer_kernel<<<blocks, 128, 0, ctx->stream>>>(p, n, stride, nleaf, lpre.p, leafx.p);
+    ss_leaf_xfer_kernel<<<blocks, 128, 0, ctx->stream>>>(p, n, stride, nleaf, lpre.p, carry ? d_sum3 : nullptr, leafx.p);
     PCP_LAUNCH_CHECK(ctx);
     const int gb = (int)((3 * ngroup + 3) / 4 < (size_t)wide ? (3 * ngroup + 3) / 4 : (size_t)wide);
     ss_group_kernel<<<gb, 128, 0, ctx->stream>>>(leafx.p, nleaf, ngroup, groupx.p);
@@ -368,7 +371,7 @@ int pcp_serial_sum_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t strid
     ss_group_kernel<<<sb, 128, 0, ctx->stream>>>(groupx.p, ngroup, nsuper, superx.p);
     PCP_LAUNCH_CHECK(ctx);
     ss_walk_kernel<<<1, 96, 0, ctx->stream>>>(p, n, stride, leafx.p, nleaf, groupx.p, ngroup, superx.p, nsuper, d_sum3,
-                                            nullptr);
+                                            carry, nullptr);
     PCP_LAUNCH_CHECK(ctx);
     return PCP_OK;
 }

@@ -163,7 +163,8 @@ int ceil_log2_u128(double cells)
 // m_host receives M (synchronises).  d_point_cell / d_cell_count may be NULL.
 int pcp_voxel_grid_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, const double leaf[3],
                           int downsample_all, void* dout, size_t out_stride, size_t* m_host, int32_t min_b[3],
-                          int32_t div_b[3], int32_t* d_point_cell, int32_t* d_cell_count)
+                          int32_t div_b[3], int32_t* d_point_cell, int32_t* d_cell_count,
+                          const int32_t* force_min_b = nullptr, const int32_t* force_div_b = nullptr)
 {
     *m_host = 0;
     if (n == 0) return PCP_OK;
@@ -186,6 +187,12 @@ int pcp_voxel_grid_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t strid
         P.min_b[d] = (int)lo;
         int max_b = (int)hi;
         P.div_b[d] = max_b - P.min_b[d] + 1;
+        if (force_min_b && force_div_b) { // a shard of a larger grid: the whole cloud's box (same cells, same order)
+            if (P.min_b[d] < force_min_b[d] || max_b > force_min_b[d] + force_div_b[d] - 1)
+                return pcp_fail(ctx, PCP_ERR_RANGE, "voxel grid: shard exceeds the imposed grid box");
+            P.min_b[d] = force_min_b[d];
+            P.div_b[d] = force_div_b[d];
+        }
         cells *= (double)P.div_b[d];
         if (min_b) min_b[d] = P.min_b[d];
         if (div_b) div_b[d] = P.div_b[d];
@@ -309,10 +316,11 @@ extern "C" int pcp_centroid(pcp_ctx* ctx, const void* pts, size_t n, size_t stri
     return PCP_OK;
 }
 
-extern "C" int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf)
+// centre == NULL: the cloud's own serial-order centroid (the reference behaviour); otherwise the given centre
+// (a shard of a larger cloud is centred on the centroid of the WHOLE cloud so that voxels line up across shards)
+static int remove_duplicate_impl(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf,
+                                 const double* centre, const int32_t* min_b = nullptr, const int32_t* div_b = nullptr)
 {
-    if (!ctx || !n_inout || stride < 40 || (*n_inout && !pts_inout))
-        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_remove_duplicate: bad argument");
     size_t n = *n_inout;
     if (n == 0) return PCP_OK;
     std::lock_guard<std::mutex> lock(ctx->mu);
@@ -326,7 +334,14 @@ extern "C" int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_ino
     PCP_TRY(tmp.alloc(ctx, n * stride));
     PCP_TRY(s3.alloc(ctx, 3));
     PCP_TRY(bb.alloc(ctx, 1));
-    {
+    if (centre) {
+        pcp_bbox one;
+        memset(&one, 0, sizeof(one));
+        one.count = 1; // shift_kernel divides the sums by the count
+        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(s3.p, centre, 24, cudaMemcpyHostToDevice, ctx->stream));
+        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(bb.p, &one, sizeof(one), cudaMemcpyHostToDevice, ctx->stream));
+        PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    } else {
         StageTimer t(ctx, "dedup.centroid", 24.0 * n);
         PCP_TRY(pcp_serial_sum_device(ctx, d, n, stride, s3.p));
         PCP_TRY(pcp_bbox_device(ctx, d, n, stride, bb.p));
@@ -341,7 +356,8 @@ extern "C" int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_ino
     double l = (double)leaf; // const float -> setLeafSize(double,double,double), point_cloud_helper.cpp:57
     double leaf3[3] = {l, l, l};
     size_t m = 0;
-    PCP_TRY(pcp_voxel_grid_device(ctx, tmp.p, n, stride, leaf3, 1, d, stride, &m, nullptr, nullptr, nullptr, nullptr));
+    PCP_TRY(pcp_voxel_grid_device(ctx, tmp.p, n, stride, leaf3, 1, d, stride, &m, nullptr, nullptr, nullptr, nullptr,
+                                  min_b, div_b));
     if (m) {
         StageTimer t(ctx, "dedup.uncentre", 48.0 * m);
         shift_kernel<<<pcp_blocks_for(m, 256), 256, 0, ctx->stream>>>(d, m, stride, s3.p, cnt, +1);
@@ -351,4 +367,19 @@ extern "C" int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_ino
     PCP_TRY(io.commit(m * stride));
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return PCP_OK;
+}
+
+extern "C" int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf)
+{
+    if (!ctx || !n_inout || stride < 40 || (*n_inout && !pts_inout))
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_remove_duplicate: bad argument");
+    return remove_duplicate_impl(ctx, pts_inout, n_inout, stride, leaf, nullptr);
+}
+
+extern "C" int pcp_remove_duplicate_centred(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf,
+                                            const double centre[3], const int32_t min_b[3], const int32_t div_b[3])
+{
+    if (!ctx || !n_inout || !centre || !min_b || !div_b || stride < 40 || (*n_inout && !pts_inout))
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_remove_duplicate_centred: bad argument");
+    return remove_duplicate_impl(ctx, pts_inout, n_inout, stride, leaf, centre, min_b, div_b);
 }
