@@ -73,15 +73,19 @@ __global__ void __launch_bounds__(256) cell_fill_kernel(const unsigned long long
     }
 }
 
-// point-weighted occupancy histogram: bin floor(log2(count)) += count
+// point-weighted occupancy histogram: bin floor(log2(count)) += count (block-local bins, one atomic per bin)
 __global__ void __launch_bounds__(256) occupancy_kernel(const uint32_t* __restrict__ cstart, uint32_t ncell,
                                                         unsigned long long* __restrict__ bins)
 {
-    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncell) return;
-    uint32_t cnt = cstart[c + 1] - cstart[c];
-    int b = 31 - __clz(cnt);
-    atomicAdd(&bins[b], (unsigned long long)cnt);
+    __shared__ unsigned long long sb[32];
+    if (threadIdx.x < 32) sb[threadIdx.x] = 0ull;
+    __syncthreads();
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < ncell; c += gridDim.x * blockDim.x) {
+        const uint32_t cnt = cstart[c + 1] - cstart[c];
+        atomicAdd(&sb[31 - __clz(cnt)], (unsigned long long)cnt);
+    }
+    __syncthreads();
+    if (threadIdx.x < 32 && sb[threadIdx.x]) atomicAdd(&bins[threadIdx.x], sb[threadIdx.x]);
 }
 
 __global__ void __launch_bounds__(256) hash_insert_kernel(const unsigned long long* __restrict__ ckey,
@@ -353,7 +357,7 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
         // data-driven cell size: aim the point-weighted median occupancy at ~16 points per cell
         unsigned long long hb[32];
         IX_CUDA(cudaMemsetAsync(bins.p, 0, 32 * 8, ctx->stream));
-        occupancy_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->cstart, ncell, bins.p);
+        occupancy_kernel<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(ix->cstart, ncell, bins.p);
         ctx->launches++;
         IX_CUDA(cudaGetLastError());
         IX_CUDA(cudaMemcpyAsync(hb, bins.p, 32 * 8, cudaMemcpyDeviceToHost, ctx->stream));
