@@ -1,0 +1,272 @@
+// pcp_facade.hpp -- source-compatible C++ facade over the C ABI (include/pcp_cuda.h) for the call shapes the
+// reference's own callers use.  std-only: no Boost / Eigen / FLANN / OpenCV.
+//
+//   cloud_blend_double::PointXYZRGBA, PointCloud<PointT>      point_type.h:9-82, point_cloud.h:54-535
+//   KdTreeFLANN<PointT>::setInputCloud / nearestKSearch / radiusSearch        kd_tree.h:772-903
+//   VoxelGrid<PointT>::setInputCloud / setLeafSize / filter                   voxel_grid.h:482-549, 429-448
+//   PointCloudHelper::remove_duplicate / getMinMax3D / compute3DCentroid      point_cloud_helper.h:16-90,192-230
+//   CalculateFeature::calculate_plan_parameter[_rpca|_h_points]               calculate_feature.h:11-16
+//
+// Every method computes on the GPU through libpcp_cuda.so; there is no CPU path behind this header.  Errors of
+// the library surface as std::runtime_error (the reference's own error style -- cout + return code -- is kept
+// for the documented cases: filter() without input prints and returns an empty cloud, voxel_grid.h:815-821).
+#pragma once
+#include <cstdint>
+#include <cstring>
+#include <iostream>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../pcp_cuda.h"
+
+namespace cloud_blend_double {
+
+// point_type.h:9-82: 48 bytes, 16-aligned
+struct alignas(16) PointXYZRGBA {
+    union {
+        double data[4];
+        struct {
+            double x, y, z;
+        };
+    };
+    union {
+        struct {
+            uint8_t b, g, r, a;
+        };
+        uint32_t rgba;
+    };
+    uint32_t stamp_id;
+    PointXYZRGBA() : rgba(0), stamp_id(0)
+    {
+        x = y = z = 0.0;
+        data[3] = 1.0;
+    }
+};
+static_assert(sizeof(PointXYZRGBA) == 48, "PointXYZRGBA must match point_type.h");
+
+// data_struct.h:161-173 and :188-198
+typedef pcp_point_property LAS_POINT_PROPERTY;
+struct PlanSegment {
+    float normal_x = 0, normal_y = 0, normal_z = 0;
+    float min_value = 0, curvature = 0, Distance = 0;
+    std::vector<int> PointID;
+};
+
+template <typename PointT> class PointCloud {
+  public:
+    typedef std::shared_ptr<PointCloud<PointT>> Ptr;
+    typedef std::shared_ptr<const PointCloud<PointT>> ConstPtr;
+    std::vector<PointT> points;
+    uint32_t width = 0, height = 1;
+    bool is_dense = true;
+    size_t size() const { return points.size(); }
+    void push_back(const PointT& p)
+    {
+        points.push_back(p);
+        width = (uint32_t)points.size();
+        height = 1;
+    }
+    void clear()
+    {
+        points.clear();
+        width = 0;
+        height = 1;
+    }
+    PointT& operator[](size_t i) { return points[i]; }
+    const PointT& operator[](size_t i) const { return points[i]; }
+};
+typedef PointXYZRGBA CloudItem;              // cmm_types.h:11-14
+typedef PointCloud<CloudItem> Cloud;
+typedef Cloud::Ptr CloudPtr;
+
+namespace detail {
+inline void check(pcp_ctx* c, int st, const char* what)
+{
+    if (st != PCP_OK) throw std::runtime_error(std::string(what) + ": " + pcp_last_error(c));
+}
+// one context per process and device 0, created on first use
+inline pcp_ctx* context()
+{
+    static pcp_ctx* ctx = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        int st = pcp_create(&ctx, 0);
+        if (st != PCP_OK) throw std::runtime_error(std::string("pcp_create: ") + pcp_last_error(nullptr));
+    });
+    return ctx;
+}
+} // namespace detail
+
+// kd_tree.h:636-1031.  The FLANN kd-tree is replaced by the library's Morton grid; results (indices ascending
+// by squared distance, squared distances in double) follow kd_tree.h:814-845 / 863-903.
+template <typename PointT> class KdTreeFLANN {
+  public:
+    typedef std::shared_ptr<const PointCloud<PointT>> PointCloudConstPtr;
+    KdTreeFLANN(bool sorted = true) : sorted_(sorted) {}
+    ~KdTreeFLANN() { pcp_index_free(index_); }
+    KdTreeFLANN(const KdTreeFLANN&) = delete;
+    KdTreeFLANN& operator=(const KdTreeFLANN&) = delete;
+    void setEpsilon(double) {}                    // kd_tree.h:694-702: the search here is always exact
+    void setSortedResults(bool s) { sorted_ = s; } // results are always delivered sorted
+    void setInputCloud(const PointCloudConstPtr& cloud)
+    {
+        pcp_index_free(index_);
+        index_ = nullptr;
+        input_ = cloud;
+        detail::check(detail::context(),
+                      pcp_index_build(detail::context(), cloud->points.data(), cloud->points.size(), sizeof(PointT), 0.0,
+                                      &index_),
+                      "KdTreeFLANN::setInputCloud");
+    }
+    // const and safe to call from several host threads on one tree (calculate_feature.cpp:222-233)
+    int nearestKSearch(const PointT& point, int k, std::vector<int>& k_indices, std::vector<double>& k_sqr_distances) const
+    {
+        const int64_t nvalid = pcp_index_size(index_);
+        if (k > nvalid) k = (int)nvalid; // kd_tree.h:820-821
+        k_indices.assign(k, -1);
+        k_sqr_distances.assign(k, 0.0);
+        if (k <= 0) return 0;
+        int32_t found = 0;
+        detail::check(detail::context(),
+                      pcp_knn(index_, &point, 1, sizeof(PointT), k, k_indices.data(), k_sqr_distances.data(), &found),
+                      "KdTreeFLANN::nearestKSearch");
+        k_indices.resize(found);
+        k_sqr_distances.resize(found);
+        return found;
+    }
+    int radiusSearch(const PointT& point, double radius, std::vector<int>& k_indices, std::vector<double>& k_sqr_distances,
+                     unsigned int max_nn = 0) const
+    {
+        int64_t off[2] = {0, 0};
+        detail::check(detail::context(), pcp_radius_count(index_, &point, 1, sizeof(PointT), radius, max_nn, off),
+                      "KdTreeFLANN::radiusSearch");
+        k_indices.assign((size_t)off[1], -1);
+        k_sqr_distances.assign((size_t)off[1], 0.0);
+        if (off[1])
+            detail::check(detail::context(),
+                          pcp_radius_fill(index_, &point, 1, sizeof(PointT), radius, max_nn, off, k_indices.data(),
+                                          k_sqr_distances.data()),
+                          "KdTreeFLANN::radiusSearch");
+        return (int)off[1];
+    }
+    const pcp_index* handle() const { return index_; }
+
+  private:
+    bool sorted_;
+    PointCloudConstPtr input_;
+    pcp_index* index_ = nullptr;
+};
+
+// voxel_grid.h:454-1056 (no field filter).
+template <typename PointT> class VoxelGrid {
+  public:
+    typedef std::shared_ptr<const PointCloud<PointT>> PointCloudConstPtr;
+    void setInputCloud(const PointCloudConstPtr& cloud) { input_ = cloud; }
+    void setLeafSize(double lx, double ly, double lz) { leaf_[0] = lx, leaf_[1] = ly, leaf_[2] = lz; }
+    void setDownsampleAllData(bool f) { downsample_all_data_ = f; }
+    const int* getMinBoxCoordinates() const { return min_b_; }
+    const int* getNrDivisions() const { return div_b_; }
+    void filter(PointCloud<PointT>& output)
+    {
+        output.clear();
+        if (!input_) { // voxel_grid.h:815-821
+            std::cout << "[applyFilter] No input dataset given!" << std::endl;
+            return;
+        }
+        output.points.resize(input_->points.size());
+        size_t m = 0;
+        detail::check(detail::context(),
+                      pcp_voxel_grid(detail::context(), input_->points.data(), input_->points.size(), sizeof(PointT), leaf_,
+                                     downsample_all_data_ ? 1 : 0, output.points.data(), &m, min_b_, div_b_, nullptr,
+                                     nullptr),
+                      "VoxelGrid::filter");
+        output.points.resize(m);
+        output.width = (uint32_t)m, output.height = 1, output.is_dense = true; // voxel_grid.h:824-825,1055
+    }
+
+  private:
+    PointCloudConstPtr input_;
+    double leaf_[3] = {0, 0, 0};
+    bool downsample_all_data_ = true;
+    int32_t min_b_[3] = {0, 0, 0}, div_b_[3] = {0, 0, 0};
+};
+
+class PointCloudHelper {
+  public:
+    // point_cloud_helper.cpp:42-63: in place, float leaf
+    static void remove_duplicate(CloudPtr cloud, const float voxel_grid_size)
+    {
+        size_t n = cloud->points.size();
+        detail::check(detail::context(),
+                      pcp_remove_duplicate(detail::context(), cloud->points.data(), &n, sizeof(CloudItem), voxel_grid_size),
+                      "PointCloudHelper::remove_duplicate");
+        cloud->points.resize(n);
+        cloud->width = (uint32_t)n, cloud->height = 1, cloud->is_dense = true;
+    }
+    // point_cloud_helper.cpp:65-73: keep the original if fewer than min_num points would remain
+    static void remove_duplicate(CloudPtr cloud, const float voxel_grid_size, int min_num)
+    {
+        Cloud copy = *cloud;
+        remove_duplicate(cloud, voxel_grid_size);
+        if ((int)cloud->points.size() < min_num) *cloud = copy;
+    }
+    static void getMinMax3D(const Cloud& cloud, double mn[3], double mx[3])
+    {
+        detail::check(detail::context(),
+                      pcp_minmax(detail::context(), cloud.points.data(), cloud.points.size(), sizeof(CloudItem), mn, mx),
+                      "getMinMax3D");
+    }
+    static unsigned compute3DCentroid(const Cloud& cloud, double c[3])
+    {
+        uint64_t n = 0;
+        detail::check(detail::context(),
+                      pcp_centroid(detail::context(), cloud.points.data(), cloud.points.size(), sizeof(CloudItem), c, &n),
+                      "compute3DCentroid");
+        return (unsigned)n;
+    }
+};
+
+class CalculateFeature {
+  public:
+    // calculate_feature.cpp:119-206
+    static PlanSegment calculate_plan_parameter_h_points(CloudPtr cloud)
+    {
+        const int64_t off[2] = {0, (int64_t)cloud->points.size()};
+        pcp_plan_segment s;
+        detail::check(detail::context(),
+                      pcp_plane_fit(detail::context(), cloud->points.data(), sizeof(CloudItem), off, 1, &s),
+                      "calculate_plan_parameter_h_points");
+        PlanSegment r;
+        r.normal_x = s.normal_x, r.normal_y = s.normal_y, r.normal_z = s.normal_z;
+        r.min_value = s.min_value, r.curvature = s.curvature, r.Distance = s.Distance;
+        return r;
+    }
+    // calculate_feature.h:15 (declared, never defined in the reference): per-point plane fit on the k nearest
+    // neighbours (radius <= 0) or on the neighbours within `radius`
+    static std::shared_ptr<LAS_POINT_PROPERTY> calculate_plan_parameter(CloudPtr cloud, double radius, int k = 20)
+    {
+        std::shared_ptr<LAS_POINT_PROPERTY> out(new LAS_POINT_PROPERTY[cloud->points.size() ? cloud->points.size() : 1],
+                                                std::default_delete<LAS_POINT_PROPERTY[]>());
+        pcp_index* ix = nullptr;
+        pcp_ctx* c = detail::context();
+        detail::check(c, pcp_index_build(c, cloud->points.data(), cloud->points.size(), sizeof(CloudItem), 0.0, &ix),
+                      "calculate_plan_parameter");
+        int st = radius > 0 ? pcp_features_radius(ix, radius, 0, out.get(), nullptr, nullptr, nullptr)
+                            : pcp_features_knn(ix, k, out.get(), nullptr, nullptr, nullptr);
+        pcp_index_free(ix);
+        detail::check(c, st, "calculate_plan_parameter");
+        return out;
+    }
+    // calculate_feature.cpp:208: Radius is unused there too and k is 20 (:233).  The randomised hypothesis loop is
+    // not reproduced (it is not reproducible in the reference either); this is the plain PCA of the 20 neighbours.
+    static std::shared_ptr<LAS_POINT_PROPERTY> calculate_plan_parameter_rpca(CloudPtr cloud, double /*Radius*/,
+                                                                             float /*Pr*/ = 0.99f, float /*epi*/ = 0.5f)
+    {
+        return calculate_plan_parameter(cloud, 0.0, 20);
+    }
+};
+
+} // namespace cloud_blend_double

@@ -1,0 +1,62 @@
+// The reference's own smoke functions test_kd_tree and test_voxel_grid (main_test.cpp:126-188), written against
+// include/pcp/pcp_facade.hpp exactly as they are written against the reference headers.  They print what the
+// reference prints; the pytest wrapper compares the output with the derivable known answers.
+#include <cstdio>
+#include "../../include/pcp/pcp_facade.hpp"
+using namespace cloud_blend_double;
+
+static void test_voxel_grid()
+{
+    CloudPtr cloud(new Cloud);
+    for (int i = 0; i < 10; i++) {
+        CloudItem p;
+        p.x = i, p.y = i, p.z = i;
+        cloud->push_back(p);
+    }
+    for (int i = 0; i < 100; i++) {
+        CloudItem p;
+        p.x = 0.1 * i, p.y = 0.1 * i, p.z = 0.1 * i;
+        cloud->push_back(p);
+    }
+    VoxelGrid<CloudItem> vg;
+    vg.setInputCloud(cloud);
+    vg.setLeafSize(1, 1, 1);
+    Cloud out;
+    vg.filter(out);
+    printf("voxel %zu\n", out.size());
+    for (size_t i = 0; i < out.size() && i < 10; i++) printf("%.17g %.17g %.17g\n", out[i].x, out[i].y, out[i].z);
+}
+
+static void test_kd_tree()
+{
+    CloudPtr cloud(new Cloud);
+    for (int i = 0; i < 100; i++) {
+        CloudItem p;
+        p.x = 0.1 * i, p.y = 0.1 * i, p.z = 0.1 * i;
+        cloud->push_back(p);
+    }
+    KdTreeFLANN<CloudItem> kdtree;
+    kdtree.setInputCloud(cloud);
+    CloudItem q;
+    std::vector<int> index;
+    std::vector<double> dis;
+    int n = kdtree.nearestKSearch(q, 10, index, dis);
+    printf("knn %d\n", n);
+    for (int i = 0; i < n; i++) printf("%d %.17g\n", index[i], dis[i]);
+    PointCloudHelper::remove_duplicate(cloud, 1.0f);
+    printf("dedup %zu\n", cloud->size());
+    std::shared_ptr<LAS_POINT_PROPERTY> props = CalculateFeature::calculate_plan_parameter_rpca(cloud, 0.15);
+    printf("props %d %.9g\n", props.get()[0].PointID, props.get()[0].curvature);
+}
+
+int main()
+{
+    try {
+        test_voxel_grid();
+        test_kd_tree();
+    } catch (const std::exception& e) {
+        printf("error: %s\n", e.what());
+        return 3;
+    }
+    return 0;
+}

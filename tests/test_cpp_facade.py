@@ -1,0 +1,48 @@
+"""The C++ facade (include/pcp/pcp_facade.hpp) compiled into the reference's own smoke functions
+(tests/cpp/main_test_port.cpp = main_test.cpp:126-188 against our headers)."""
+import os
+import shutil
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _build(tmp_path):
+    cxx = shutil.which("g++") or "/usr/bin/g++"
+    exe = str(tmp_path / "main_test_port")
+    libdir = os.path.join(ROOT, "pointcloudprocess_b200")
+    r = subprocess.run([cxx, "-std=c++17", "-O1", "-Wall", os.path.join(ROOT, "tests", "cpp", "main_test_port.cpp"), "-o", exe,
+                        "-L" + libdir, "-lpcp_cuda", "-Wl,-rpath," + libdir], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+def test_facade_compiles_and_fails_loudly_without_gpu(tmp_path):
+    import pointcloudprocess_b200 as pcp
+    exe = _build(tmp_path)
+    if pcp.load_library().pcp_device_count() > 0:
+        pytest.skip("a GPU is present")
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 3 and "no CPU fallback" in r.stdout
+
+
+@pytest.mark.gpu
+def test_reference_smoke_functions_known_answers(tmp_path):
+    r = subprocess.run([_build(tmp_path)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    lines = r.stdout.strip().split("\n")
+    assert lines[0] == "voxel 10"  # 110 points -> 10 cells of 11 (main_test.cpp:126-154)
+    for c in range(10):
+        vals = [np.float32(c)] + [np.float32(0.1 * i) for i in range(10 * c, 10 * c + 10)]
+        exp = sum(float(v) for v in vals) / 11.0
+        assert [float(t) for t in lines[1 + c].split()] == [exp, exp, exp]
+    assert lines[11] == "knn 10"   # main_test.cpp:156-188: neighbours of the origin are 0..9 in order
+    for i in range(10):
+        idx, d2 = lines[12 + i].split()
+        d = 0.1 * i
+        assert int(idx) == i and float(d2) == (d * d + d * d) + d * d
+    assert lines[22] == "dedup 10"
+    assert lines[23].startswith("props 0 ")
