@@ -170,26 +170,62 @@ __global__ void __launch_bounds__(256) cinfo_kernel(const unsigned long long* __
     cinfo[c] = make_uint4((unsigned)x, (unsigned)y, (unsigned)z, cstart[c]);
 }
 
-__global__ void __launch_bounds__(256) item_count_kernel(const uint32_t* __restrict__ cstart, uint32_t ncell,
-                                                         uint32_t* __restrict__ nchunk)
+// ---- work items of the dense kNN kernel: the leaves of the implicit octree with capacity cmax ----
+// A base cell with more than cmax points is cut into chunks of 32 queries (level 0).  Sparser cells are merged
+// upwards: the leaf of base cell c is its largest ancestor (level <= PCP_ITEM_LMAX) that still holds at most
+// cmax points; the first base cell of the leaf emits the one item that carries all of the leaf's points, so
+// that the 3x3x3 block staged for them grows with the local point spacing (knn_fast.cuh).
+__device__ __forceinline__ int leaf_of_cell(const unsigned long long* __restrict__ ckey,
+                                            const uint32_t* __restrict__ cstart, const pcp_hslot* __restrict__ ltab,
+                                            uint32_t lmask, uint32_t c, uint32_t cmax, uint32_t& ca, uint32_t& npts)
 {
-    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncell) return;
-    nchunk[c] = (cstart[c + 1] - cstart[c] + 31) >> 5;
+    int level = 0;
+    ca = c;
+    npts = cstart[c + 1] - cstart[c];
+    if (npts > cmax) return 0;
+    const unsigned long long key = ckey[c];
+    for (int l = 1; l <= PCP_ITEM_LMAX; l++) {
+        uint32_t a = 0, cn = 0;
+        if (!pcp_hash_find(ltab, lmask, PCP_LKEY(l, key >> (3 * l)), a, cn)) break;
+        const uint32_t np = cstart[a + cn] - cstart[a];
+        if (np > cmax) break;
+        level = l, ca = a, npts = np;
+    }
+    return level;
 }
 
-__global__ void __launch_bounds__(256) item_fill_kernel(const uint32_t* __restrict__ cstart,
-                                                        const uint32_t* __restrict__ nchunk,
-                                                        const uint32_t* __restrict__ off, uint32_t ncell,
-                                                        uint32_t* __restrict__ item_cell,
-                                                        uint32_t* __restrict__ item_first, uint32_t* __restrict__ nitem)
+__global__ void __launch_bounds__(256) item_count_kernel(const unsigned long long* __restrict__ ckey,
+                                                         const uint32_t* __restrict__ cstart,
+                                                         const pcp_hslot* __restrict__ ltab, uint32_t lmask,
+                                                         uint32_t ncell, uint32_t cmax, uint32_t* __restrict__ nchunk)
 {
     uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= ncell) return;
-    uint32_t o = off[c], k = nchunk[c], s = cstart[c];
-    for (uint32_t j = 0; j < k; j++) {
-        item_cell[o + j] = c;
-        item_first[o + j] = s + 32 * j;
+    uint32_t ca, npts;
+    const int level = leaf_of_cell(ckey, cstart, ltab, lmask, c, cmax, ca, npts);
+    nchunk[c] = level == 0 ? (npts + 31) >> 5 : (ca == c ? 1u : 0u);
+}
+
+__global__ void __launch_bounds__(256) item_fill_kernel(const unsigned long long* __restrict__ ckey,
+                                                        const uint32_t* __restrict__ cstart,
+                                                        const pcp_hslot* __restrict__ ltab, uint32_t lmask,
+                                                        const uint32_t* __restrict__ nchunk,
+                                                        const uint32_t* __restrict__ off, uint32_t ncell, uint32_t cmax,
+                                                        uint32_t* __restrict__ item_cell,
+                                                        uint32_t* __restrict__ item_first,
+                                                        uint32_t* __restrict__ item_meta, uint32_t* __restrict__ nitem)
+{
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncell) return;
+    const uint32_t o = off[c], k = nchunk[c], s = cstart[c];
+    if (k) {
+        uint32_t ca, npts;
+        const int level = leaf_of_cell(ckey, cstart, ltab, lmask, c, cmax, ca, npts);
+        for (uint32_t j = 0; j < k; j++) {
+            item_cell[o + j] = c;
+            item_first[o + j] = s + 32 * j;
+            item_meta[o + j] = ((uint32_t)level << 8) | min(32u, npts - 32 * j);
+        }
     }
     if (c == ncell - 1) *nitem = o + k;
 }
@@ -241,7 +277,51 @@ static void index_release(pcp_index* ix)
     pcp_arena_free(c, ix->cinfo);
     pcp_arena_free(c, ix->item_cell);
     pcp_arena_free(c, ix->item_first);
+    pcp_arena_free(c, ix->item_meta);
     delete ix;
+}
+
+int pcp_index_build_items(pcp_ctx* ctx, pcp_index* ix, uint32_t cmax)
+{
+    if (cmax < 1) cmax = 1;
+    if (cmax > 32) cmax = 32;
+    if (ix->item_cell && ix->item_cmax == cmax) return PCP_OK;
+    StageTimer t(ctx, "index.items");
+    const uint32_t ncell = ix->ncell;
+    pcp_arena_free(ctx, ix->item_cell);
+    pcp_arena_free(ctx, ix->item_first);
+    pcp_arena_free(ctx, ix->item_meta);
+    ix->item_cell = ix->item_first = ix->item_meta = nullptr;
+    ix->nitem = 0;
+    DevBuf<uint32_t> nchunk, off, cnt;
+    PCP_TRY(nchunk.alloc(ctx, ncell));
+    PCP_TRY(off.alloc(ctx, ncell));
+    PCP_TRY(cnt.alloc(ctx, 1));
+    item_count_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->ckey, ix->cstart, ix->ltab, ix->lmask,
+                                                                         ncell, cmax, nchunk.p);
+    ctx->launches++;
+    PCP_CUDA_TRY(ctx, cudaGetLastError());
+    PCP_TRY(pcp_exclusive_scan_u32(ctx, nchunk.p, off.p, ncell));
+    // nitem <= ncell + n/32
+    const size_t cap_items = (size_t)ncell + ix->n / 32 + 1;
+    void* q = nullptr;
+    PCP_TRY(pcp_arena_alloc(ctx, cap_items * 4, &q));
+    ix->item_cell = (uint32_t*)q;
+    PCP_TRY(pcp_arena_alloc(ctx, cap_items * 4, &q));
+    ix->item_first = (uint32_t*)q;
+    PCP_TRY(pcp_arena_alloc(ctx, cap_items * 4, &q));
+    ix->item_meta = (uint32_t*)q;
+    item_fill_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->ckey, ix->cstart, ix->ltab, ix->lmask,
+                                                                        nchunk.p, off.p, ncell, cmax, ix->item_cell,
+                                                                        ix->item_first, ix->item_meta, cnt.p);
+    ctx->launches++;
+    PCP_CUDA_TRY(ctx, cudaGetLastError());
+    uint32_t ni = 0;
+    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(&ni, cnt.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    ix->nitem = ni;
+    ix->item_cmax = cmax;
+    return PCP_OK;
 }
 
 int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, double cell_size, pcp_index** out)
@@ -445,31 +525,7 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
         ctx->launches++;
         IX_CUDA(cudaGetLastError());
     }
-    {
-        StageTimer t(ctx, "index.items");
-        DevBuf<uint32_t> nchunk, off;
-        IX_TRY(nchunk.alloc(ctx, ncell));
-        IX_TRY(off.alloc(ctx, ncell));
-        item_count_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->cstart, ncell, nchunk.p);
-        ctx->launches++;
-        IX_CUDA(cudaGetLastError());
-        IX_TRY(pcp_exclusive_scan_u32(ctx, nchunk.p, off.p, ncell));
-        // nitem <= ncell + nv/32
-        size_t cap_items = (size_t)ncell + nv / 32 + 1;
-        IX_TRY(pcp_arena_alloc(ctx, cap_items * 4, &q));
-        ix->item_cell = (uint32_t*)q;
-        IX_TRY(pcp_arena_alloc(ctx, cap_items * 4, &q));
-        ix->item_first = (uint32_t*)q;
-        item_fill_kernel<<<pcp_blocks_for(ncell, 256), 256, 0, ctx->stream>>>(ix->cstart, nchunk.p, off.p, ncell,
-                                                                            ix->item_cell, ix->item_first,
-                                                                            ncell_dev.p + 1);
-        ctx->launches++;
-        IX_CUDA(cudaGetLastError());
-        uint32_t ni = 0;
-        IX_CUDA(cudaMemcpyAsync(&ni, ncell_dev.p + 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        IX_CUDA(cudaStreamSynchronize(ctx->stream));
-        ix->nitem = ni;
-    }
+    IX_TRY(pcp_index_build_items(ctx, ix, PCP_ITEM_CMAX_DEFAULT));
 #undef IX_TRY
 #undef IX_CUDA
     *out = ix;

@@ -50,11 +50,15 @@ struct pcp_index {
     // per-cell work items for the cell-cooperative kernels: item -> (cell, chunk of 32 queries)
     uint32_t* item_cell = nullptr;
     uint32_t* item_first = nullptr; // first sorted point of the chunk
+    uint32_t* item_meta = nullptr;  // level << 8 | queries (index.cu: octree leaves of capacity item_cmax)
     uint32_t nitem = 0;
+    uint32_t item_cmax = 0;
 };
 
 #define PCP_EMPTY_KEY 0xffffffffffffffffull
 #define PCP_HLEVELS 5
+#define PCP_ITEM_LMAX 3           // coarsest level of a dense-kernel work item
+#define PCP_ITEM_CMAX_DEFAULT 24  // leaf capacity tuned for k = 20 (see pcp_item_cmax)
 #define PCP_LKEY(level, prefix) (((unsigned long long)(level) << 58) | (prefix))
 
 __host__ __device__ __forceinline__ unsigned long long pcp_spread3(unsigned long long v)
@@ -149,4 +153,5 @@ __device__ __forceinline__ void pcp_level_range(const unsigned long long* __rest
 }
 #endif
 
+int pcp_index_build_items(pcp_ctx* ctx, pcp_index* ix, uint32_t cmax);
 int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, double cell_size, pcp_index** out);

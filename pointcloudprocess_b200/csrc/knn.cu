@@ -3,6 +3,7 @@
 // (KdTreeFLANN::nearestKSearch, kd_tree.h:814-845).
 #include "knn_warp.cuh"
 #include "knn_far.cuh"
+#include <algorithm>
 #include <climits>
 #include <cstdlib>
 
@@ -139,6 +140,9 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
         PCP_CUDA_TRY(ctx, cudaMemsetAsync(counters.p, 0, 32, ctx->stream));
         uint32_t nfail = 0;
         if (kk <= 128) {
+            // work items = octree leaves whose capacity follows k (index.cu; 24 for k = 20)
+            // (a cache inside the index, rebuilt under the context lock when k changes)
+            PCP_TRY(pcp_index_build_items(ctx, const_cast<pcp_index*>(ix), (uint32_t)std::min(32, std::max(8, (int)(1.15 * kk + 0.5)))));
             pcp_fknn_params P;
             P.rec = ix->rec;
             P.fpt = ix->fpt;
@@ -152,6 +156,7 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
             P.ncell = ix->ncell;
             P.item_cell = ix->item_cell;
             P.item_first = ix->item_first;
+            P.item_meta = ix->item_meta;
             P.nitem = ix->nitem;
             P.g = ix->grid;
             P.k = k;
@@ -172,8 +177,8 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
             DevBuf<unsigned long long> dbg;
             const bool want_dbg = getenv("PCP_KNN_DEBUG") != nullptr;
             if (want_dbg) {
-                PCP_TRY(dbg.alloc(ctx, 16));
-                PCP_CUDA_TRY(ctx, cudaMemsetAsync(dbg.p, 0, 16 * 8, ctx->stream));
+                PCP_TRY(dbg.alloc(ctx, 24));
+                PCP_CUDA_TRY(ctx, cudaMemsetAsync(dbg.p, 0, 24 * 8, ctx->stream));
                 P.dbg = dbg.p;
             }
             {
@@ -184,10 +189,9 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 unsigned long long h[16];
                 PCP_CUDA_TRY(ctx, cudaMemcpyAsync(h, dbg.p, 16 * 8, cudaMemcpyDeviceToHost, ctx->stream));
                 PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-                fprintf(stderr, "[pcp knn] h=%.4f items=%llu staged=%llu queries=%llu cand/item=%.1f dense_items=%llu ok1=%llu ranged_second=%llu "
-                                "uncert=%llu overflow=%llu ranged_attempts=%llu ranged_cand/attempt=%.1f ranged_uncert=%llu\n", ix->grid.h,
-                        h[0], h[1], h[2], h[0] ? (double)h[3] / h[0] : 0.0, h[4], h[5], h[6], h[7], h[8], h[9],
-                        h[9] ? (double)h[10] / h[9] : 0.0, h[11]);
+                fprintf(stderr, "[pcp knn] h=%.4f items=%llu staged=%llu queries=%llu cand/item=%.1f settled=%llu beyond=%llu "
+                                "ambiguous=%llu too_dense: items=%llu queries=%llu too_sparse queries=%llu\n", ix->grid.h,
+                        h[0], h[1], h[2], h[0] ? (double)h[3] / h[0] : 0.0, h[5], h[6], h[7], h[4], h[8], h[9]);
             }
             {
                 // everything the dense kernel left open: sparse cells, far neighbours, FP32 ambiguities
@@ -205,7 +209,15 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
             PCP_CUDA_TRY(ctx, cudaMemcpyAsync(hc, counters.p, 20, cudaMemcpyDeviceToHost, ctx->stream));
             PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
             nfail = hc[4];
-            if (want_dbg) fprintf(stderr, "[pcp knn] far queries=%u, streaming-kernel queries=%u\n", hc[0], hc[4]);
+            if (want_dbg) {
+                unsigned long long h[24];
+                PCP_CUDA_TRY(ctx, cudaMemcpyAsync(h, dbg.p, 24 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+                PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+                fprintf(stderr, "[pcp knn] far queries=%u attempts=%llu (block too sparse %llu) cells/attempt=%.1f searches=%llu "
+                                "cand/search=%.1f selected cells/search=%.1f uncertified=%llu streaming-kernel queries=%u\n",
+                        hc[0], h[10], h[16], h[10] ? (double)h[11] / h[10] : 0.0, h[12], h[12] ? (double)h[13] / h[12] : 0.0,
+                        h[12] ? (double)h[14] / h[12] : 0.0, h[15], hc[4]);
+            }
             if (nfail) PCP_CUDA_TRY(ctx, cudaMemcpyAsync(counters.p, &hc[4], 4, cudaMemcpyHostToDevice, ctx->stream));
         } else {
             // k too large for the cell kernel's shared-memory lists: every query takes the warp kernel

@@ -223,6 +223,8 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
                 if (lane >= o) cpre += v;
             }
             const uint32_t NC = __shfl_sync(0xffffffffu, cpre, 31);
+            PCP_FK_DBG(10, 1);
+            PCP_FK_DBG(11, NC);
             __syncwarp();
             S.tab[lane] = lane < 27 ? cpre - (cb - ca) : 0xffffffffu;
             S.tab[32 + lane] = ca;
@@ -232,7 +234,10 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
                 uint32_t tl = (cb > ca) ? __ldg(P.cstart + cb) - __ldg(P.cstart + ca) : 0u;
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) tl += __shfl_xor_sync(0xffffffffu, tl, o);
-                if (tl < (uint32_t)P.kk && level < P.g.top_level) continue;
+                if (tl < (uint32_t)P.kk && level < P.g.top_level) {
+                    PCP_FK_DBG(16, 1);
+                    continue;
+                }
                 // ---- bound: cells binned by farthest-corner distance, weighted by point count ----
                 const double H = ldexp(P.g.h, level);
                 const float topA = (float)(27.0 * H * H) * 1.001f;
@@ -314,11 +319,15 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
                 T += __shfl_sync(0xffffffffu, inc, 31);
             }
             __syncwarp();
+            PCP_FK_DBG(12, 1);
+            PCP_FK_DBG(13, T);
+            PCP_FK_DBG(14, nsel);
             pcp_far_src src{P.rec, S.cand, S.selpre, S.selstart, T, q.x, q.y, q.z, T <= PCP_FK_CAND};
             if (src.resident) src.stage(0, lane);
             double dk;
             const float top = Ueff * 1.001f;
             st = pcp_fk_search<32, CAP>(src, S, P.rec, lane, true, slot, P.kk, 0.f, 0.f, 0.f, q.x, q.y, q.z, top, g2, e1, dk);
+            PCP_FK_DBG(15, st == PCP_FK_UNCERT);
             if (st == PCP_FK_OK) U = __double2float_ru(dk);
             if (st == PCP_FK_OK || st == PCP_FK_OVERFLOW) break;
             if (st == PCP_FK_UNCERT) U = __double2float_ru(dk) * 1.000001f; // exact k-th of the scanned set: a true bound

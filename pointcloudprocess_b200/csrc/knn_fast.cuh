@@ -42,6 +42,7 @@ struct pcp_fknn_params {
     uint32_t ncell;
     const uint32_t* item_cell;
     const uint32_t* item_first;
+    const uint32_t* item_meta; // level << 8 | queries
     uint32_t nitem;
     pcp_grid g;
     int k, kk;
@@ -518,11 +519,6 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
     S.sqpos[lane] = 0xffffffffu;
     __syncwarp();
     int fill = 0;
-    const double h0 = P.g.h;
-    // |float - true| of a block-relative coordinate difference: operands up to 2h and 3h in magnitude, each
-    // rounded once (2^-24 relative), plus the rounding of the double subtraction p - origin
-    const float e1 = (float)(8.0 * 5.97e-8 * h0 + 2.0 * P.epsd) * 1.0001f;
-    const float top0 = (float)(2.25 * h0 * h0); // nothing farther than 1.5 h can be certified at level 0
     while (true) {
         uint32_t item = 0;
         if (lane == 0) item = atomicAdd(P.work_counter, 1u);
@@ -530,8 +526,15 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
         if (item >= P.nitem) break;
         const uint32_t cell = __ldg(P.item_cell + item);
         const uint32_t first = __ldg(P.item_first + item);
-        const uint32_t cend = __ldg(P.cstart + cell + 1);
-        const int nq = (int)min(32u, cend - first);
+        const uint32_t meta = __ldg(P.item_meta + item);
+        // the item is an octree leaf: a cell of edge h0 = h * 2^level holding the nq queries first..first+nq-1
+        const int level = (int)(meta >> 8);
+        const int nq = (int)(meta & 0xffu);
+        const double h0 = P.g.h * (double)(1 << level);
+        // |float - true| of a block-relative coordinate difference: operands up to 2h and 3h in magnitude, each
+        // rounded once (2^-24 relative), plus the rounding of the double subtraction p - origin
+        const float e1 = (float)(8.0 * 5.97e-8 * h0 + 2.0 * P.epsd) * 1.0001f;
+        const float top0 = (float)(2.25 * h0 * h0); // nothing farther than 1.5 h can be certified in this block
         // lane j holds query j of the item (halo points are candidates only)
         const pcp_rec myq = pcp_load_rec(P.rec, first + (lane < nq ? lane : 0));
         const unsigned want = __ballot_sync(0xffffffffu, lane < nq && myq.idx < P.query_limit);
@@ -542,7 +545,9 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
             fill = 0;
         }
         int cx, cy, cz;
-        pcp_demorton(__ldg(P.ckey + cell), cx, cy, cz);
+        pcp_demorton(__ldg(P.ckey + cell) >> (3 * level), cx, cy, cz);
+        const int dimx = ((P.g.dims[0] - 1) >> level) + 1, dimy = ((P.g.dims[1] - 1) >> level) + 1,
+                  dimz = ((P.g.dims[2] - 1) >> level) + 1;
         const double ox = P.g.org[0] + (double)cx * h0, oy = P.g.org[1] + (double)cy * h0, oz = P.g.org[2] + (double)cz * h0;
         const float myfx = (float)(myq.x - ox), myfy = (float)(myq.y - oy), myfz = (float)(myq.z - oz);
 
@@ -552,8 +557,17 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
             int dx, dy, dz;
             pcp_nb_offset(lane, dx, dy, dz);
             const int nx = cx + dx, ny = cy + dy, nz = cz + dz;
-            if (nx >= 0 && ny >= 0 && nz >= 0 && nx < P.g.dims[0] && ny < P.g.dims[1] && nz < P.g.dims[2])
-                if (!pcp_hash_find(P.htab, P.hmask, pcp_morton(nx, ny, nz), nb_start, nb_count)) nb_count = 0;
+            if (nx >= 0 && ny >= 0 && nz >= 0 && nx < dimx && ny < dimy && nz < dimz) {
+                if (level == 0) {
+                    if (!pcp_hash_find(P.htab, P.hmask, pcp_morton(nx, ny, nz), nb_start, nb_count)) nb_count = 0;
+                } else {
+                    uint32_t a = 0, cn = 0;
+                    if (pcp_hash_find(P.ltab, P.lmask, PCP_LKEY(level, pcp_morton(nx, ny, nz)), a, cn)) {
+                        nb_start = __ldg(P.cstart + a);
+                        nb_count = __ldg(P.cstart + a + cn) - nb_start;
+                    }
+                }
+            }
         }
         uint32_t pre = nb_count;
 #pragma unroll
@@ -569,6 +583,8 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
         PCP_FK_DBG(2, nwant);
         PCP_FK_DBG(3, total);
         PCP_FK_DBG(4, total > PCP_FK_CAND);
+        PCP_FK_DBG(8, total > PCP_FK_CAND ? nwant : 0);
+        PCP_FK_DBG(9, total < (uint32_t)P.kk ? nwant : 0);
         unsigned okmask = 0;
         // lane j: upper bound of query j's k-th squared distance (+inf: none; -1: none, block too dense to stage)
         float myU = (total > PCP_FK_CAND) ? -1.0f : __int_as_float(0x7f800000);
@@ -603,11 +619,11 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
                 float dout = 3.0e38f;
                 const float hf = (float)h0;
                 if (cx > 0) dout = fminf(dout, qfx + hf);
-                if (cx + 1 < P.g.dims[0]) dout = fminf(dout, 2.0f * hf - qfx);
+                if (cx + 1 < dimx) dout = fminf(dout, 2.0f * hf - qfx);
                 if (cy > 0) dout = fminf(dout, qfy + hf);
-                if (cy + 1 < P.g.dims[1]) dout = fminf(dout, 2.0f * hf - qfy);
+                if (cy + 1 < dimy) dout = fminf(dout, 2.0f * hf - qfy);
                 if (cz > 0) dout = fminf(dout, qfz + hf);
-                if (cz + 1 < P.g.dims[2]) dout = fminf(dout, 2.0f * hf - qfz);
+                if (cz + 1 < dimz) dout = fminf(dout, 2.0f * hf - qfz);
                 dout = fmaxf(dout - (4.0f * e1 + 1e-6f * hf), 0.0f);
                 const float g2 = dout * dout * 0.999999f;
                 const int slot = fill + __popc(want & ((1u << sj) - 1u));
@@ -621,6 +637,8 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
                     const int sg = __shfl_sync(0xffffffffu, st, g * GS);
                     const float dg = __shfl_sync(0xffffffffu, dku, g * GS);
                     if (jg >= 0) {
+                        PCP_FK_DBG(6, sg == PCP_FD_BEYOND);
+                        PCP_FK_DBG(7, sg == PCP_FD_AMBIG);
                         if (sg == PCP_FD_OK) okmask |= 1u << jg;
                         if ((sg == PCP_FD_AMBIG || sg == PCP_FD_OK) && lane == jg) myU = dg * 1.000001f;
                     }
