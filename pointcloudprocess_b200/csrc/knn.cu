@@ -214,9 +214,11 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 PCP_CUDA_TRY(ctx, cudaMemcpyAsync(h, dbg.p, 24 * 8, cudaMemcpyDeviceToHost, ctx->stream));
                 PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
                 fprintf(stderr, "[pcp knn] far queries=%u attempts=%llu (block too sparse %llu) cells/attempt=%.1f searches=%llu "
-                                "cand/search=%.1f selected cells/search=%.1f uncertified=%llu streaming-kernel queries=%u\n",
+                                "cand/search=%.1f selected cells/search=%.1f uncertified=%llu tightened=%llu streaming-kernel queries=%u\n",
                         hc[0], h[10], h[16], h[10] ? (double)h[11] / h[10] : 0.0, h[12], h[12] ? (double)h[13] / h[12] : 0.0,
-                        h[12] ? (double)h[14] / h[12] : 0.0, h[15], hc[4]);
+                        h[12] ? (double)h[14] / h[12] : 0.0, h[15], h[17], hc[4]);
+                fprintf(stderr, "[pcp knn] far failures: overflow=%llu (cells %llu) beyond=%llu uncert=%llu no-bound=%llu mean level=%.2f\n",
+                        h[18], h[23], h[19], h[20], h[21], hc[4] ? (double)h[22] / hc[4] : 0.0);
             }
             if (nfail) PCP_CUDA_TRY(ctx, cudaMemcpyAsync(counters.p, &hc[4], 4, cudaMemcpyHostToDevice, ctx->stream));
         } else {

@@ -267,58 +267,78 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
                 __syncwarp();
             }
             // ---- prune: keep the base cells the sphere of radius sqrt(Ueff) touches ----
-            uint32_t nsel = 0;
-            __syncwarp();
-            for (int i = lane; i < PCP_FAR_NSEL; i += 32) S.selpre[i] = 0xffffffffu;
-            __syncwarp();
-            const bool cached = (U == INF); // pass A ran for this block and filled the cache
-            for (uint32_t c0 = 0; c0 < NC; c0 += 32) {
-                const uint32_t fc = c0 + lane;
-                bool sel = false;
-                uint32_t cs = 0, cc = 0;
-                if (fc < NC) {
-                    if (cached && fc < PCP_FAR_CCACHE) {
-                        const float4 e = S.ccache[fc];
-                        sel = e.x <= Ueff;
-                        cs = __float_as_uint(e.y), cc = __float_as_uint(e.z);
-                    } else {
-                        int t = 0;
+            // (inside = true: only the cells that lie entirely inside the sphere)
+            auto select_cells = [&](float bound, bool inside, bool cached) -> uint32_t {
+                uint32_t nsel = 0;
+                __syncwarp();
+                for (int i = lane; i < PCP_FAR_NSEL; i += 32) S.selpre[i] = 0xffffffffu;
+                __syncwarp();
+                for (uint32_t c0 = 0; c0 < NC; c0 += 32) {
+                    const uint32_t fc = c0 + lane;
+                    bool sel = false;
+                    uint32_t cs = 0, cc = 0;
+                    if (fc < NC) {
+                        if (cached && fc < PCP_FAR_CCACHE) {
+                            const float4 e = S.ccache[fc];
+                            sel = e.x <= bound;
+                            cs = __float_as_uint(e.y), cc = __float_as_uint(e.z);
+                        } else {
+                            int t = 0;
 #pragma unroll
-                        for (int step = 16; step; step >>= 1)
-                            if (S.tab[t + step] <= fc) t += step;
-                        const uint32_t ci = S.tab[32 + t] + (fc - S.tab[t]);
-                        const uint4 ce = __ldg(P.cinfo + ci);
-                        float mn, mx;
-                        pcp_cell_dist2(Q, (int)ce.x, (int)ce.y, (int)ce.z, mn, mx);
-                        sel = mn <= Ueff;
-                        if (sel) cs = ce.w, cc = __ldg(P.cstart + ci + 1) - cs;
+                            for (int step = 16; step; step >>= 1)
+                                if (S.tab[t + step] <= fc) t += step;
+                            const uint32_t ci = S.tab[32 + t] + (fc - S.tab[t]);
+                            const uint4 ce = __ldg(P.cinfo + ci);
+                            float mn, mx;
+                            pcp_cell_dist2(Q, (int)ce.x, (int)ce.y, (int)ce.z, mn, mx);
+                            sel = (inside ? mx : mn) <= bound;
+                            if (sel) cs = ce.w, cc = __ldg(P.cstart + ci + 1) - cs;
+                        }
                     }
+                    const unsigned mask = __ballot_sync(0xffffffffu, sel);
+                    const uint32_t at = nsel + __popc(mask & ((1u << lane) - 1u));
+                    if (sel && at < PCP_FAR_NSEL) S.selstart[at] = cs, S.selpre[at] = cc;
+                    nsel += __popc(mask);
                 }
-                const unsigned mask = __ballot_sync(0xffffffffu, sel);
-                const uint32_t at = nsel + __popc(mask & ((1u << lane) - 1u));
-                if (sel && at < PCP_FAR_NSEL) S.selstart[at] = cs, S.selpre[at] = cc;
-                nsel += __popc(mask);
+                __syncwarp();
+                return nsel;
+            };
+            // exclusive prefix of the selected cells' counts; returns the number of candidates
+            auto prefix_counts = [&](uint32_t nsel) -> uint32_t {
+                uint32_t T = 0;
+                for (uint32_t c0 = 0; c0 < nsel; c0 += 32) {
+                    const uint32_t i = c0 + lane;
+                    const uint32_t cnt = i < nsel ? S.selpre[i] : 0u;
+                    uint32_t inc = cnt;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+                        if (lane >= o) inc += v;
+                    }
+                    if (i < nsel) S.selpre[i] = T + inc - cnt;
+                    T += __shfl_sync(0xffffffffu, inc, 31);
+                }
+                __syncwarp();
+                return T;
+            };
+            // Too many cells for the corner bound (a sparse query next to a dense surface): the cells that lie
+            // entirely inside that sphere hold k points by construction, and their exact k-th distance is a much
+            // tighter bound; search those, take it and run this level again.
+            uint32_t nsel = 0;
+            bool inner = false;
+#pragma unroll 1
+            for (int pass = 0; pass < 2; pass++) {
+                nsel = select_cells(Ueff, pass == 1, pass == 0 && U == INF); // pass A filled the cache
+                if (nsel <= PCP_FAR_NSEL || U != INF) break;
+                inner = pass == 0;
             }
-            __syncwarp();
             if (nsel > PCP_FAR_NSEL) {
+                PCP_FK_DBG(23, 1);
                 st = PCP_FK_OVERFLOW;
                 break;
             }
-            // exclusive prefix of the counts
-            uint32_t T = 0;
-            for (uint32_t c0 = 0; c0 < nsel; c0 += 32) {
-                const uint32_t i = c0 + lane;
-                const uint32_t cnt = i < nsel ? S.selpre[i] : 0u;
-                uint32_t inc = cnt;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
-                    if (lane >= o) inc += v;
-                }
-                if (i < nsel) S.selpre[i] = T + inc - cnt;
-                T += __shfl_sync(0xffffffffu, inc, 31);
-            }
-            __syncwarp();
+            const uint32_t T = prefix_counts(nsel);
+            PCP_FK_DBG(17, inner);
             PCP_FK_DBG(12, 1);
             PCP_FK_DBG(13, T);
             PCP_FK_DBG(14, nsel);
@@ -326,7 +346,17 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
             if (src.resident) src.stage(0, lane);
             double dk;
             const float top = Ueff * 1.001f;
-            st = pcp_fk_search<32, CAP>(src, S, P.rec, lane, true, slot, P.kk, 0.f, 0.f, 0.f, q.x, q.y, q.z, top, g2, e1, dk);
+            st = pcp_fk_search<32, CAP>(src, S, P.rec, lane, true, slot, P.kk, 0.f, 0.f, 0.f, q.x, q.y, q.z, top,
+                                        inner ? 0.0 : g2, e1, dk);
+            if (inner) {
+                if (st != PCP_FK_UNCERT) {
+                    st = PCP_FK_OVERFLOW;
+                    break;
+                }
+                U = __double2float_ru(dk) * 1.000001f;
+                level--;
+                continue;
+            }
             PCP_FK_DBG(15, st == PCP_FK_UNCERT);
             if (st == PCP_FK_OK) U = __double2float_ru(dk);
             if (st == PCP_FK_OK || st == PCP_FK_OVERFLOW) break;
@@ -337,6 +367,11 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
             S.skd[slot] = U; // set below from the exact k-th distance of the successful attempt
             fill++;
         } else {
+            PCP_FK_DBG(18, st == PCP_FK_OVERFLOW);
+            PCP_FK_DBG(19, st == PCP_FK_BEYOND);
+            PCP_FK_DBG(20, st == PCP_FK_UNCERT);
+            PCP_FK_DBG(21, U == INF);
+            PCP_FK_DBG(22, level);
             if (lane == 0) A.fail_list[atomicAdd(A.fail_count, 1u)] = qpos;
         }
     }

@@ -234,7 +234,53 @@ __device__ __forceinline__ int pcp_fk_search(const Src& src, const pcp_fk_smem<C
     const int bstar = __shfl_sync(0xffffffffu, myb, gbase + L);
     if (st == PCP_FK_OK && bstar >= PCP_FK_NB - 1) st = PCP_FK_BEYOND;
     // every true kk-nearest has FP32 d2 <= edge + 3*delta (delta: FP32 error bound at that distance)
-    const float edge = pcp_fk_edge(min(bstar, PCP_FK_NB - 2), key0);
+    float edge = pcp_fk_edge(min(bstar, PCP_FK_NB - 2), key0);
+    if constexpr (G == 32) {
+        // A bucket spans 19% of d2; behind a gap in the distances (a sparse query over a dense surface) it can
+        // hold far more than the list does.  Cut that bucket into 64 linear slices and take the slice at which
+        // the count reaches kk.
+        uint32_t below = 0, upto = 0; // candidates in the buckets before b*, and up to and including it
+        {
+            uint32_t c = incl - tot;
+#pragma unroll
+            for (int i = 0; i < NBL; i++) {
+                if (gl * NBL + i == bstar) below = c, upto = c + hb[i];
+                c += hb[i];
+            }
+            below = __shfl_sync(0xffffffffu, below, L);
+            upto = __shfl_sync(0xffffffffu, upto, L);
+        }
+        if (st == PCP_FK_OK && upto > (uint32_t)CAP) {
+            const float lo = bstar ? pcp_fk_edge(bstar - 1, key0) : 0.0f;
+            const float w = (edge - lo) * (1.0f / PCP_FK_NB), iw = 1.0f / w;
+            __syncwarp();
+            hist[lane] = 0, hist[lane + 32] = 0;
+            __syncwarp();
+            src.for_each(gl, [&](bool valid, float x, float y, float z, uint32_t) {
+                const float dx = qfx - x, dy = qfy - y, dz = qfz - z;
+                const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+                if (valid && pcp_fk_bucket(d2, key0) == bstar)
+                    atomicAdd(&hist[min(max((int)((d2 - lo) * iw), 0), PCP_FK_NB - 1)], 1u);
+            });
+            __syncwarp();
+            const uint32_t s0 = hist[2 * lane], s1 = hist[2 * lane + 1];
+            uint32_t si = s0 + s1;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, si, o);
+                if (lane >= o) si += v;
+            }
+            const uint32_t need = (uint32_t)kk - below; // >= 1: the count reaches kk inside b*
+            const unsigned sb = __ballot_sync(0xffffffffu, si >= need);
+            if (sb) {
+                const int SLn = __ffs(sb) - 1;
+                const uint32_t before = __shfl_sync(0xffffffffu, si - s1, SLn); // cumulative through slice 2*SLn
+                const int slice = before >= need ? 2 * SLn : 2 * SLn + 1;
+                // slice(d2) <= slice for every d2 below this value (and a little beyond: harmless)
+                edge = fminf(edge, __fmaf_rn((float)(slice + 1), w, lo) * 1.000002f);
+            }
+        }
+    }
     const float delta = 4.0f * sqrtf(edge) * e1 + 4.0f * e1 * e1 + 1e-6f * edge;
     const float thr = (edge + 3.0f * delta) * 1.000001f;
     bool live = st == PCP_FK_OK;
