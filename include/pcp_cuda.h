@@ -98,6 +98,17 @@ PCP_API int pcp_host_free_pinned(pcp_ctx* ctx, void* hptr);
 PCP_API int pcp_memcpy(pcp_ctx* ctx, void* dst, const void* src, size_t bytes); /* any direction, synchronous */
 /* Same, ordered on the context's stream without waiting (host memory should be pinned to overlap). */
 PCP_API int pcp_memcpy_async(pcp_ctx* ctx, void* dst, const void* src, size_t bytes);
+/* Copy lanes: PCP_COPY_LANES extra streams for host<->device copies that overlap the context's compute stream
+ * (upload the next cloud and download the previous results while the current one is processed).
+ *   pcp_copy_async  the copy starts once the work submitted to the context SO FAR has finished (so it may read a
+ *                   result buffer, or overwrite an input buffer, of an earlier call); returns at once.
+ *   pcp_copy_fence  work submitted to the context from now on waits for the copies enqueued on the lane so far.
+ *   pcp_copy_wait   the calling thread waits for the copies enqueued on the lane so far.
+ * Host memory must be pinned (pcp_host_alloc_pinned) for the copy to overlap. */
+#define PCP_COPY_LANES 4
+PCP_API int pcp_copy_async(pcp_ctx* ctx, int lane, void* dst, const void* src, size_t bytes);
+PCP_API int pcp_copy_fence(pcp_ctx* ctx, int lane);
+PCP_API int pcp_copy_wait(pcp_ctx* ctx, int lane);
 
 /* ---- search structure ------------------------------------------------------------------------------
  * Replaces KdTreeFLANN<PointT>::setInputCloud + convertCloudToArray (kd_tree.h:772-798, 928-956):

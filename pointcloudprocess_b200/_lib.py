@@ -11,6 +11,7 @@ SYMBOLS = [
     "pcp_create", "pcp_destroy", "pcp_last_error", "pcp_set_stream", "pcp_synchronize", "pcp_device_count",
     "pcp_version", "pcp_trim", "pcp_profile_enable", "pcp_profile_reset", "pcp_profile_get", "pcp_launch_count",
     "pcp_dev_alloc", "pcp_dev_free", "pcp_host_alloc_pinned", "pcp_host_free_pinned", "pcp_memcpy", "pcp_memcpy_async",
+    "pcp_copy_async", "pcp_copy_fence", "pcp_copy_wait",
     "pcp_index_build", "pcp_index_free", "pcp_index_size", "pcp_index_cell_size", "pcp_knn", "pcp_radius_count",
     "pcp_radius_fill", "pcp_features_knn", "pcp_features_radius", "pcp_plane_fit", "pcp_voxel_grid",
     "pcp_remove_duplicate", "pcp_features_knn_ex", "pcp_remove_duplicate_centred", "pcp_serial_sum",
@@ -61,6 +62,9 @@ def load():
         "pcp_host_free_pinned": (i32, [vp, vp]),
         "pcp_memcpy": (i32, [vp, vp, vp, sz]),
         "pcp_memcpy_async": (i32, [vp, vp, vp, sz]),
+        "pcp_copy_async": (i32, [vp, i32, vp, vp, sz]),
+        "pcp_copy_fence": (i32, [vp, i32]),
+        "pcp_copy_wait": (i32, [vp, i32]),
         "pcp_index_build": (i32, [vp, vp, sz, sz, dbl, pp]),
         "pcp_index_free": (None, [vp]),
         "pcp_index_size": (i64, [vp]),

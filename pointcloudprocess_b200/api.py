@@ -141,6 +141,16 @@ class Context:
     def memcpy_async(self, dst, src, nbytes):
         self._check(self.L.pcp_memcpy_async(self.h, _ptr(dst), _ptr(src), int(nbytes)))
 
+    # copy lanes (pcp_copy_async ...): host<->device copies that overlap the compute stream
+    def copy_async(self, lane, dst, src, nbytes):
+        self._check(self.L.pcp_copy_async(self.h, int(lane), _ptr(dst), _ptr(src), int(nbytes)))
+
+    def copy_fence(self, lane):
+        self._check(self.L.pcp_copy_fence(self.h, int(lane)))
+
+    def copy_wait(self, lane):
+        self._check(self.L.pcp_copy_wait(self.h, int(lane)))
+
     def alloc(self, nbytes):
         return DeviceArray(self, nbytes)
 

@@ -38,9 +38,19 @@ struct pcp_ctx {
     };
     std::vector<pending_ev> pending;
     std::vector<cudaEvent_t> ev_free;
+    // copy lanes (pcp_copy_async): streams created on first use, one reusable event per direction
+    void* rb_host = nullptr; // mapped pinned scratch of pcp_readback
+    cudaStream_t lane[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t lane_in[4] = {nullptr, nullptr, nullptr, nullptr};  // compute -> lane
+    cudaEvent_t lane_out[4] = {nullptr, nullptr, nullptr, nullptr}; // lane -> compute
 };
 
 int pcp_fail(pcp_ctx* ctx, int code, const char* fmt, ...);
+// A few bytes from device memory to the host, ordered on the context's stream, and a wait for them.  A kernel
+// writes them into mapped host memory: a cudaMemcpy would queue behind whatever bulk download a copy lane
+// has in flight on the device-to-host copy engine (pcp_copy_async).
+#define PCP_READBACK_MAX 1024
+int pcp_readback(pcp_ctx* ctx, void* host_dst, const void* dev_src, size_t bytes);
 void pcp_set_global_error(const char* msg);
 
 #define PCP_CUDA_TRY(ctx, expr)                                                                              \

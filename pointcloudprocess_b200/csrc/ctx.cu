@@ -1,5 +1,7 @@
 // ctx.cu -- context lifecycle, arena, staging, stage timing, raw memory helpers (include/pcp_cuda.h).
 #include "common.cuh"
+#include <cstring>
+#include <algorithm>
 #include <cstdarg>
 
 static thread_local std::string g_last_error;
@@ -204,6 +206,14 @@ void pcp_destroy(pcp_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     pcp_profile_resolve(ctx);
     for (auto e : ctx->ev_free) cudaEventDestroy(e);
+    for (int l = 0; l < PCP_COPY_LANES; l++) {
+        if (!ctx->lane[l]) continue;
+        cudaStreamSynchronize(ctx->lane[l]);
+        cudaStreamDestroy(ctx->lane[l]);
+        cudaEventDestroy(ctx->lane_in[l]);
+        cudaEventDestroy(ctx->lane_out[l]);
+    }
+    if (ctx->rb_host) cudaFreeHost(ctx->rb_host);
     if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
@@ -310,6 +320,85 @@ int pcp_memcpy_async(pcp_ctx* ctx, void* dst, const void* src, size_t bytes)
     if (!ctx) return PCP_ERR_INVALID;
     if (!bytes) return PCP_OK;
     PCP_CUDA_TRY(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, ctx->stream));
+    return PCP_OK;
+}
+
+static __global__ void readback_kernel(unsigned char* __restrict__ dst, const unsigned char* __restrict__ src, unsigned bytes)
+{
+    for (unsigned i = threadIdx.x; i < bytes; i += blockDim.x) dst[i] = src[i];
+}
+
+} // extern "C"
+
+int pcp_readback(pcp_ctx* ctx, void* host_dst, const void* dev_src, size_t bytes)
+{
+    if (!bytes) return PCP_OK;
+    if (bytes > PCP_READBACK_MAX) {
+        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+        PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+        return PCP_OK;
+    }
+    if (!ctx->rb_host) PCP_CUDA_TRY(ctx, cudaHostAlloc(&ctx->rb_host, PCP_READBACK_MAX, cudaHostAllocMapped));
+    void* dalias = nullptr;
+    PCP_CUDA_TRY(ctx, cudaHostGetDevicePointer(&dalias, ctx->rb_host, 0));
+    readback_kernel<<<1, 128, 0, ctx->stream>>>(static_cast<unsigned char*>(dalias), static_cast<const unsigned char*>(dev_src),
+                                                (unsigned)bytes);
+    PCP_CUDA_TRY(ctx, cudaGetLastError());
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    memcpy(host_dst, ctx->rb_host, bytes);
+    return PCP_OK;
+}
+
+extern "C" {
+
+static int lane_open(pcp_ctx* ctx, int lane)
+{
+    if (lane < 0 || lane >= PCP_COPY_LANES) return pcp_fail(ctx, PCP_ERR_INVALID, "copy lane %d out of range", lane);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (!ctx->lane[lane]) {
+        PCP_CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->lane[lane], cudaStreamNonBlocking));
+        PCP_CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->lane_in[lane], cudaEventDisableTiming));
+        PCP_CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->lane_out[lane], cudaEventDisableTiming));
+    }
+    return PCP_OK;
+}
+
+int pcp_copy_async(pcp_ctx* ctx, int lane, void* dst, const void* src, size_t bytes)
+{
+    if (!ctx || (bytes && (!dst || !src))) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_copy_async: bad argument");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    PCP_TRY(lane_open(ctx, lane));
+    PCP_CUDA_TRY(ctx, cudaEventRecord(ctx->lane_in[lane], ctx->stream));
+    PCP_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->lane[lane], ctx->lane_in[lane], 0));
+    // In pieces: a copy engine serves one copy at a time, and the few-byte read-backs of the compute stream
+    // (counts, cell totals) must not queue behind a gigabyte transfer.
+    const size_t piece = (size_t)4 << 20;
+    for (size_t off = 0; off < bytes; off += piece)
+        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(static_cast<char*>(dst) + off, static_cast<const char*>(src) + off,
+                                          std::min(piece, bytes - off), cudaMemcpyDefault, ctx->lane[lane]));
+    return PCP_OK;
+}
+
+int pcp_copy_fence(pcp_ctx* ctx, int lane)
+{
+    if (!ctx) return PCP_ERR_INVALID;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    PCP_TRY(lane_open(ctx, lane));
+    PCP_CUDA_TRY(ctx, cudaEventRecord(ctx->lane_out[lane], ctx->lane[lane]));
+    PCP_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->lane_out[lane], 0));
+    return PCP_OK;
+}
+
+int pcp_copy_wait(pcp_ctx* ctx, int lane)
+{
+    if (!ctx) return PCP_ERR_INVALID;
+    cudaStream_t s = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(ctx->mu);
+        PCP_TRY(lane_open(ctx, lane));
+        s = ctx->lane[lane];
+    }
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(s));
     return PCP_OK;
 }
 

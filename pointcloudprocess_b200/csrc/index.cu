@@ -317,7 +317,7 @@ int pcp_index_build_items(pcp_ctx* ctx, pcp_index* ix, uint32_t cmax)
     ctx->launches++;
     PCP_CUDA_TRY(ctx, cudaGetLastError());
     uint32_t ni = 0;
-    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(&ni, cnt.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_TRY(pcp_readback(ctx, &ni, cnt.p, 4));
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     ix->nitem = ni;
     ix->item_cmax = cmax;
@@ -411,8 +411,8 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
             IX_TRY(pcp_exclusive_scan_u32(ctx, flag.p, scan.p, nv));
             // ncell = scan[nv-1] + flag[nv-1]
             uint32_t tail[2];
-            IX_CUDA(cudaMemcpyAsync(&tail[0], scan.p + (nv - 1), 4, cudaMemcpyDeviceToHost, ctx->stream));
-            IX_CUDA(cudaMemcpyAsync(&tail[1], flag.p + (nv - 1), 4, cudaMemcpyDeviceToHost, ctx->stream));
+            IX_TRY(pcp_readback(ctx, &tail[0], scan.p + (nv - 1), 4));
+            IX_TRY(pcp_readback(ctx, &tail[1], flag.p + (nv - 1), 4));
             IX_CUDA(cudaStreamSynchronize(ctx->stream));
             ncell = tail[0] + tail[1];
         }
@@ -440,7 +440,7 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
         occupancy_kernel<<<ctx->sm_count * 4, 256, 0, ctx->stream>>>(ix->cstart, ncell, bins.p);
         ctx->launches++;
         IX_CUDA(cudaGetLastError());
-        IX_CUDA(cudaMemcpyAsync(hb, bins.p, 32 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        IX_TRY(pcp_readback(ctx, hb, bins.p, 32 * 8));
         IX_CUDA(cudaStreamSynchronize(ctx->stream));
         unsigned long long acc = 0;
         int mb = 0;
@@ -505,7 +505,7 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
         ctx->launches++;
         IX_CUDA(cudaGetLastError());
         unsigned long long ne = 0;
-        IX_CUDA(cudaMemcpyAsync(&ne, tot.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        IX_TRY(pcp_readback(ctx, &ne, tot.p, 8));
         IX_CUDA(cudaStreamSynchronize(ctx->stream));
         uint32_t cap = 64;
         while ((unsigned long long)cap < 2ull * ne && cap < 0x80000000u) cap <<= 1;

@@ -175,6 +175,7 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
             P.work_counter = counters.p + 2;
             P.dbg = nullptr;
             DevBuf<unsigned long long> dbg;
+            unsigned long long hfast6 = 0, hfast7 = 0;
             const bool want_dbg = getenv("PCP_KNN_DEBUG") != nullptr;
             if (want_dbg) {
                 PCP_TRY(dbg.alloc(ctx, 24));
@@ -187,8 +188,9 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
             }
             if (want_dbg) {
                 unsigned long long h[16];
-                PCP_CUDA_TRY(ctx, cudaMemcpyAsync(h, dbg.p, 16 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+                PCP_TRY(pcp_readback(ctx, h, dbg.p, 16 * 8));
                 PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+                hfast6 = h[6], hfast7 = h[7];
                 fprintf(stderr, "[pcp knn] h=%.4f items=%llu staged=%llu queries=%llu cand/item=%.1f settled=%llu beyond=%llu "
                                 "ambiguous=%llu too_dense: items=%llu queries=%llu too_sparse queries=%llu\n", ix->grid.h,
                         h[0], h[1], h[2], h[0] ? (double)h[3] / h[0] : 0.0, h[5], h[6], h[7], h[4], h[8], h[9]);
@@ -206,17 +208,18 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 PCP_TRY(launch_far(ctx, P, A));
             }
             uint32_t hc[5];
-            PCP_CUDA_TRY(ctx, cudaMemcpyAsync(hc, counters.p, 20, cudaMemcpyDeviceToHost, ctx->stream));
+            PCP_TRY(pcp_readback(ctx, hc, counters.p, 20));
             PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
             nfail = hc[4];
             if (want_dbg) {
                 unsigned long long h[24];
-                PCP_CUDA_TRY(ctx, cudaMemcpyAsync(h, dbg.p, 24 * 8, cudaMemcpyDeviceToHost, ctx->stream));
+                PCP_TRY(pcp_readback(ctx, h, dbg.p, 24 * 8));
                 PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
                 fprintf(stderr, "[pcp knn] far queries=%u attempts=%llu (block too sparse %llu) cells/attempt=%.1f searches=%llu "
                                 "cand/search=%.1f selected cells/search=%.1f uncertified=%llu tightened=%llu streaming-kernel queries=%u\n",
                         hc[0], h[10], h[16], h[10] ? (double)h[11] / h[10] : 0.0, h[12], h[12] ? (double)h[13] / h[12] : 0.0,
                         h[12] ? (double)h[14] / h[12] : 0.0, h[15], h[17], hc[4]);
+                fprintf(stderr, "[pcp knn] far searches with bound >= certified radius: %llu, of which certified anyway %llu\n", h[6] - hfast6, h[7] - hfast7);
                 fprintf(stderr, "[pcp knn] far failures: overflow=%llu (cells %llu) beyond=%llu uncert=%llu no-bound=%llu mean level=%.2f\n",
                         h[18], h[23], h[19], h[20], h[21], hc[4] ? (double)h[22] / hc[4] : 0.0);
             }

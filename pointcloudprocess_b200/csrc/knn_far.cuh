@@ -358,6 +358,8 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
                 continue;
             }
             PCP_FK_DBG(15, st == PCP_FK_UNCERT);
+            PCP_FK_DBG(6, !((double)Ueff < g2));
+            PCP_FK_DBG(7, !((double)Ueff < g2) && st == PCP_FK_OK);
             if (st == PCP_FK_OK) U = __double2float_ru(dk);
             if (st == PCP_FK_OK || st == PCP_FK_OVERFLOW) break;
             if (st == PCP_FK_UNCERT) U = __double2float_ru(dk) * 1.000001f; // exact k-th of the scanned set: a true bound

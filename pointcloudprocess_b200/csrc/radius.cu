@@ -296,7 +296,7 @@ extern "C" int pcp_radius_fill(const pcp_index* ix, const void* q, size_t nq, si
     PCP_TRY(radius_counts(ctx, P, cnt.p));
     PCP_TRY(pcp_exclusive_scan_u64(ctx, cnt.p, foff.p, nq + 1));
     unsigned long long total = 0;
-    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(&total, foff.p + nq, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_TRY(pcp_readback(ctx, &total, foff.p + nq, 8));
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     if (total == 0) return PCP_OK;
     if (total > 0x7fffffffull) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_radius_fill: more than 2^31-1 neighbours in one call");
@@ -335,7 +335,7 @@ extern "C" int pcp_radius_fill(const pcp_index* ix, const void* q, size_t nq, si
         OutStage oi, od;
         // user lists are addressed through the user's (capped) offsets
         long long utotal = 0;
-        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(&utotal, (const long long*)uoff.dptr + nq, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        PCP_TRY(pcp_readback(ctx, &utotal, (const long long*)uoff.dptr + nq, 8));
         PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
         PCP_TRY(oi.open(ctx, idx, (size_t)utotal * 4));
         PCP_TRY(od.open(ctx, d2, (size_t)utotal * 8));

@@ -105,7 +105,7 @@ int pcp_bbox_host(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, pcp_b
     DevBuf<pcp_bbox> d;
     PCP_TRY(d.alloc(ctx, 1));
     PCP_TRY(pcp_bbox_device(ctx, dpts, n, stride, d.p));
-    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(h_out, d.p, sizeof(pcp_bbox), cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_TRY(pcp_readback(ctx, h_out, d.p, sizeof(pcp_bbox)));
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return PCP_OK;
 }

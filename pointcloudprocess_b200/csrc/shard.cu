@@ -96,7 +96,7 @@ extern "C" int pcp_serial_sum(pcp_ctx* ctx, const void* pts, size_t n, size_t st
     PCP_TRY(pcp_serial_sum_device(ctx, in.dptr, n, stride, s3.p, 1));
     pcp_bbox bb;
     PCP_TRY(pcp_bbox_host(ctx, in.dptr, n, stride, &bb));
-    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(sum3, s3.p, 24, cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_TRY(pcp_readback(ctx, sum3, s3.p, 24));
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     if (count) *count += bb.count;
     return PCP_OK;
@@ -146,7 +146,7 @@ static int select_impl(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, c
                                                                         scan.p, static_cast<char*>(o.dptr), md.p);
     PCP_LAUNCH_CHECK(ctx);
     uint32_t mh = 0;
-    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(&mh, md.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_TRY(pcp_readback(ctx, &mh, md.p, 4));
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     *m = mh;
     PCP_TRY(o.commit((size_t)mh * stride));

@@ -263,7 +263,7 @@ int pcp_voxel_grid_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t strid
         PCP_LAUNCH_CHECK(ctx);
     }
     uint32_t m = 0;
-    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(&m, m_dev.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_TRY(pcp_readback(ctx, &m, m_dev.p, 4));
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     *m_host = m;
     return PCP_OK;
@@ -308,7 +308,7 @@ extern "C" int pcp_centroid(pcp_ctx* ctx, const void* pts, size_t n, size_t stri
     PCP_TRY(pcp_serial_sum_device(ctx, in.dptr, n, stride, s3.p));
     PCP_TRY(pcp_bbox_host(ctx, in.dptr, n, stride, &bb));
     double h[3];
-    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(h, s3.p, 24, cudaMemcpyDeviceToHost, ctx->stream));
+    PCP_TRY(pcp_readback(ctx, h, s3.p, 24));
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     double dn = (double)bb.count;
     for (int d = 0; d < 3; d++) c[d] = bb.count ? h[d] / dn : 0.0;

@@ -327,36 +327,64 @@ class ShardedPipeline:
         return m
 
     # ---- end to end: host buffers through the C ABI ----
-    def time_e2e(self, steps, barrier):
+    def time_e2e(self, steps, barrier, sync, keep=None):
         """Times `steps` passes whose input cloud starts in pinned HOST memory and whose LAS_POINT_PROPERTY
-        records end in pinned HOST memory.  Returns (ms_per_step, h2d_bytes, d2h_bytes, featured per step)."""
+        records end in pinned HOST memory, every byte moved through the C ABI inside the timed region.  The
+        passes are pipelined over the library's copy lanes (pcp_copy_async): while pass i is processed, the
+        cloud of pass i+1 is uploaded and the records of pass i-1 are downloaded, each pass with its own device
+        and host buffers.  Wall clock around all of it (fill and drain included), barrier + device
+        synchronisation on both sides.  Returns (ms_per_step, h2d_bytes, d2h_bytes, featured per step).
+        keep: optional list that receives a copy of the host records of the last two passes (tests)."""
         import time
-        ctx, torch = self.ctx, self.torch
-        host_in, pin_in = ctx.pinned(self.n * 48)
-        host_props, pin_props = ctx.pinned(self.n * 48)
-        ctx.memcpy(pin_in, self._p(self.cloud), self.n * 48)
-        ctx.synchronize()
-        t_ms, feat, d2h = [], 0, 0
-        for it in range(steps + 1):
+        ctx = self.ctx
+        nb = self.n * 48
+        host_in, pin_in = ctx.pinned(nb)
+        pins = [ctx.pinned(self.cap * 48) for _ in range(2)]
+        dev_in = [self._alloc(nb) for _ in range(2)]
+        props = [self.props, self._alloc(self.cap * 48)]
+        ctx.memcpy(pin_in, self._p(self.cloud), nb)
+        UP, DOWN = 0, (1, 2)
+
+        def run(nsteps):
+            feat = d2h = 0
+            ctx.copy_async(UP, self._p(dev_in[0]), pin_in, nb)
+            for i in range(nsteps):
+                b = i & 1
+                ctx.copy_fence(UP)            # pass i reads dev_in[b]: wait for its upload
+                ctx.copy_fence(DOWN[b])       # ... and writes props[b]: wait for the download of pass i-2
+                if i + 1 < nsteps:            # dev_in[1-b] was last read by pass i-1, already submitted
+                    ctx.copy_async(UP, self._p(dev_in[1 - b]), pin_in, nb)
+                self.props = props[b]
+                gen = self._step_gen(self._p(dev_in[b]))
+                m = self._run(gen) if self.world > 1 else self._drain(gen)
+                ctx.copy_async(DOWN[b], pins[b][1], self._p(props[b]), m * 48)
+                feat += m
+                d2h = m * 48
+            ctx.copy_wait(DOWN[0])
+            ctx.copy_wait(DOWN[1])
+            return feat, d2h
+
+        try:
+            run(2)  # warms the arena, the lanes and both buffer sets
+            sync()
             barrier()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            stream = torch.cuda.current_stream()
             t0 = time.perf_counter()
-            e0.record(stream)
-            m = self._run(self._step_gen(pin_in)) if self.world > 1 else self._drain(self._step_gen(pin_in))
-            ctx.memcpy(pin_props, self._p(self.props), m * 48)
-            e1.record(stream)
+            feat, d2h = run(steps)
+            sync()
             barrier()
-            wall = (time.perf_counter() - t0) * 1e3
-            if it == 0:
-                continue  # first pass warms the staging arena
-            # host-side work (ctypes calls, synchronisations) sits between the events: take the larger clock
-            t_ms.append(max(e0.elapsed_time(e1), wall))
-            feat += m
-            d2h = m * 48
-        ctx.free_pinned(pin_in)
-        ctx.free_pinned(pin_props)
-        return sum(t_ms) / len(t_ms), self.n * 48, d2h, feat / len(t_ms)
+            ms = (time.perf_counter() - t0) * 1e3 / steps
+            if keep is not None:
+                keep.extend(pins[b][0][:d2h].copy() for b in ((steps - 1) & 1, steps & 1)[:min(steps, 2)])
+        finally:
+            self.props = props[0]
+            ctx.synchronize()
+            ctx.free_pinned(pin_in)
+            for _, p in pins:
+                ctx.free_pinned(p)
+            for a in dev_in + [props[1]]:
+                if hasattr(a, "free"):
+                    a.free()
+        return ms, nb, d2h, feat / steps
 
     @staticmethod
     def _drain(gen):
