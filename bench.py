@@ -225,7 +225,10 @@ def run_gpu(args):
     ctx.set_stream(stream.cuda_stream)
 
     n_shard = args.points
-    comm = sharded.DistComm(dist, torch, rank, world, torch.device("cuda", local)) if world > 1 else None
+    comm = None
+    if world > 1:  # payloads over NCCL, message sizes host to host over gloo
+        comm = sharded.DistComm(dist, torch, rank, world, torch.device("cuda", local),
+                                host_group=dist.new_group(backend="gloo"))
     job = sharded.ShardedPipeline(ctx, rank, world, n_shard, seed=5, leaf=LEAF, k=K, comm=comm, torch=torch)
     job.generate()  # this rank's spatial shard, resident in HBM (untimed)
 

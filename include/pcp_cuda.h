@@ -194,6 +194,14 @@ PCP_API int pcp_select_range(pcp_ctx* ctx, const void* pts, size_t n, size_t str
                              void* out_pts, size_t* m);
 PCP_API int pcp_select_columns(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, int axis, float leaf,
                                double centre, int32_t min_b, int32_t col_lo, int32_t col_hi, void* out_pts, size_t* m);
+/* The queries of a shard whose k-th neighbour may lie beyond the halo the shard received: point i of the first m
+ * is selected when kth_d2[i] (pcp_features_knn_ex) >= reach^2, reach = coordinate - lo (has_lo) or hi - coordinate
+ * (has_hi), lo / hi being the outer faces of the halo along `axis`.  Writes the selected indices (ascending) and
+ * their coordinates (3 doubles each), at most `cap`; *count receives the number selected (PCP_ERR_RANGE when it
+ * exceeds cap: call again with more room). */
+PCP_API int pcp_select_boundary(pcp_ctx* ctx, const void* pts, size_t m, size_t stride, int axis, const float* kth_d2,
+                                int has_lo, double lo, int has_hi, double hi, size_t cap, int32_t* out_idx,
+                                double* out_xyz, size_t* count);
 /* Exact features of queries whose neighbourhood spans shards: list l (of nlists <= 4) holds, for each of the nq
  * queries, k candidate neighbours sorted by squared distance (xyz_lists [nlists][nq][k][3], d2_lists
  * [nlists][nq][k], +inf padded).  The k nearest distinct candidates are merged and fitted

@@ -15,7 +15,7 @@ SYMBOLS = [
     "pcp_index_build", "pcp_index_free", "pcp_index_size", "pcp_index_cell_size", "pcp_knn", "pcp_radius_count",
     "pcp_radius_fill", "pcp_features_knn", "pcp_features_radius", "pcp_plane_fit", "pcp_voxel_grid",
     "pcp_remove_duplicate", "pcp_features_knn_ex", "pcp_remove_duplicate_centred", "pcp_serial_sum",
-    "pcp_column_histogram", "pcp_select_range", "pcp_select_columns", "pcp_features_merge", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
+    "pcp_column_histogram", "pcp_select_range", "pcp_select_columns", "pcp_select_boundary", "pcp_features_merge", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
 ]
 
 
@@ -83,6 +83,7 @@ def load():
         "pcp_column_histogram": (i32, [vp, vp, sz, sz, i32, C.c_float, dbl, i32, i32, i32, i32, vp]),
         "pcp_select_range": (i32, [vp, vp, sz, sz, i32, dbl, dbl, vp, C.POINTER(sz)]),
         "pcp_select_columns": (i32, [vp, vp, sz, sz, i32, C.c_float, dbl, i32, i32, i32, vp, C.POINTER(sz)]),
+        "pcp_select_boundary": (i32, [vp, vp, sz, sz, i32, vp, i32, dbl, i32, dbl, sz, vp, vp, C.POINTER(sz)]),
         "pcp_features_merge": (i32, [vp, sz, i32, i32, vp, vp, vp, vp, vp, vp]),
         "pcp_centroid": (i32, [vp, vp, sz, sz, vp, C.POINTER(u64)]),
         "pcp_minmax": (i32, [vp, vp, sz, sz, vp, vp]),

@@ -261,6 +261,19 @@ class Context:
         self._check(self.L.pcp_select_range(self.h, p, n, s, axis, float(lo), float(hi), _ptr(out), C.byref(m)))
         return m.value
 
+    def select_boundary(self, cloud, axis, kth_d2, lo, hi, cap, out_idx, out_xyz):
+        """lo / hi: outer halo faces or None.  Returns the number selected, or minus that number when it exceeds
+        cap (nothing usable was written: call again with more room)."""
+        p, n, s, keep = _pts(cloud)
+        c = C.c_size_t(0)
+        st = self.L.pcp_select_boundary(self.h, p, n, s, axis, _ptr(kth_d2), int(lo is not None), float(lo or 0.0),
+                                        int(hi is not None), float(hi or 0.0), int(cap), _ptr(out_idx), _ptr(out_xyz),
+                                        C.byref(c))
+        if st == -4 and c.value > cap:
+            return -int(c.value)  # not enough room: the caller grows its buffers and calls again
+        self._check(st)
+        return c.value
+
     def select_columns(self, cloud, axis, leaf, centre, min_b, col_lo, col_hi, out):
         p, n, s, keep = _pts(cloud)
         m = C.c_size_t(0)

@@ -175,6 +175,89 @@ extern "C" int pcp_select_columns(pcp_ctx* ctx, const void* pts, size_t n, size_
     return select_impl(ctx, pts, n, stride, P, out_pts, m);
 }
 
+// ---- queries whose k-th neighbour may lie beyond the halo ----------------------------------------------------------
+namespace {
+
+__global__ void __launch_bounds__(256) bnd_flag_kernel(const char* __restrict__ pts, size_t m, size_t stride, int axis,
+                                                       const float* __restrict__ kth, int has_lo, double lo, int has_hi,
+                                                       double hi, uint32_t* __restrict__ flag)
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const double v = reinterpret_cast<const double*>(pts + i * stride)[axis];
+    const double kd = (double)kth[i];
+    bool f = false;
+    if (has_lo) {
+        const double reach = __dsub_rn(v, lo);
+        f |= kd >= __dmul_rn(reach, reach);
+    }
+    if (has_hi) {
+        const double reach = __dsub_rn(hi, v);
+        f |= kd >= __dmul_rn(reach, reach);
+    }
+    flag[i] = f ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(256) bnd_scatter_kernel(const char* __restrict__ pts, size_t m, size_t stride,
+                                                          const uint32_t* __restrict__ flag,
+                                                          const uint32_t* __restrict__ scan, size_t cap,
+                                                          int32_t* __restrict__ out_idx, double* __restrict__ out_xyz,
+                                                          uint32_t* __restrict__ count)
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    if (flag[i] && scan[i] < cap) {
+        const double* p = reinterpret_cast<const double*>(pts + i * stride);
+        out_idx[scan[i]] = (int32_t)i;
+        out_xyz[3 * (size_t)scan[i] + 0] = p[0];
+        out_xyz[3 * (size_t)scan[i] + 1] = p[1];
+        out_xyz[3 * (size_t)scan[i] + 2] = p[2];
+    }
+    if (i == m - 1) *count = scan[i] + flag[i];
+}
+
+} // namespace
+
+extern "C" int pcp_select_boundary(pcp_ctx* ctx, const void* pts, size_t m, size_t stride, int axis, const float* kth_d2,
+                                   int has_lo, double lo, int has_hi, double hi, size_t cap, int32_t* out_idx,
+                                   double* out_xyz, size_t* count)
+{
+    if (!ctx || !count || stride < 24 || (stride & 7) || axis < 0 || axis > 2 || (m && (!pts || !kth_d2)) ||
+        (cap && (!out_idx || !out_xyz)))
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_select_boundary: bad argument");
+    *count = 0;
+    if (m == 0 || (!has_lo && !has_hi)) return PCP_OK;
+    if (m > 0x7ffffff0ull) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_select_boundary: too many points");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    InStage in, kin;
+    OutStage oi, ox;
+    PCP_TRY(in.open(ctx, pts, m * stride));
+    PCP_TRY(kin.open(ctx, kth_d2, m * 4));
+    PCP_TRY(oi.open(ctx, out_idx, cap * 4));
+    PCP_TRY(ox.open(ctx, out_xyz, cap * 24));
+    DevBuf<uint32_t> flag, scan, cd;
+    PCP_TRY(flag.alloc(ctx, m));
+    PCP_TRY(scan.alloc(ctx, m));
+    PCP_TRY(cd.alloc(ctx, 1));
+    bnd_flag_kernel<<<pcp_blocks_for(m, 256), 256, 0, ctx->stream>>>(static_cast<const char*>(in.dptr), m, stride, axis,
+                                                                     static_cast<const float*>(kin.dptr), has_lo, lo, has_hi,
+                                                                     hi, flag.p);
+    PCP_LAUNCH_CHECK(ctx);
+    PCP_TRY(pcp_exclusive_scan_u32(ctx, flag.p, scan.p, m));
+    bnd_scatter_kernel<<<pcp_blocks_for(m, 256), 256, 0, ctx->stream>>>(static_cast<const char*>(in.dptr), m, stride, flag.p,
+                                                                        scan.p, cap, static_cast<int32_t*>(oi.dptr),
+                                                                        static_cast<double*>(ox.dptr), cd.p);
+    PCP_LAUNCH_CHECK(ctx);
+    uint32_t c = 0;
+    PCP_TRY(pcp_readback(ctx, &c, cd.p, 4));
+    *count = c;
+    if (c > cap) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_select_boundary: %u queries selected, room for %zu", c, cap);
+    PCP_TRY(oi.commit((size_t)c * 4));
+    PCP_TRY(ox.commit((size_t)c * 24));
+    return PCP_OK;
+}
+
 // ---- exact merge of per-shard neighbour candidates -------------------------------------------------------------
 namespace {
 

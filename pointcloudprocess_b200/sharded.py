@@ -82,8 +82,11 @@ def make_plan(ctx, chunks, world, leaf, halo):
 class DistComm:
     """Neighbour exchange over torch.distributed (NCCL on GPUs, gloo in CPU tests)."""
 
-    def __init__(self, dist, torch, rank, world, device):
+    def __init__(self, dist, torch, rank, world, device, host_group=None):
+        """host_group: optional gloo group for the message sizes, so that they travel host to host instead of
+        through device memory (a device-to-host read would queue behind a bulk download on the copy engine)."""
         self.dist, self.torch, self.rank, self.world, self.device = dist, torch, rank, world, device
+        self.host_group = host_group
 
     def exchange(self, send_l, send_r):
         """send_l / send_r: uint8 tensors for ranks rank-1 / rank+1 (None or empty allowed).
@@ -93,14 +96,16 @@ class DistComm:
         send_l = empty if send_l is None else send_l
         send_r = empty if send_r is None else send_r
         has_l, has_r = self.rank > 0, self.rank < self.world - 1
-        sz_out = [t.tensor([send_l.numel()], dtype=t.int64, device=self.device),
-                  t.tensor([send_r.numel()], dtype=t.int64, device=self.device)]
-        sz_in = [t.zeros(1, dtype=t.int64, device=self.device), t.zeros(1, dtype=t.int64, device=self.device)]
+        sdev = "cpu" if self.host_group is not None else self.device
+        grp = self.host_group
+        sz_out = [t.tensor([send_l.numel()], dtype=t.int64, device=sdev),
+                  t.tensor([send_r.numel()], dtype=t.int64, device=sdev)]
+        sz_in = [t.zeros(1, dtype=t.int64, device=sdev), t.zeros(1, dtype=t.int64, device=sdev)]
         ops = []
         if has_l:
-            ops += [d.P2POp(d.isend, sz_out[0], self.rank - 1), d.P2POp(d.irecv, sz_in[0], self.rank - 1)]
+            ops += [d.P2POp(d.isend, sz_out[0], self.rank - 1, grp), d.P2POp(d.irecv, sz_in[0], self.rank - 1, grp)]
         if has_r:
-            ops += [d.P2POp(d.isend, sz_out[1], self.rank + 1), d.P2POp(d.irecv, sz_in[1], self.rank + 1)]
+            ops += [d.P2POp(d.isend, sz_out[1], self.rank + 1, grp), d.P2POp(d.irecv, sz_in[1], self.rank + 1, grp)]
         if ops:
             for w in d.batch_isend_irecv(ops):
                 w.wait()
@@ -164,6 +169,7 @@ class ShardedPipeline:
         self.cap = 0
         self.stats = {}
         self.last_m = 0
+        self.bnd_cap, self.bnd_idx, self.bnd_xyz = 1 << 16, None, None  # boundary queries (grown on demand)
 
     # ---- buffers: torch tensors when torch is given (needed for the exchanges), library allocations otherwise ----
     def _alloc(self, nbytes):
@@ -274,18 +280,18 @@ class ShardedPipeline:
                             kth_d2=self._p(self.kth))
             # ---- queries whose k-th neighbour may lie beyond the halo ----
             pts = self.work[:ntot * 48].view(t.float64).view(ntot, 6)
-            x = pts[:m, 0]
-            kth = self.kth[:m * 4].view(t.float32).to(t.float64)
-            flag = t.zeros(m, dtype=t.bool, device="cuda")
-            if has_l:
-                reach = x - (xlo - H)
-                flag |= kth >= reach * reach
-            if has_r:
-                reach = (xhi + H) - x
-                flag |= kth >= reach * reach
-            F = t.nonzero(flag).view(-1)
-            nF = int(F.numel())
-            qF = pts[F, :3].contiguous()
+            while True:
+                if self.bnd_idx is None or self.bnd_idx.numel() < self.bnd_cap:
+                    self.bnd_idx = t.empty(self.bnd_cap, dtype=t.int32, device="cuda")
+                    self.bnd_xyz = t.empty((self.bnd_cap, 3), dtype=t.float64, device="cuda")
+                nF = ctx.select_boundary((wp, m, 48), 0, self._p(self.kth), (xlo - H) if has_l else None,
+                                         (xhi + H) if has_r else None, self.bnd_cap, self.bnd_idx.data_ptr(),
+                                         self.bnd_xyz.data_ptr())
+                if nF >= 0:
+                    break
+                self.bnd_cap = -nF + (-nF) // 4
+            F = self.bnd_idx[:nF]
+            qF = self.bnd_xyz[:nF]
             qbytes = qF.view(t.uint8).view(-1)
             # ---- exchange 2: the flagged queries go to both neighbours ----
             q_l, q_r = yield (qbytes if has_l else None, qbytes if has_r else None)
@@ -316,7 +322,7 @@ class ShardedPipeline:
                     xyz_lists.append(a[:nF * k * 24].contiguous().view(t.float64))
                     d2_lists.append(a[nF * k * 24:].contiguous().view(t.float64))
                 nlists = len(xyz_lists)
-                xyz_all, d2_all, pid = t.cat(xyz_lists), t.cat(d2_lists), F.to(t.int32)
+                xyz_all, d2_all, pid = t.cat(xyz_lists), t.cat(d2_lists), F
                 ctx.features_merge(nF, k, nlists, xyz_all.data_ptr(), d2_all.data_ptr(), pid.data_ptr(),
                                    self._p(self.props))
                 del xyz_all, d2_all, pid

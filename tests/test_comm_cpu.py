@@ -14,14 +14,16 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, q):
+def _worker(rank, world, port, q, host_group=False):
     import torch
     import torch.distributed as dist
     from pointcloudprocess_b200.sharded import DistComm
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    comm = DistComm(dist, torch, rank, world, torch.device("cpu"))
+    # host_group: the message sizes travel over a second (gloo) group, as bench.py sets it up beside NCCL
+    comm = DistComm(dist, torch, rank, world, torch.device("cpu"),
+                    host_group=dist.new_group(backend="gloo") if host_group else None)
     ok = True
     for rnd in range(3):  # variable sizes, including empty messages
         mk = lambda dst: torch.full((rnd * 7 + rank + 1 if (rnd + dst) % 2 else 0,), 10 * rank + dst, dtype=torch.uint8)
@@ -41,13 +43,13 @@ def _worker(rank, world, port, q):
     q.put((rank, ok))
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_neighbour_exchange_gloo(world):
+@pytest.mark.parametrize("world,host_group", [(2, False), (3, False), (2, True)])
+def test_neighbour_exchange_gloo(world, host_group):
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q, host_group)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=120) for _ in procs]
