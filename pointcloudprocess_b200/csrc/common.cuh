@@ -40,6 +40,7 @@ struct pcp_ctx {
     std::vector<cudaEvent_t> ev_free;
     // copy lanes (pcp_copy_async): streams created on first use, one reusable event per direction
     void* rb_host = nullptr; // mapped pinned scratch of pcp_readback
+    double hint_h = 0, hint_areal = 0; // index.cu: cell size and areal density of the previous index
     cudaStream_t lane[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t lane_in[4] = {nullptr, nullptr, nullptr, nullptr};  // compute -> lane
     cudaEvent_t lane_out[4] = {nullptr, nullptr, nullptr, nullptr}; // lane -> compute

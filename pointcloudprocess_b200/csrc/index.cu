@@ -354,6 +354,14 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
     double a = fmax(e[0] * e[1], fmax(e[0] * e[2], e[1] * e[2]));
     double h = cell_size > 0 ? cell_size : sqrt(16.0 * a / (double)nv);
     if (!(h > 0) || !std::isfinite(h)) h = 1.0;
+    // Warm start: the cell size the data-driven search below settled on for the previous cloud of this context,
+    // scaled by the change of the areal density.  Successive clouds of a job (tiles, shards, passes) are alike, so
+    // the first grid usually passes the occupancy test and the second sort is saved; the test itself is unchanged.
+    const double areal = a > 0 ? (double)nv / a : 0.0;
+    if (!(cell_size > 0) && ctx->hint_h > 0 && areal > 0 && ctx->hint_areal > 0) {
+        const double ratio = ctx->hint_areal / areal;
+        if (ratio > 0.25 && ratio < 4.0) h = ctx->hint_h * sqrt(ratio);
+    }
 
     DevBuf<unsigned long long> k0, k1, bins;
     DevBuf<uint32_t> v0, v1, flag, scan, ncell_dev;
@@ -461,6 +469,7 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
             break;
         }
     }
+    if (!(cell_size > 0) && nv > 64) ctx->hint_h = ix->grid.h, ctx->hint_areal = areal;
     void* q = nullptr;
     IX_TRY(pcp_arena_alloc(ctx, nv * sizeof(pcp_rec), &q));
     ix->rec = (pcp_rec*)q;
@@ -525,7 +534,7 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
         ctx->launches++;
         IX_CUDA(cudaGetLastError());
     }
-    IX_TRY(pcp_index_build_items(ctx, ix, PCP_ITEM_CMAX_DEFAULT));
+    IX_TRY(pcp_index_build_items(ctx, ix, pcp_item_cmax(20)));
 #undef IX_TRY
 #undef IX_CUDA
     *out = ix;

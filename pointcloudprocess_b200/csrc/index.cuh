@@ -58,7 +58,14 @@ struct pcp_index {
 #define PCP_EMPTY_KEY 0xffffffffffffffffull
 #define PCP_HLEVELS 5
 #define PCP_ITEM_LMAX 3           // coarsest level of a dense-kernel work item
-#define PCP_ITEM_CMAX_DEFAULT 24  // leaf capacity tuned for k = 20 (see pcp_item_cmax)
+// leaf capacity for k neighbours: a planar patch of cmax/4..cmax points per leaf keeps the k-th neighbour inside
+// the 3x3x3 block of leaves for most queries while the block stays within the staging capacity (tuned on the
+// city cloud: 1.15 k; 23 for the reference's k = 20)
+static inline uint32_t pcp_item_cmax(int k)
+{
+    const int c = (int)(1.15 * k + 0.5);
+    return (uint32_t)(c < 8 ? 8 : (c > 32 ? 32 : c));
+}
 #define PCP_LKEY(level, prefix) (((unsigned long long)(level) << 58) | (prefix))
 
 __host__ __device__ __forceinline__ unsigned long long pcp_spread3(unsigned long long v)

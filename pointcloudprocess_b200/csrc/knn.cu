@@ -142,7 +142,7 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
         if (kk <= 128) {
             // work items = octree leaves whose capacity follows k (index.cu; 24 for k = 20)
             // (a cache inside the index, rebuilt under the context lock when k changes)
-            PCP_TRY(pcp_index_build_items(ctx, const_cast<pcp_index*>(ix), (uint32_t)std::min(32, std::max(8, (int)(1.15 * kk + 0.5)))));
+            PCP_TRY(pcp_index_build_items(ctx, const_cast<pcp_index*>(ix), pcp_item_cmax(kk)));
             pcp_fknn_params P;
             P.rec = ix->rec;
             P.fpt = ix->fpt;
