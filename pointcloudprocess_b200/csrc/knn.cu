@@ -46,18 +46,19 @@ template <int KPL> int launch_wknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint3
     return PCP_OK;
 }
 
-template <int CAP, int GS> int launch_fknn_t(pcp_ctx* ctx, const pcp_fknn_params& P)
+template <int CAP, int GS, int CAND, bool FLAT> int launch_fknn_t(pcp_ctx* ctx, const pcp_fknn_params& P)
 {
-    const size_t smem = PCP_FK_WARPS * pcp_fd_smem<CAP, GS>::bytes(P.k);
-    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_fast_kernel<CAP, GS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = PCP_FK_WARPS * pcp_fd_smem<CAP, GS, CAND>::bytes(P.k);
+    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_fast_kernel<CAP, GS, CAND, FLAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_fast_kernel<CAP, GS>, 32 * PCP_FK_WARPS, smem));
+    PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_fast_kernel<CAP, GS, CAND, FLAT>, 32 * PCP_FK_WARPS, smem));
     if (per_sm < 1) per_sm = 1;
     // persistent warps: every resident slot of every SM is filled once, items come from the work counter
     unsigned blocks = (unsigned)(ctx->sm_count * per_sm);
     const unsigned need = pcp_blocks_for(P.nitem, PCP_FK_WARPS);
     if (blocks > need) blocks = need;
-    knn_fast_kernel<CAP, GS><<<blocks, 32 * PCP_FK_WARPS, smem, ctx->stream>>>(P);
+    if (P.dbg) fprintf(stderr, "[pcp knn] dense kernel: %zu bytes of shared memory per block, %d blocks per SM, %u blocks\n", smem, per_sm, blocks);
+    knn_fast_kernel<CAP, GS, CAND, FLAT><<<blocks, 32 * PCP_FK_WARPS, smem, ctx->stream>>>(P);
     PCP_LAUNCH_CHECK(ctx);
     return PCP_OK;
 }
@@ -65,9 +66,10 @@ template <int CAP, int GS> int launch_fknn_t(pcp_ctx* ctx, const pcp_fknn_params
 // list capacity CAP >= k plus room for the candidates of the boundary bucket
 int launch_fknn(pcp_ctx* ctx, const pcp_fknn_params& P)
 {
-    if (P.kk <= 24) return launch_fknn_t<32, 8>(ctx, P);
-    if (P.kk <= 52) return launch_fknn_t<64, 8>(ctx, P);
-    return launch_fknn_t<160, 8>(ctx, P);
+    if (P.kk <= 24 && getenv("PCP_FK_NOFLAT")) return launch_fknn_t<32, 8, 288, false>(ctx, P);
+    if (P.kk <= 24) return launch_fknn_t<32, 8, 288, true>(ctx, P);
+    if (P.kk <= 52) return launch_fknn_t<64, 8, 448, true>(ctx, P);
+    return launch_fknn_t<160, 8, 448, true>(ctx, P);
 }
 
 template <int CAP> int launch_far_t(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)

@@ -25,6 +25,7 @@
 #define PCP_FK_NB 64      // histogram buckets (last one = beyond range)
 #define PCP_FK_CAND 256   // staged candidates per item
 #define PCP_FK_WARPS 4
+#define PCP_FK_STAGE_U 2  // candidates a lane loads before it converts and stores them
 #ifndef PCP_FK_MINB
 #define PCP_FK_MINB 6
 #endif
@@ -391,28 +392,43 @@ template <class SM> __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_
 // FP32 only, coordinates relative to the item's cell origin (error ~1e-7 h, see pcp_fd_e1).  Queries whose FP32
 // ordering is not provably the exact one (two candidates closer in d2 than the error bound, or a k-th distance
 // too close to the certified radius) are not settled here: they go to the far list with their upper bound.
-template <int CAP, int GS> struct pcp_fd_smem {
+// CAND: staged candidates per item.  288 candidates, lists for 4 queries of 32 entries and k = 20 come to 9472
+// bytes per warp: 6 blocks of 4 warps per SM.  (Candidates stay 16-byte records: the 4 query groups of a warp read
+// the same 8 candidates per step, one shared-memory wavefront as LDS.128 against three for split x / y / z arrays.)
+template <int CAP, int GS, int CAND> struct pcp_fd_smem {
     static constexpr int NSET = 32 / GS;
-    float4* cand;    // [PCP_FK_CAND]  x, y, z relative to the cell origin, w = sorted position
+    static_assert(CAND % 4 == 0 && CAND < 65536 && (NSET * CAP) % 2 == 0, "pcp_fd_smem: layout");
+    float4* cand;    // [CAND]  x, y, z relative to the leaf origin, w = sorted position
     uint32_t* hist;  // [NSET][PCP_FK_NB]
     float* ld2;      // [NSET][CAP]
-    uint32_t* lpos;  // [NSET][CAP]
+    uint16_t* lpos;  // [NSET][CAP]  candidate number
+    uint32_t* tab;   // [64]  exclusive prefix of the staged runs' lengths (0xffffffff beyond the 27), first points
     uint32_t* nbr;   // [k][32]
     uint32_t* sqpos; // [32]
     float* skd;      // [32]
     static __host__ __device__ size_t bytes(int k)
     {
-        return (size_t)PCP_FK_CAND * 16 + (size_t)NSET * PCP_FK_NB * 4 + (size_t)NSET * CAP * 8 + (size_t)32 * k * 4 + 256;
+        return (size_t)CAND * 16 + (size_t)NSET * PCP_FK_NB * 4 + (size_t)NSET * CAP * 6 + 256 + (size_t)32 * k * 4 + 256;
     }
     __device__ pcp_fd_smem(unsigned char* base, int k)
     {
         cand = reinterpret_cast<float4*>(base);
-        hist = reinterpret_cast<uint32_t*>(base + PCP_FK_CAND * 16);
+        hist = reinterpret_cast<uint32_t*>(cand + CAND);
         ld2 = reinterpret_cast<float*>(hist + NSET * PCP_FK_NB);
-        lpos = reinterpret_cast<uint32_t*>(ld2 + NSET * CAP);
-        nbr = lpos + NSET * CAP;
+        lpos = reinterpret_cast<uint16_t*>(ld2 + NSET * CAP);
+        tab = reinterpret_cast<uint32_t*>(lpos + NSET * CAP);
+        nbr = tab + 64;
         sqpos = nbr + 32 * k;
         skd = reinterpret_cast<float*>(sqpos + 32);
+    }
+    // sorted position of the f-th point of the staged runs
+    __device__ __forceinline__ uint32_t position(uint32_t f) const
+    {
+        int t = 0;
+#pragma unroll
+        for (int step = 16; step; step >>= 1)
+            if (tab[t + step] <= f) t += step;
+        return tab[32 + t] + (f - tab[t]);
     }
 };
 
@@ -423,8 +439,8 @@ template <int CAP, int GS> struct pcp_fd_smem {
 
 // Every group of G lanes searches the staged block for its own query.  dku: upper bound of the k-th squared
 // distance (valid for OK and AMBIG).
-template <int G, int CAP>
-__device__ __forceinline__ int pcp_fd_search(const float4* __restrict__ cand, int T, const pcp_fd_smem<CAP, G>& S, int lane,
+template <int G, int CAP, int CAND>
+__device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CAND>& S, int lane,
                                              bool active, int slot, int kk, float qfx, float qfy, float qfz, float top,
                                              float g2, float e1, float& dku)
 {
@@ -435,7 +451,7 @@ __device__ __forceinline__ int pcp_fd_search(const float4* __restrict__ cand, in
     const unsigned gmask = (G == 32) ? 0xffffffffu : ((1u << G) - 1u);
     uint32_t* hist = S.hist + set * PCP_FK_NB;
     float* ld2 = S.ld2 + set * CAP;
-    uint32_t* lpos = S.lpos + set * CAP;
+    uint16_t* lpos = S.lpos + set * CAP;
     const int key0 = (__float_as_int(top) >> 21) - (PCP_FK_NB - 2);
 #pragma unroll
     for (int i = 0; i < NBL; i++) hist[gl + i * G] = 0;
@@ -443,10 +459,13 @@ __device__ __forceinline__ int pcp_fd_search(const float4* __restrict__ cand, in
     // ---- pass 1: histogram of FP32 squared distances ----
     for (int f0 = 0; f0 < T; f0 += G) {
         const int i = f0 + gl;
-        const float4 c = cand[i < T ? i : 0];
+        const float4 c = S.cand[i < T ? i : 0];
         const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
         const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-        if (i < T && active) atomicAdd(&hist[pcp_fk_bucket(d2, key0)], 1u);
+        // (the last bucket = beyond `top` is never counted: nothing is decided there, and it is the one address
+        // most lanes would collide on)
+        const int b = pcp_fk_bucket(d2, key0);
+        if (i < T && active && b < PCP_FK_NB - 1) atomicAdd(&hist[b], 1u);
     }
     __syncwarp();
     // ---- scan: bucket b* of the kk-th candidate; hist[b] becomes the write cursor (exclusive prefix) ----
@@ -500,14 +519,14 @@ __device__ __forceinline__ int pcp_fd_search(const float4* __restrict__ cand, in
     // ---- pass 2: scatter the candidates of buckets <= b* into the list, bucket by bucket ----
     for (int f0 = 0; f0 < T; f0 += G) {
         const int i = f0 + gl;
-        const float4 c = cand[i < T ? i : 0];
+        const float4 c = S.cand[i < T ? i : 0];
         const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
         const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
         const int b = pcp_fk_bucket(d2, key0);
         if (live && i < T && b <= bstar) {
             const uint32_t at = atomicAdd(&hist[b], 1u);
             ld2[at] = d2;
-            lpos[at] = __float_as_uint(c.w);
+            lpos[at] = (uint16_t)i;
         }
     }
     __syncwarp();
@@ -533,7 +552,7 @@ __device__ __forceinline__ int pcp_fd_search(const float4* __restrict__ cand, in
                 r += dj < d ? 1u : 0u;
                 if (j != (uint32_t)e && fabsf(dj - d) <= amb2) ambig = true;
             }
-            if (r < (uint32_t)kk) S.nbr[r * 32 + slot] = lpos[e];
+            if (r < (uint32_t)kk) S.nbr[r * 32 + slot] = __float_as_uint(S.cand[lpos[e]].w);
             if (r == (uint32_t)kk - 1u) dkl = d;
         }
     }
@@ -553,14 +572,14 @@ __device__ __forceinline__ int pcp_fd_search(const float4* __restrict__ cand, in
 // Settles every query whose k nearest provably lie inside the 3x3x3 block of base cells around its cell; the
 // others are appended to the "far" list with the best known upper bound of their k-th squared distance
 // (+inf if none) for knn_far_kernel.
-template <int CAP, int GS>
+template <int CAP, int GS, int CAND, bool FLAT>
 static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fast_kernel(pcp_fknn_params P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int NSET = 32 / GS;
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const pcp_fd_smem<CAP, GS> S(smem_raw + pcp_fd_smem<CAP, GS>::bytes(P.k) * warp, P.k);
+    const pcp_fd_smem<CAP, GS, CAND> S(smem_raw + pcp_fd_smem<CAP, GS, CAND>::bytes(P.k) * warp, P.k);
     const int set = lane / GS;
     S.sqpos[lane] = 0xffffffffu;
     __syncwarp();
@@ -623,27 +642,56 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
         }
         const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
         pre -= nb_count;
-        const bool staged = total <= PCP_FK_CAND && total >= (uint32_t)P.kk;
+        const bool staged = total <= (uint32_t)CAND && total >= (uint32_t)P.kk;
         PCP_FK_DBG(0, 1);
         PCP_FK_DBG(1, staged ? 1 : 0);
         PCP_FK_DBG(2, nwant);
         PCP_FK_DBG(3, total);
-        PCP_FK_DBG(4, total > PCP_FK_CAND);
-        PCP_FK_DBG(8, total > PCP_FK_CAND ? nwant : 0);
+        PCP_FK_DBG(4, total > (uint32_t)CAND);
+        PCP_FK_DBG(8, total > (uint32_t)CAND ? nwant : 0);
         PCP_FK_DBG(9, total < (uint32_t)P.kk ? nwant : 0);
         unsigned okmask = 0;
         // lane j: upper bound of query j's k-th squared distance (+inf: none; -1: none, block too dense to stage)
-        float myU = (total > PCP_FK_CAND) ? -1.0f : __int_as_float(0x7f800000);
+        float myU = (total > (uint32_t)CAND) ? -1.0f : __int_as_float(0x7f800000);
         if (staged) {
-            for (int nb = 0; nb < 27; nb++) {
-                const uint32_t c = __shfl_sync(0xffffffffu, nb_count, nb);
-                if (c == 0) continue;
-                const uint32_t s = __shfl_sync(0xffffffffu, nb_start, nb);
-                const uint32_t p = __shfl_sync(0xffffffffu, pre, nb);
-                for (uint32_t t = lane; t < c; t += 32) {
-                    const pcp_rec r = pcp_load_rec(P.rec, s + t);
-                    S.cand[p + t] = make_float4((float)(r.x - ox), (float)(r.y - oy), (float)(r.z - oz),
-                                                __uint_as_float(s + t));
+            if constexpr (FLAT) {
+                // the runs' table, then the block itself, flat over the candidates with PCP_FK_STAGE_U loads in
+                // flight per lane
+                S.tab[lane] = lane < 27 ? pre : 0xffffffffu;
+                S.tab[32 + lane] = nb_start;
+                __syncwarp();
+#pragma unroll 1
+                for (uint32_t f0 = 0; f0 < total; f0 += 32 * PCP_FK_STAGE_U) {
+                    pcp_rec r[PCP_FK_STAGE_U];
+                    uint32_t ps[PCP_FK_STAGE_U];
+#pragma unroll
+                    for (int u = 0; u < PCP_FK_STAGE_U; u++) {
+                        const uint32_t f = f0 + 32 * u + lane;
+                        ps[u] = 0;
+                        if (f < total) {
+                            ps[u] = S.position(f);
+                            r[u] = pcp_load_rec(P.rec, ps[u]);
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < PCP_FK_STAGE_U; u++) {
+                        const uint32_t f = f0 + 32 * u + lane;
+                        if (f < total)
+                            S.cand[f] = make_float4((float)(r[u].x - ox), (float)(r[u].y - oy), (float)(r[u].z - oz),
+                                                    __uint_as_float(ps[u]));
+                    }
+                }
+            } else {
+                for (int nb = 0; nb < 27; nb++) {
+                    const uint32_t c = __shfl_sync(0xffffffffu, nb_count, nb);
+                    if (c == 0) continue;
+                    const uint32_t s = __shfl_sync(0xffffffffu, nb_start, nb);
+                    const uint32_t p = __shfl_sync(0xffffffffu, pre, nb);
+                    for (uint32_t t = lane; t < c; t += 32) {
+                        const pcp_rec r = pcp_load_rec(P.rec, s + t);
+                        S.cand[p + t] = make_float4((float)(r.x - ox), (float)(r.y - oy), (float)(r.z - oz),
+                                                    __uint_as_float(s + t));
+                    }
                 }
             }
             __syncwarp();
@@ -674,7 +722,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
                 const float g2 = dout * dout * 0.999999f;
                 const int slot = fill + __popc(want & ((1u << sj) - 1u));
                 float dku;
-                const int st = pcp_fd_search<GS, CAP>(S.cand, (int)total, S, lane, active, slot, P.kk, qfx, qfy, qfz,
+                const int st = pcp_fd_search<GS, CAP, CAND>((int)total, S, lane, active, slot, P.kk, qfx, qfy, qfz,
                                                       top0, g2, e1, dku);
                 // collect the group results as query bits
 #pragma unroll
