@@ -269,4 +269,59 @@ class CalculateFeature {
     }
 };
 
+// io::loadPCDFile / savePCDFile* (pcd_helper.h:1343-1497): 0 = ok, -1 = error with the message on stdout, as
+// PCDReader / PCDWriter report.  Host-side code of the library (csrc/pcd_io.cu); no device is needed.
+namespace io {
+namespace detail {
+// PointXYZRGBA stores x y z rgba stamp_id; any other record type (PointC ...) stores its leading x y z doubles
+template <typename PointT> struct point_kind {
+    static const int value = PCP_PCD_POINT_XYZ;
+};
+template <> struct point_kind<PointXYZRGBA> {
+    static const int value = PCP_PCD_POINT_XYZRGBA;
+};
+inline int report(int st)
+{
+    if (st == PCP_OK) return 0;
+    std::cout << pcp_last_error(nullptr) << std::endl;
+    return -1;
+}
+template <typename PointT> int save(const std::string& file_name, const PointCloud<PointT>& cloud, int mode, int precision)
+{
+    return report(pcp_pcd_save(file_name.c_str(), point_kind<PointT>::value, cloud.points.data(), cloud.points.size(),
+                               sizeof(PointT), cloud.width, cloud.height, mode, precision));
+}
+} // namespace detail
+
+template <typename PointT> int loadPCDFile(const std::string& file_name, PointCloud<PointT>& cloud)
+{
+    pcp_pcd_header h;
+    if (pcp_pcd_read_header(file_name.c_str(), &h) != PCP_OK) return detail::report(-1);
+    cloud.points.assign((size_t)h.points, PointT());
+    size_t n = 0;
+    int dense = 1;
+    const int st = pcp_pcd_load(file_name.c_str(), detail::point_kind<PointT>::value, cloud.points.data(), cloud.points.size(),
+                                sizeof(PointT), &n, &dense);
+    if (st != PCP_OK) return detail::report(st);
+    cloud.width = h.width, cloud.height = h.height, cloud.is_dense = dense != 0;
+    return 0;
+}
+template <typename PointT> int savePCDFile(const std::string& file_name, const PointCloud<PointT>& cloud, bool binary_mode = true)
+{
+    return detail::save(file_name, cloud, binary_mode ? PCP_PCD_BINARY : PCP_PCD_ASCII, 8);
+}
+template <typename PointT> int savePCDFileASCII(const std::string& file_name, const PointCloud<PointT>& cloud)
+{
+    return detail::save(file_name, cloud, PCP_PCD_ASCII, 8);
+}
+template <typename PointT> int savePCDFileBinary(const std::string& file_name, const PointCloud<PointT>& cloud)
+{
+    return detail::save(file_name, cloud, PCP_PCD_BINARY, 8);
+}
+template <typename PointT> int savePCDFileBinaryCompressed(const std::string& file_name, const PointCloud<PointT>& cloud)
+{
+    return detail::save(file_name, cloud, PCP_PCD_BINARY_COMPRESSED, 8);
+}
+} // namespace io
+
 } // namespace cloud_blend_double

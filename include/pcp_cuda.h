@@ -41,7 +41,8 @@ typedef enum pcp_status {
     PCP_ERR_CUDA = -2,    /* CUDA runtime error, see pcp_last_error */
     PCP_ERR_NOMEM = -3,
     PCP_ERR_RANGE = -4,   /* value not representable (e.g. > 2^31-1 points, voxel grid wider than 2^21) */
-    PCP_ERR_NCCL = -5
+    PCP_ERR_NCCL = -5,
+    PCP_ERR_IO = -6       /* file could not be opened / read / written */
 } pcp_status;
 
 /* LAS_POINT_PROPERTY, data_struct.h:161-173.  48 bytes. */
@@ -219,6 +220,45 @@ PCP_API int pcp_minmax(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, d
  * centred != 0 omits the UTM-scale world offset. */
 PCP_API int pcp_synth_cloud(pcp_ctx* ctx, int kind, uint64_t n_total, uint64_t first, uint64_t n, uint64_t seed,
                             int centred, void* out_pts);
+
+/* ---- PCD v0.7 files and LZF (host side, no device work) ----------------------------------------------------
+ * Replace io::loadPCDFile / savePCDFile* (pcd_helper.h:1343-1497), PCDReader::readHeader / read
+ * (pcd_helper.cpp:71-333, 845-1181), PCDWriter::generateHeader / writeASCII / writeBinary /
+ * writeBinaryCompressed (pcd_helper.h:323-371, 489-1090) and lzfCompress / lzfDecompress (lzf.cpp:86-415).
+ * Errors: negative status, text through pcp_last_error(NULL). */
+#define PCP_PCD_ASCII 0
+#define PCP_PCD_BINARY 1
+#define PCP_PCD_BINARY_COMPRESSED 2
+#define PCP_PCD_POINT_XYZRGBA 0 /* records shaped like PointXYZRGBA: x, y, z doubles @0, w @24, rgba @32, stamp_id @36 */
+#define PCP_PCD_POINT_XYZ 1     /* records that start with x, y, z doubles (PointC); only those fields are stored */
+#define PCP_PCD_MAX_FIELDS 16
+typedef struct pcp_pcd_header {
+    uint64_t points;
+    uint64_t data_offset; /* first byte of the payload */
+    uint32_t width, height;
+    int32_t data_type;    /* PCP_PCD_ASCII / BINARY / BINARY_COMPRESSED */
+    int32_t nfields;
+    char names[PCP_PCD_MAX_FIELDS][32];
+    int32_t size[PCP_PCD_MAX_FIELDS];
+    int32_t count[PCP_PCD_MAX_FIELDS];
+    char type[PCP_PCD_MAX_FIELDS]; /* 'F', 'U', 'I' */
+    double viewpoint[7];           /* tx ty tz qw qx qy qz */
+} pcp_pcd_header;
+PCP_API int pcp_pcd_read_header(const char* path, pcp_pcd_header* header);
+/* Reads the file's points into `cap` records of `stride` bytes.  Fields are matched to the record's members on
+ * name + type + size + count as point_traits.h:271-279 does; other fields are ignored and unmatched members keep
+ * the default constructor's values (0, w = 1).  *n = points in the file (also on PCP_ERR_RANGE when cap is too
+ * small).  *is_dense = 0 when a binary payload holds a non-finite value (ascii files are not checked, as in the
+ * reference). */
+PCP_API int pcp_pcd_load(const char* path, int point_kind, void* pts, size_t cap, size_t stride, size_t* n, int* is_dense);
+/* Writes n records.  width = height = 0 means an unorganised cloud (n x 1).  mode: PCP_PCD_*; precision: significant
+ * digits of the ascii writer (the reference's default is 8).  The payload holds the registered fields only, packed;
+ * binary_compressed is limited to 4 GiB of them (32-bit size words). */
+PCP_API int pcp_pcd_save(const char* path, int point_kind, const void* pts, size_t n, size_t stride, uint32_t width,
+                         uint32_t height, int mode, int precision);
+/* liblzf streams as the reference's lzf.cpp writes them (byte-identical); 0 = failure (output too small / corrupt). */
+PCP_API unsigned int pcp_lzf_compress(const void* in, unsigned int in_len, void* out, unsigned int out_len);
+PCP_API unsigned int pcp_lzf_decompress(const void* in, unsigned int in_len, void* out, unsigned int out_len);
 
 #ifdef __cplusplus
 }

@@ -16,6 +16,7 @@ SYMBOLS = [
     "pcp_radius_fill", "pcp_features_knn", "pcp_features_radius", "pcp_plane_fit", "pcp_voxel_grid",
     "pcp_remove_duplicate", "pcp_features_knn_ex", "pcp_remove_duplicate_centred", "pcp_serial_sum",
     "pcp_column_histogram", "pcp_select_range", "pcp_select_columns", "pcp_select_boundary", "pcp_features_merge", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
+    "pcp_pcd_read_header", "pcp_pcd_load", "pcp_pcd_save", "pcp_lzf_compress", "pcp_lzf_decompress",
 ]
 
 
@@ -30,6 +31,13 @@ class PcpError(RuntimeError):
 
 
 _lib = None
+
+
+class PcdHeader(C.Structure):
+    """pcp_pcd_header (include/pcp_cuda.h)."""
+    _fields_ = [("points", C.c_uint64), ("data_offset", C.c_uint64), ("width", C.c_uint32), ("height", C.c_uint32),
+                ("data_type", C.c_int32), ("nfields", C.c_int32), ("names", (C.c_char * 32) * 16),
+                ("size", C.c_int32 * 16), ("count", C.c_int32 * 16), ("type", C.c_char * 16), ("viewpoint", C.c_double * 7)]
 
 
 def load():
@@ -85,6 +93,11 @@ def load():
         "pcp_select_columns": (i32, [vp, vp, sz, sz, i32, C.c_float, dbl, i32, i32, i32, vp, C.POINTER(sz)]),
         "pcp_select_boundary": (i32, [vp, vp, sz, sz, i32, vp, i32, dbl, i32, dbl, sz, vp, vp, C.POINTER(sz)]),
         "pcp_features_merge": (i32, [vp, sz, i32, i32, vp, vp, vp, vp, vp, vp]),
+        "pcp_pcd_read_header": (i32, [C.c_char_p, C.POINTER(PcdHeader)]),
+        "pcp_pcd_load": (i32, [C.c_char_p, i32, vp, sz, sz, C.POINTER(sz), C.POINTER(i32)]),
+        "pcp_pcd_save": (i32, [C.c_char_p, i32, vp, sz, sz, u32, u32, i32, i32]),
+        "pcp_lzf_compress": (u32, [vp, u32, vp, u32]),
+        "pcp_lzf_decompress": (u32, [vp, u32, vp, u32]),
         "pcp_centroid": (i32, [vp, vp, sz, sz, vp, C.POINTER(u64)]),
         "pcp_minmax": (i32, [vp, vp, sz, sz, vp, vp]),
         "pcp_synth_cloud": (i32, [vp, i32, u64, u64, u64, u64, i32, vp]),

@@ -412,7 +412,7 @@ class PointCloud:
 
     @property
     def width(self):
-        return len(self.points)
+        return len(self.points) // max(int(self.height), 1)
 
     def size(self):
         return len(self.points)
@@ -421,6 +421,87 @@ class PointCloud:
         p = np.zeros(1, dtype=POINT_DTYPE)
         p["x"], p["y"], p["z"], p["w"], p["rgba"], p["stamp_id"] = x, y, z, 1.0, rgba, stamp_id
         self.points = np.concatenate([self.points, p])
+
+
+class io:
+    """io::loadPCDFile / savePCDFile* (pcd_helper.h:1343-1497) and lzfCompress / lzfDecompress (lzf.h) over the
+    library's host-side PCD code (csrc/pcd_io.cu).  Return conventions of the reference: 0 = ok, -1 = error (the
+    message is printed, as PCDReader does)."""
+
+    @staticmethod
+    def _fail(L):
+        print(L.pcp_last_error(None).decode())
+        return -1
+
+    @staticmethod
+    def readHeader(file_name):
+        """-> dict (fields, sizes, types, counts, width, height, points, data_type, data_offset, viewpoint) or None."""
+        L = _lib.load()
+        h = _lib.PcdHeader()
+        if L.pcp_pcd_read_header(str(file_name).encode(), C.byref(h)) != 0:
+            io._fail(L)
+            return None
+        n = h.nfields
+        return {"fields": [h.names[i].value.decode() for i in range(n)], "sizes": list(h.size[:n]),
+                "types": [h.type[i:i + 1].decode() for i in range(n)], "counts": list(h.count[:n]), "width": h.width,
+                "height": h.height, "points": h.points, "data_type": ("ascii", "binary", "binary_compressed")[h.data_type],
+                "data_offset": h.data_offset, "viewpoint": list(h.viewpoint)}
+
+    @staticmethod
+    def loadPCDFile(file_name, cloud):
+        L = _lib.load()
+        h = _lib.PcdHeader()
+        if L.pcp_pcd_read_header(str(file_name).encode(), C.byref(h)) != 0:
+            return io._fail(L)
+        pts = np.zeros(int(h.points), dtype=POINT_DTYPE)
+        n, dense = C.c_size_t(0), C.c_int(1)
+        if L.pcp_pcd_load(str(file_name).encode(), 0, pts.ctypes.data, len(pts), 48, C.byref(n), C.byref(dense)) != 0:
+            return io._fail(L)
+        cloud.points, cloud.height, cloud.is_dense = pts, int(h.height), bool(dense.value)
+        return 0
+
+    @staticmethod
+    def _save(file_name, cloud, mode, precision=8):
+        L = _lib.load()
+        pts = np.ascontiguousarray(cloud.points if isinstance(cloud, PointCloud) else cloud)
+        height = int(cloud.height) if isinstance(cloud, PointCloud) else 1
+        width = len(pts) // max(height, 1)
+        st = L.pcp_pcd_save(str(file_name).encode(), 0, pts.ctypes.data, len(pts), pts.dtype.itemsize, width, height, mode,
+                            precision)
+        return 0 if st == 0 else io._fail(L)
+
+    @staticmethod
+    def savePCDFile(file_name, cloud, binary_mode=True):
+        return io._save(file_name, cloud, 1 if binary_mode else 0)
+
+    @staticmethod
+    def savePCDFileASCII(file_name, cloud, precision=8):
+        return io._save(file_name, cloud, 0, precision)
+
+    @staticmethod
+    def savePCDFileBinary(file_name, cloud):
+        return io._save(file_name, cloud, 1)
+
+    @staticmethod
+    def savePCDFileBinaryCompressed(file_name, cloud):
+        return io._save(file_name, cloud, 2)
+
+    @staticmethod
+    def lzfCompress(data):
+        """-> the LZF stream (bytes), b"" when the data does not shrink into 1.5x its size (lzf.cpp returns 0)."""
+        L = _lib.load()
+        src = bytes(data)
+        out = C.create_string_buffer(int(len(src) * 1.5) + 16)
+        n = L.pcp_lzf_compress(src, len(src), out, len(out))
+        return out.raw[:n]
+
+    @staticmethod
+    def lzfDecompress(data, out_len):
+        L = _lib.load()
+        src = bytes(data)
+        out = C.create_string_buffer(max(int(out_len), 1))
+        n = L.pcp_lzf_decompress(src, len(src), out, int(out_len))
+        return out.raw[:n]
 
 
 class KdTreeFLANN:

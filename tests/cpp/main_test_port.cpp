@@ -1,6 +1,7 @@
 // The reference's own smoke functions test_kd_tree and test_voxel_grid (main_test.cpp:126-188), written against
 // include/pcp/pcp_facade.hpp exactly as they are written against the reference headers.  They print what the
 // reference prints; the pytest wrapper compares the output with the derivable known answers.
+#include <cmath>
 #include <cstdio>
 #include "../../include/pcp/pcp_facade.hpp"
 using namespace cloud_blend_double;
@@ -49,8 +50,28 @@ static void test_kd_tree()
     printf("props %d %.9g\n", props.get()[0].PointID, props.get()[0].curvature);
 }
 
-int main()
+// main_test.cpp:188-208 (test_double_io): ten points at pi*i saved as a binary PCD and loaded back
+static int test_double_io(const char* path)
 {
+    CloudPtr cloud(new Cloud);
+    for (int i = 0; i < 10; i++) {
+        CloudItem p;
+        p.x = M_PI * i, p.y = M_PI * i, p.z = M_PI * i;
+        cloud->push_back(p);
+    }
+    if (io::savePCDFileBinary(path, *cloud) != 0) return 1;
+    cloud->clear();
+    if (io::loadPCDFile(path, *cloud) != 0) return 1;
+    printf("io %zu\n", cloud->size());
+    for (size_t i = 0; i < cloud->size(); i++) printf("%.17g %.17g %.17g %u\n", (*cloud)[i].x, (*cloud)[i].y, (*cloud)[i].z, (*cloud)[i].rgba);
+    Cloud missing;
+    printf("missing %d\n", io::loadPCDFile(std::string(path) + ".not-there", missing));
+    return 0;
+}
+
+int main(int argc, char** argv)
+{
+    if (argc == 3 && std::string(argv[1]) == "io") return test_double_io(argv[2]); // host only: no device needed
     try {
         test_voxel_grid();
         test_kd_tree();

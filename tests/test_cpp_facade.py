@@ -29,6 +29,18 @@ def test_facade_compiles_and_fails_loudly_without_gpu(tmp_path):
     assert r.returncode == 3 and "no CPU fallback" in r.stdout
 
 
+def test_reference_double_io_through_the_facade(tmp_path):
+    """main_test.cpp:188-208 against our headers; PCD I/O is host code, so this runs without a GPU."""
+    r = subprocess.run([_build(tmp_path), "io", str(tmp_path / "1.pcd")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    lines = r.stdout.strip().split("\n")
+    assert lines[0] == "io 10"
+    for i in range(10):
+        x, y, z, rgba = lines[1 + i].split()
+        assert float(x) == float(y) == float(z) == np.pi * i and rgba == "0"
+    assert "Could not open file" in lines[11] and lines[12] == "missing -1"
+
+
 @pytest.mark.gpu
 def test_reference_smoke_functions_known_answers(tmp_path):
     r = subprocess.run([_build(tmp_path)], capture_output=True, text=True)

@@ -316,3 +316,25 @@ def test_serial_centroid_full_size(ctx, orc):
     c, cnt = ctx.centroid(cloud)
     rc, rcnt = orc.centroid(cloud)
     assert cnt == rcnt and c.tobytes() == rc.tobytes()
+
+
+# ---- BASELINE.json configs[0]: calculate_feature k=20 on a cloud that went through a binary_compressed PCD -------
+@pytest.mark.parametrize("n", [100000, 1000000])
+def test_config0_features_on_a_cloud_loaded_from_compressed_pcd(ctx, orc, tmp_path, n):
+    import pointcloudprocess_b200 as pcp
+    cloud = ctx.synth_cloud("strip", n, seed=1)
+    path = tmp_path / "synth.pcd"
+    assert pcp.io.savePCDFileBinaryCompressed(path, cloud) == 0
+    loaded = pcp.PointCloud()
+    assert pcp.io.loadPCDFile(path, loaded) == 0
+    assert_clouds_equal(loaded.points, cloud)  # x y z rgba stamp_id survive bit for bit; w is the constructor's 1
+    ix = pcp.Index(ctx, loaded.points)
+    got = ix.features_knn(20, want_idx=(n <= 100000))
+    ix.free()
+    if n <= 100000:
+        props, eig, lps, kidx = orc.features_knn(loaded.points, 20, want_idx=True)
+        assert np.array_equal(got["knn_idx"], kidx)
+    else:
+        props, eig, lps = orc.features_knn(loaded.points, 20)[:3]
+    assert_props_equal(got["props"], props)
+    assert np.array_equal(got["eig"], eig, equal_nan=True)
