@@ -11,6 +11,7 @@
 // the library surface as std::runtime_error (the reference's own error style -- cout + return code -- is kept
 // for the documented cases: filter() without input prints and returns an empty cloud, voxel_grid.h:815-821).
 #pragma once
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
 #include <iostream>
@@ -18,6 +19,7 @@
 #include <mutex>
 #include <stdexcept>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../pcp_cuda.h"
@@ -167,31 +169,85 @@ template <typename PointT> class VoxelGrid {
     void setInputCloud(const PointCloudConstPtr& cloud) { input_ = cloud; }
     void setLeafSize(double lx, double ly, double lz) { leaf_[0] = lx, leaf_[1] = ly, leaf_[2] = lz; }
     void setDownsampleAllData(bool f) { downsample_all_data_ = f; }
+    bool getDownsampleAllData() const { return downsample_all_data_; }
+    void setSaveLeafLayout(bool f) { save_leaf_layout_ = f; }
+    bool getSaveLeafLayout() const { return save_leaf_layout_; }
+    // voxel_grid.h:592-615 (plain arrays where the reference returns Eigen::Vector3i)
     const int* getMinBoxCoordinates() const { return min_b_; }
+    const int* getMaxBoxCoordinates() const { return max_b_; }
     const int* getNrDivisions() const { return div_b_; }
+    const long long* getDivisionMultiplier() const { return divb_mul_; }
+    // voxel_grid.h:672-678: truncating
+    void getGridCoordinates(double x, double y, double z, int ijk[3]) const
+    {
+        ijk[0] = static_cast<int>(double(x * (1.0 / leaf_[0])));
+        ijk[1] = static_cast<int>(double(y * (1.0 / leaf_[1])));
+        ijk[2] = static_cast<int>(double(z * (1.0 / leaf_[2])));
+    }
+    // voxel_grid.h:684-696: -1 outside the grid, for an empty cell, or when the layout was not saved
+    int getCentroidIndexAt(const int ijk[3]) const
+    {
+        if (layout_.empty()) return -1;
+        long long idx = 0;
+        for (int a = 0; a < 3; a++) idx += ((long long)ijk[a] - min_b_[a]) * divb_mul_[a];
+        if (idx < 0 || idx >= (long long)div_b_[0] * div_b_[1] * div_b_[2]) return -1;
+        auto it = layout_.find(idx);
+        return it == layout_.end() ? -1 : it->second;
+    }
+    int getCentroidIndex(const PointT& p) const
+    {
+        int ijk[3];
+        getGridCoordinates(p.x, p.y, p.z, ijk);
+        return getCentroidIndexAt(ijk);
+    }
+    // voxel_grid.h:648-652: one entry per cell of the grid, -1 = empty (can be large: div_x * div_y * div_z)
+    std::vector<int> getLeafLayout() const
+    {
+        std::vector<int> full;
+        if (layout_.empty()) return full;
+        full.assign((size_t)div_b_[0] * div_b_[1] * div_b_[2], -1);
+        for (const auto& kv : layout_) full[(size_t)kv.first] = kv.second;
+        return full;
+    }
     void filter(PointCloud<PointT>& output)
     {
         output.clear();
+        layout_.clear();
         if (!input_) { // voxel_grid.h:815-821
             std::cout << "[applyFilter] No input dataset given!" << std::endl;
             return;
         }
-        output.points.resize(input_->points.size());
+        const size_t n = input_->points.size();
+        output.points.resize(n);
+        std::vector<int32_t> cell(save_leaf_layout_ ? 3 * n : 0);
         size_t m = 0;
         detail::check(detail::context(),
-                      pcp_voxel_grid(detail::context(), input_->points.data(), input_->points.size(), sizeof(PointT), leaf_,
-                                     downsample_all_data_ ? 1 : 0, output.points.data(), &m, min_b_, div_b_, nullptr,
-                                     nullptr),
+                      pcp_voxel_grid(detail::context(), input_->points.data(), n, sizeof(PointT), leaf_,
+                                     downsample_all_data_ ? 1 : 0, output.points.data(), &m, min_b_, div_b_,
+                                     save_leaf_layout_ ? cell.data() : nullptr, nullptr),
                       "VoxelGrid::filter");
         output.points.resize(m);
         output.width = (uint32_t)m, output.height = 1, output.is_dense = true; // voxel_grid.h:824-825,1055
+        for (int a = 0; a < 3; a++) max_b_[a] = min_b_[a] + div_b_[a] - 1;
+        divb_mul_[0] = 1, divb_mul_[1] = div_b_[0], divb_mul_[2] = (long long)div_b_[0] * div_b_[1];
+        if (save_leaf_layout_) { // outputs are in ascending cell index (voxel_grid.h:948, 1031)
+            std::vector<long long> idx;
+            idx.reserve(n);
+            for (size_t i = 0; i < n; i++)
+                if (cell[3 * i] >= 0) idx.push_back(cell[3 * i] + cell[3 * i + 1] * divb_mul_[1] + cell[3 * i + 2] * divb_mul_[2]);
+            std::sort(idx.begin(), idx.end());
+            idx.erase(std::unique(idx.begin(), idx.end()), idx.end());
+            for (size_t i = 0; i < idx.size(); i++) layout_[idx[i]] = (int)i;
+        }
     }
 
   private:
     PointCloudConstPtr input_;
     double leaf_[3] = {0, 0, 0};
-    bool downsample_all_data_ = true;
-    int32_t min_b_[3] = {0, 0, 0}, div_b_[3] = {0, 0, 0};
+    bool downsample_all_data_ = true, save_leaf_layout_ = false;
+    int32_t min_b_[3] = {0, 0, 0}, div_b_[3] = {0, 0, 0}, max_b_[3] = {0, 0, 0};
+    long long divb_mul_[3] = {0, 0, 0};
+    std::unordered_map<long long, int> layout_; // cell index -> output index (sparse leaf_layout_)
 };
 
 class PointCloudHelper {

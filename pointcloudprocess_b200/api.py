@@ -531,12 +531,17 @@ class KdTreeFLANN:
 
 
 class VoxelGrid:
+    """voxel_grid.h:455-810 (setters / accessors) over pcp_voxel_grid.  The leaf layout (voxel_grid.h:964-983,
+    1031-1032) is kept sparse: cell index -> output index; getLeafLayout() expands it."""
+
     def __init__(self, ctx=None):
         self.ctx = ctx or default_context()
         self.input = None
         self.leaf = None
         self.downsample_all_data = True  # voxel_grid.h:499
+        self.save_leaf_layout = False
         self.min_b = self.div_b = None
+        self._layout = None
 
     def setInputCloud(self, cloud):
         self.input = cloud
@@ -544,14 +549,71 @@ class VoxelGrid:
     def setLeafSize(self, lx, ly, lz):
         self.leaf = (float(lx), float(ly), float(lz))
 
+    def getLeafSize(self):
+        return self.leaf
+
     def setDownsampleAllData(self, flag):
         self.downsample_all_data = bool(flag)
+
+    def getDownsampleAllData(self):
+        return self.downsample_all_data
+
+    def setSaveLeafLayout(self, flag):
+        self.save_leaf_layout = bool(flag)
+
+    def getSaveLeafLayout(self):
+        return self.save_leaf_layout
 
     def getMinBoxCoordinates(self):
         return self.min_b
 
+    def getMaxBoxCoordinates(self):
+        return None if self.min_b is None else self.min_b + self.div_b - 1
+
     def getNrDivisions(self):
         return self.div_b
+
+    def getDivisionMultiplier(self):
+        d = self.div_b
+        return None if d is None else np.array([1, d[0], d[0] * d[1]], dtype=np.int64)
+
+    def getGridCoordinates(self, x, y, z):
+        """(int)(x * inverse_leaf) per axis, truncating (voxel_grid.h:672-678)."""
+        inv = [1.0 / l for l in self.leaf]
+        return np.array([int(x * inv[0]), int(y * inv[1]), int(z * inv[2])], dtype=np.int32)
+
+    def getCentroidIndexAt(self, ijk):
+        if self._layout is None:
+            return -1
+        rel = np.asarray(ijk, dtype=np.int64) - self.min_b
+        idx = int(rel.dot(self.getDivisionMultiplier()))
+        if idx < 0 or idx >= int(np.prod(self.div_b.astype(np.int64))):
+            return -1
+        return self._layout.get(idx, -1)
+
+    def getCentroidIndex(self, p):
+        x, y, z = (p["x"], p["y"], p["z"]) if hasattr(p, "dtype") and p.dtype.names else p[:3]
+        return self.getCentroidIndexAt(self.getGridCoordinates(x, y, z))
+
+    def getNeighborCentroidIndices(self, reference_point, relative_coordinates):
+        """relative_coordinates: 3 x m integer offsets; -1 for cells outside the grid (voxel_grid.h:627-646)."""
+        x, y, z = (reference_point["x"], reference_point["y"], reference_point["z"]) \
+            if hasattr(reference_point, "dtype") and reference_point.dtype.names else reference_point[:3]
+        ijk = self.getGridCoordinates(x, y, z).astype(np.int64)
+        rel = np.asarray(relative_coordinates, dtype=np.int64).reshape(3, -1)
+        lo, hi = self.min_b - ijk, self.getMaxBoxCoordinates() - ijk
+        out = []
+        for c in range(rel.shape[1]):
+            d = rel[:, c]
+            out.append(self.getCentroidIndexAt(ijk + d) if (lo <= d).all() and (hi >= d).all() else -1)
+        return out
+
+    def getLeafLayout(self):
+        if self._layout is None:
+            return np.zeros(0, dtype=np.int32)
+        full = np.full(int(np.prod(self.div_b.astype(np.int64))), -1, dtype=np.int32)
+        full[np.fromiter(self._layout.keys(), dtype=np.int64)] = np.fromiter(self._layout.values(), dtype=np.int32)
+        return full
 
     def filter(self):
         out = PointCloud()
@@ -559,8 +621,14 @@ class VoxelGrid:
             print("[applyFilter] No input dataset given")
             return out
         pts = self.input.points if isinstance(self.input, PointCloud) else self.input
-        r = self.ctx.voxel_grid(pts, self.leaf, self.downsample_all_data)
+        r = self.ctx.voxel_grid(pts, self.leaf, self.downsample_all_data, want_cells=self.save_leaf_layout)
         self.min_b, self.div_b = r["min_b"], r["div_b"]
+        self._layout = None
+        if self.save_leaf_layout:
+            cell = r["point_cell"].astype(np.int64)
+            cell = cell[cell[:, 0] >= 0]
+            idx = np.unique(cell.dot(self.getDivisionMultiplier()))  # outputs are in ascending cell index
+            self._layout = {int(v): i for i, v in enumerate(idx)}
         out.points = r["points"].copy()
         return out
 

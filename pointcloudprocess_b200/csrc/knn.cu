@@ -318,12 +318,26 @@ extern "C" int pcp_knn(const pcp_index* ix, const void* q, size_t nq, size_t qst
     W.out_pos = pos.p;
     W.out_d2 = (double*)o_d2.dptr;
     W.work_counter = counter.p;
+    DevBuf<unsigned long long> dbg;
+    if (getenv("PCP_KNN_DEBUG")) {
+        PCP_TRY(dbg.alloc(ctx, 17));
+        PCP_CUDA_TRY(ctx, cudaMemsetAsync(dbg.p, 0, 17 * 8, ctx->stream));
+        W.dbg = dbg.p;
+    }
     {
         StageTimer t(ctx, "knn.query_kernel");
         PCP_TRY(run_wknn(ctx, W, (uint32_t)nq));
         knn_export_kernel<<<pcp_blocks_for(nq * (size_t)k, 256), 256, 0, ctx->stream>>>(
             ix->rec, pos.p, nq * (size_t)k, k, (int32_t*)o_idx.dptr, (int32_t*)o_found.dptr);
         PCP_LAUNCH_CHECK(ctx);
+    }
+    if (W.dbg) {
+        unsigned long long h[17];
+        PCP_TRY(pcp_readback(ctx, h, dbg.p, 17 * 8));
+        fprintf(stderr, "[pcp knn] %zu external queries, settled at level:", nq);
+        for (int l = 0; l < 16; l++)
+            if (h[l]) fprintf(stderr, " %d:%llu", l, h[l]);
+        fprintf(stderr, "; %.0f points scanned per query (top level %d)\n", (double)h[16] / (double)nq, ix->grid.top_level);
     }
     PCP_TRY(o_idx.commit());
     PCP_TRY(o_d2.commit());

@@ -181,7 +181,10 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
         const int by = min(max(pcp_cell_coord(q.y, P.g.org[1], P.g.inv_h, 0), 0), P.g.dims[1] - 1);
         const int bz = min(max(pcp_cell_coord(q.z, P.g.org[2], P.g.inv_h, 0), 0), P.g.dims[2] - 1);
         int level = (U == INF) ? 1 : 0;
-        if (U < 0.f) U = INF;
+        if (U < 0.f) { // PCP_FAR_HINT: no bound, start level given
+            level = min((int)(-U - 1.0f), P.g.top_level);
+            U = INF;
+        }
         pcp_qcell Q;
         {
             const double tx = (q.x - P.g.org[0]) * P.g.inv_h, ty = (q.y - P.g.org[1]) * P.g.inv_h,

@@ -432,6 +432,8 @@ template <int CAP, int GS, int CAND> struct pcp_fd_smem {
     }
 };
 
+// far-list entries without a bound carry the level the far kernel should start at, as -(1 + level)
+#define PCP_FAR_HINT(level) (-1.0f - (float)(level))
 #define PCP_FD_OK 0
 #define PCP_FD_BEYOND 1 // fewer than kk candidates inside `top`, or list overflow: no bound known
 #define PCP_FD_AMBIG 2  // kk nearest found among the staged candidates but order / certification not provable in FP32
@@ -652,7 +654,11 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
         PCP_FK_DBG(9, total < (uint32_t)P.kk ? nwant : 0);
         unsigned okmask = 0;
         // lane j: upper bound of query j's k-th squared distance (+inf: none; -1: none, block too dense to stage)
-        float myU = (total > (uint32_t)CAND) ? -1.0f : __int_as_float(0x7f800000);
+        // (PCP_FAR_HINT: no bound, but a level to start from -- the block of this leaf's level holds too many points
+        // to stage, so the level below it is the first worth trying; or too few, so the level above it is)
+        float myU = (total > (uint32_t)CAND)  ? PCP_FAR_HINT(level > 0 ? level - 1 : 0)
+                    : (total < (uint32_t)P.kk) ? PCP_FAR_HINT(level + 1)
+                                               : __int_as_float(0x7f800000);
         if (staged) {
             if constexpr (FLAT) {
                 // the runs' table, then the block itself, flat over the candidates with PCP_FK_STAGE_U loads in

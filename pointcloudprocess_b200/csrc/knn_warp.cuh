@@ -24,6 +24,7 @@ struct pcp_wknn_params {
     uint32_t* out_pos; // [nq][k]
     double* out_d2;    // [nq][k] or NULL
     uint32_t* work_counter;
+    unsigned long long* dbg; // optional (PCP_KNN_DEBUG): [level] queries settled there, [16] points scanned
 };
 
 template <int KPL> struct pcp_wlist {
@@ -146,9 +147,14 @@ template <int KPL> static __global__ void __launch_bounds__(128) knn_warp_kernel
                     }
                 }
                 const double g2 = pcp_guarantee2(P.g, level, cx, cy, cz, qx, qy, qz);
+                if (P.dbg) {
+                    const unsigned scanned = __reduce_add_sync(0xffffffffu, hi - lo);
+                    if (lane == 0) atomicAdd(P.dbg + 16, (unsigned long long)scanned);
+                }
                 if (level == P.g.top_level || (kd < DBL_MAX && kd < g2)) break;
             }
             found = P.kk;
+            if (P.dbg && lane == 0) atomicAdd(P.dbg + min(level, 15), 1ull);
         }
         // write the list: entry e -> out[qi*k + e]
 #pragma unroll

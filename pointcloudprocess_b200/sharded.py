@@ -292,9 +292,21 @@ class ShardedPipeline:
                 self.bnd_cap = -nF + (-nF) // 4
             F = self.bnd_idx[:nF]
             qF = self.bnd_xyz[:nF]
-            qbytes = qF.view(t.uint8).view(-1)
-            # ---- exchange 2: the flagged queries go to both neighbours ----
-            q_l, q_r = yield (qbytes if has_l else None, qbytes if has_r else None)
+            # each flagged query goes only to the neighbour(s) whose halo it outreaches (a query sent to the far
+            # side would be a whole slab away from that rank's points: correct, but a search over everything)
+            kthF = self.kth[:m * 4].view(t.float32)[F.long()].contiguous()
+            side = []
+            for has, lo, hi in ((has_l, xlo - H, None), (has_r, None, xhi + H)):
+                if not has or nF == 0:
+                    side.append(None)
+                    continue
+                sub = t.empty(nF, dtype=t.int32, device="cuda")
+                sxyz = t.empty((nF, 3), dtype=t.float64, device="cuda")
+                c = ctx.select_boundary((qF.data_ptr(), nF, 24), 0, kthF.data_ptr(), lo, hi, nF, sub.data_ptr(),
+                                        sxyz.data_ptr())
+                side.append((sub[:c], sxyz[:c]))
+            # ---- exchange 2: the flagged queries ----
+            q_l, q_r = yield tuple(None if sd is None else sd[1].view(t.uint8).view(-1) for sd in side)
             answers = []
             for q in (q_l, q_r):
                 if q is None or q.numel() == 0:
@@ -315,12 +327,19 @@ class ShardedPipeline:
                 ix.knn_device(qF.data_ptr(), nF, 24, k, idx.data_ptr(), d2o.data_ptr())
                 xyz_lists = [pts[idx.view(-1).long().clamp(min=0), :3].contiguous().view(-1)]
                 d2_lists = [d2o.view(-1)]
-                for a in (a_l, a_r):
-                    if a is None or a.numel() == 0:
+                for a, sd in ((a_l, side[0]), (a_r, side[1])):
+                    if a is None or a.numel() == 0 or sd is None:
                         continue
-                    assert a.numel() == nF * k * 32, (a.numel(), nF, k)
-                    xyz_lists.append(a[:nF * k * 24].contiguous().view(t.float64))
-                    d2_lists.append(a[nF * k * 24:].contiguous().view(t.float64))
+                    rows = sd[0].long()
+                    c = rows.numel()
+                    assert a.numel() == c * k * 32, (a.numel(), c, k)
+                    # queries that were not sent to this side get an empty list (d2 = +inf)
+                    xyz_full = t.zeros((nF, k, 3), dtype=t.float64, device="cuda")
+                    d2_full = t.full((nF, k), math.inf, dtype=t.float64, device="cuda")
+                    xyz_full[rows] = a[:c * k * 24].contiguous().view(t.float64).view(c, k, 3)
+                    d2_full[rows] = a[c * k * 24:].contiguous().view(t.float64).view(c, k)
+                    xyz_lists.append(xyz_full.view(-1))
+                    d2_lists.append(d2_full.view(-1))
                 nlists = len(xyz_lists)
                 xyz_all, d2_all, pid = t.cat(xyz_lists), t.cat(d2_lists), F
                 ctx.features_merge(nF, k, nlists, xyz_all.data_ptr(), d2_all.data_ptr(), pid.data_ptr(),
@@ -328,7 +347,8 @@ class ShardedPipeline:
                 del xyz_all, d2_all, pid
         finally:
             ix.free()
-        self.stats = {"halo_m": H, "own": int(m), "halo_points": int(nl + nr), "boundary_queries": nF}
+        self.stats = {"halo_m": H, "own": int(m), "halo_points": int(nl + nr), "boundary_queries": nF,
+                      "sent": [0 if sd is None else int(sd[0].numel()) for sd in side]}
         self.last_m = m
         return m
 

@@ -22,10 +22,14 @@ static void test_voxel_grid()
     VoxelGrid<CloudItem> vg;
     vg.setInputCloud(cloud);
     vg.setLeafSize(1, 1, 1);
+    vg.setSaveLeafLayout(true);
     Cloud out;
     vg.filter(out);
     printf("voxel %zu\n", out.size());
     for (size_t i = 0; i < out.size() && i < 10; i++) printf("%.17g %.17g %.17g\n", out[i].x, out[i].y, out[i].z);
+    const int probe[3] = {4, 4, 4}, hole[3] = {4, 5, 4};
+    printf("layout %d %d %d %zu\n", vg.getCentroidIndexAt(probe), vg.getCentroidIndexAt(hole), vg.getCentroidIndex(out[7]),
+           vg.getLeafLayout().size());
 }
 
 static void test_kd_tree()

@@ -51,6 +51,8 @@ def test_reference_smoke_functions_known_answers(tmp_path):
         vals = [np.float32(c)] + [np.float32(0.1 * i) for i in range(10 * c, 10 * c + 10)]
         exp = sum(float(v) for v in vals) / 11.0
         assert [float(t) for t in lines[1 + c].split()] == [exp, exp, exp]
+    assert lines[11] == "layout 4 -1 7 1000"  # voxel_grid.h:595-706 accessors on the saved leaf layout
+    lines = lines[:11] + lines[12:]
     assert lines[11] == "knn 10"   # main_test.cpp:156-188: neighbours of the origin are 0..9 in order
     for i in range(10):
         idx, d2 = lines[12 + i].split()

@@ -338,3 +338,33 @@ def test_config0_features_on_a_cloud_loaded_from_compressed_pcd(ctx, orc, tmp_pa
         props, eig, lps = orc.features_knn(loaded.points, 20)[:3]
     assert_props_equal(got["props"], props)
     assert np.array_equal(got["eig"], eig, equal_nan=True)
+
+
+def test_voxel_grid_accessors_and_leaf_layout(ctx):
+    """voxel_grid.h:595-706 on main_test.cpp:126-154's cloud: 10 cells along the diagonal of a 10^3 grid."""
+    import pointcloudprocess_b200 as pcp
+    cloud = pcp.PointCloud()
+    for i in range(10):
+        cloud.push_back(i, i, i)
+    for i in range(100):
+        cloud.push_back(0.1 * i, 0.1 * i, 0.1 * i)
+    vg = pcp.VoxelGrid(ctx)
+    vg.setInputCloud(cloud)
+    vg.setLeafSize(1, 1, 1)
+    vg.setSaveLeafLayout(True)
+    out = vg.filter()
+    assert out.size() == 10
+    assert list(vg.getMinBoxCoordinates()) == [0, 0, 0] and list(vg.getMaxBoxCoordinates()) == [9, 9, 9]
+    assert list(vg.getNrDivisions()) == [10, 10, 10] and list(vg.getDivisionMultiplier()) == [1, 10, 100]
+    layout = vg.getLeafLayout()
+    assert layout.shape == (1000,) and (layout >= 0).sum() == 10
+    for c in range(10):
+        assert layout[111 * c] == c and vg.getCentroidIndexAt([c, c, c]) == c
+        assert vg.getCentroidIndex(out.points[c]) == c
+    assert vg.getCentroidIndexAt([0, 1, 0]) == -1 and vg.getCentroidIndexAt([10, 0, 0]) == -1
+    assert list(vg.getGridCoordinates(3.7, -0.2, 9.99)) == [3, 0, 9]
+    rel = np.array([[0, 1, -1, 1], [0, 1, -1, 0], [0, 1, -1, 0]])
+    assert vg.getNeighborCentroidIndices(out.points[0], rel) == [0, 1, -1, -1]
+    vg.setSaveLeafLayout(False)
+    vg.filter()
+    assert vg.getLeafLayout().size == 0 and vg.getCentroidIndexAt([0, 0, 0]) == -1

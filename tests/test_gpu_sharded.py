@@ -53,3 +53,8 @@ def test_sharded_pipeline_equals_single_device(ctx, world, n_total, halo, kind):
         bad = ~((a == b) | (np.isnan(a) & np.isnan(b)))
         assert not bad.any(), (f, int(bad.sum()), stats)
     assert sum(s["boundary_queries"] for s in stats) > 0  # the second exchange was exercised
+    for r, s in enumerate(stats):
+        # a flagged query goes to the side(s) it outreaches, not to both neighbours by default
+        assert max(s["sent"]) <= s["boundary_queries"] <= sum(s["sent"])
+        if 0 < r < world - 1 and s["boundary_queries"] > 50:
+            assert sum(s["sent"]) < 1.5 * s["boundary_queries"], s
