@@ -266,10 +266,17 @@ def run_gpu(args):
             featured += job.step_device()
         e1.record(stream)
         barrier()
-    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    ms_local = e0.elapsed_time(e1)
+    ms_total = max_over_ranks(ms_local)
     launches = ctx.launch_count() - l0
     stages = ctx.profile_get()
     ctx.profile(False)
+    per_rank = None
+    if world > 1:  # every rank's own clock and stage timers, for the report (host to host)
+        mine = {"ms_per_step": ms_local / args.steps, "stages": {st["name"]: round(st["ms"] / args.steps, 3) for st in stages},
+                "halo": job.halo_info()}
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, mine, group=comm.host_group)
     total_featured = sum_over_ranks(float(featured))
     ms_per_step = ms_total / args.steps
     value = total_featured / (ms_total * 1e-3)
@@ -332,6 +339,11 @@ def run_gpu(args):
                 "gpu_launches": int(launches), "clocks": clk.summary(), "roofline": roof, "cpu_baseline": cpu,
                 "fallback_queries_per_step": sum(s["bytes"] for s in stages if s["name"] == "knn.warp_kernel") / 72.0 / args.steps,
                 "stages_ms_per_step": {s["name"]: round(s["ms"] / args.steps, 4) for s in stages}}
+        if per_rank:
+            names = sorted({k for r in per_rank for k in r["stages"]})
+            line["per_rank_ms_per_step"] = [round(r["ms_per_step"], 3) for r in per_rank]
+            line["stages_ms_per_step_max_over_ranks"] = {k: max(r["stages"].get(k, 0.0) for r in per_rank) for k in names}
+            line["boundary_queries_per_rank"] = [(r["halo"] or {}).get("boundary_queries") for r in per_rank]
         print(json.dumps(line), flush=True)
     job.close()
     ctx.close()

@@ -68,7 +68,8 @@ typedef struct pcp_plan_segment {
 PCP_API int pcp_create(pcp_ctx** out, int cuda_device);
 PCP_API void pcp_destroy(pcp_ctx* ctx);
 PCP_API const char* pcp_last_error(const pcp_ctx* ctx); /* ctx may be NULL: error of a failed pcp_create */
-/* Run on a caller-owned stream (a cudaStream_t passed as void*); NULL restores the context's own stream. */
+/* Run on a caller-owned stream (a cudaStream_t passed as void*); NULL restores the context's own (non-blocking)
+ * stream.  To share the default stream with the caller pass cudaStreamLegacy ((cudaStream_t)0x1), not NULL. */
 PCP_API int pcp_set_stream(pcp_ctx* ctx, void* cuda_stream);
 PCP_API int pcp_synchronize(pcp_ctx* ctx);
 PCP_API int pcp_device_count(void);

@@ -130,7 +130,12 @@ class Context:
             pass
 
     def set_stream(self, cuda_stream):
-        self._check(self.L.pcp_set_stream(self.h, cuda_stream))
+        """cuda_stream: a cudaStream_t handle (int).  None restores the context's own stream.  0 -- the handle
+        torch reports for its default stream -- selects the legacy default stream explicitly (cudaStreamLegacy,
+        (cudaStream_t)1): a NULL handle would mean "own stream" to pcp_set_stream, and the library's kernels would
+        then race with the caller's work on stream 0."""
+        handle = None if cuda_stream is None else (int(cuda_stream) or 1)
+        self._check(self.L.pcp_set_stream(self.h, handle))
 
     def synchronize(self):
         self._check(self.L.pcp_synchronize(self.h))

@@ -18,6 +18,7 @@ torch.distributed (NCCL / gloo) and, for single-GPU parity tests, with all ranks
 """
 import ctypes as C
 import math
+import os
 
 import numpy as np
 
@@ -292,6 +293,9 @@ class ShardedPipeline:
                 self.bnd_cap = -nF + (-nF) // 4
             F = self.bnd_idx[:nF]
             qF = self.bnd_xyz[:nF]
+            check = os.environ.get("PCP_SHARD_CHECK")  # debugging aid: validate every index before it is used
+            if check and nF:
+                assert int(F.min()) >= 0 and int(F.max()) < m, ("F", self.rank, int(F.min()), int(F.max()), m, nF)
             # each flagged query goes only to the neighbour(s) whose halo it outreaches (a query sent to the far
             # side would be a whole slab away from that rank's points: correct, but a search over everything)
             kthF = self.kth[:m * 4].view(t.float32)[F.long()].contiguous()
@@ -305,6 +309,9 @@ class ShardedPipeline:
                 c = ctx.select_boundary((qF.data_ptr(), nF, 24), 0, kthF.data_ptr(), lo, hi, nF, sub.data_ptr(),
                                         sxyz.data_ptr())
                 side.append((sub[:c], sxyz[:c]))
+                if check and c:
+                    assert 0 <= c <= nF and int(sub[:c].min()) >= 0 and int(sub[:c].max()) < nF, \
+                        ("side", self.rank, c, nF, int(sub[:c].min()), int(sub[:c].max()))
             # ---- exchange 2: the flagged queries ----
             q_l, q_r = yield tuple(None if sd is None else sd[1].view(t.uint8).view(-1) for sd in side)
             answers = []
@@ -317,6 +324,8 @@ class ShardedPipeline:
                 idx = t.empty((nq, k), dtype=t.int32, device="cuda")
                 d2 = t.empty((nq, k), dtype=t.float64, device="cuda")
                 ix.knn_device(qq.data_ptr(), nq, 24, k, idx.data_ptr(), d2.data_ptr())
+                if check:
+                    assert int(idx.max()) < ntot and int(idx.min()) >= -1, ("answer idx", self.rank, int(idx.min()), int(idx.max()), ntot, nq)
                 xyz = pts[idx.view(-1).long().clamp(min=0), :3].contiguous()  # padded entries carry d2 = +inf
                 answers.append(t.cat([xyz.view(t.uint8).view(-1), d2.view(t.uint8).view(-1)]))
             # ---- exchange 3: candidate lists back to the owners ----
@@ -325,6 +334,8 @@ class ShardedPipeline:
                 idx = t.empty((nF, k), dtype=t.int32, device="cuda")
                 d2o = t.empty((nF, k), dtype=t.float64, device="cuda")
                 ix.knn_device(qF.data_ptr(), nF, 24, k, idx.data_ptr(), d2o.data_ptr())
+                if check:
+                    assert int(idx.max()) < ntot and int(idx.min()) >= -1, ("own idx", self.rank, int(idx.min()), int(idx.max()), ntot, nF)
                 xyz_lists = [pts[idx.view(-1).long().clamp(min=0), :3].contiguous().view(-1)]
                 d2_lists = [d2o.view(-1)]
                 for a, sd in ((a_l, side[0]), (a_r, side[1])):
