@@ -423,9 +423,12 @@ class PointCloud:
         return len(self.points)
 
     def push_back(self, x, y, z, rgba=0, stamp_id=0):
-        p = np.zeros(1, dtype=POINT_DTYPE)
-        p["x"], p["y"], p["z"], p["w"], p["rgba"], p["stamp_id"] = x, y, z, 1.0, rgba, stamp_id
-        self.points = np.concatenate([self.points, p])
+        pts = np.zeros(len(self.points) + 1, dtype=POINT_DTYPE)  # (np.concatenate would drop the record's padding)
+        for f in POINT_DTYPE.names:
+            pts[f][:-1] = self.points[f]
+        last = pts[-1:]
+        last["x"], last["y"], last["z"], last["w"], last["rgba"], last["stamp_id"] = x, y, z, 1.0, rgba, stamp_id
+        self.points = pts
 
 
 class io:
@@ -596,15 +599,20 @@ class VoxelGrid:
             return -1
         return self._layout.get(idx, -1)
 
+    @staticmethod
+    def _xyz(p):
+        if hasattr(p, "dtype") and p.dtype.names:
+            return float(p["x"]), float(p["y"]), float(p["z"])
+        if isinstance(p, np.void):  # a record of an unnamed dtype: xyz doubles come first
+            return tuple(np.frombuffer(p.tobytes()[:24], dtype=np.float64))
+        return tuple(float(v) for v in p[:3])
+
     def getCentroidIndex(self, p):
-        x, y, z = (p["x"], p["y"], p["z"]) if hasattr(p, "dtype") and p.dtype.names else p[:3]
-        return self.getCentroidIndexAt(self.getGridCoordinates(x, y, z))
+        return self.getCentroidIndexAt(self.getGridCoordinates(*self._xyz(p)))
 
     def getNeighborCentroidIndices(self, reference_point, relative_coordinates):
         """relative_coordinates: 3 x m integer offsets; -1 for cells outside the grid (voxel_grid.h:627-646)."""
-        x, y, z = (reference_point["x"], reference_point["y"], reference_point["z"]) \
-            if hasattr(reference_point, "dtype") and reference_point.dtype.names else reference_point[:3]
-        ijk = self.getGridCoordinates(x, y, z).astype(np.int64)
+        ijk = self.getGridCoordinates(*self._xyz(reference_point)).astype(np.int64)
         rel = np.asarray(relative_coordinates, dtype=np.int64).reshape(3, -1)
         lo, hi = self.min_b - ijk, self.getMaxBoxCoordinates() - ijk
         out = []
