@@ -66,10 +66,10 @@ template <int CAP, int GS, int CAND, bool FLAT> int launch_fknn_t(pcp_ctx* ctx, 
 // list capacity CAP >= k plus room for the candidates of the boundary bucket
 int launch_fknn(pcp_ctx* ctx, const pcp_fknn_params& P)
 {
-    if (P.kk <= 24 && getenv("PCP_FK_NOFLAT")) return launch_fknn_t<32, 8, 288, false>(ctx, P);
-    if (P.kk <= 24) return launch_fknn_t<32, 8, 288, true>(ctx, P);
-    if (P.kk <= 52) return launch_fknn_t<64, 8, 448, true>(ctx, P);
-    return launch_fknn_t<160, 8, 448, true>(ctx, P);
+    if (P.kk <= 24 && getenv("PCP_FK_NOFLAT")) return launch_fknn_t<32, 8, 320, false>(ctx, P);
+    if (P.kk <= 24) return launch_fknn_t<32, 8, 320, true>(ctx, P);
+    if (P.kk <= 52) return launch_fknn_t<64, 8, 480, true>(ctx, P);
+    return launch_fknn_t<160, 8, 480, true>(ctx, P);
 }
 
 template <int CAP> int launch_far_t(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)

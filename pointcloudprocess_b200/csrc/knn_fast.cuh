@@ -22,7 +22,8 @@
 #pragma once
 #include "knn_cell.cuh"
 
-#define PCP_FK_NB 64      // histogram buckets (last one = beyond range)
+#define PCP_FK_NB 64      // histogram buckets of the exact search (last one = beyond range)
+#define PCP_FD_NB 32      // ... of the dense kernel: 8 octaves below the certifiable radius, nearer ones share bucket 0
 #define PCP_FK_CAND 256   // staged candidates per item
 #define PCP_FK_WARPS 4
 #define PCP_FK_STAGE_U 2  // candidates a lane loads before it converts and stores them
@@ -167,6 +168,10 @@ struct pcp_fk_chunked {
 __device__ __forceinline__ int pcp_fk_bucket(float d2, int key0)
 {
     return min(max((__float_as_int(d2) >> 21) - key0, 0), PCP_FK_NB - 1);
+}
+__device__ __forceinline__ int pcp_fd_bucket(float d2, int key0)
+{
+    return min(max((__float_as_int(d2) >> 21) - key0, 0), PCP_FD_NB - 1);
 }
 // exclusive upper edge of bucket b (b <= 62)
 __device__ __forceinline__ float pcp_fk_edge(int b, int key0) { return __int_as_float((key0 + b + 1) << 21); }
@@ -392,14 +397,14 @@ template <class SM> __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_
 // FP32 only, coordinates relative to the item's cell origin (error ~1e-7 h, see pcp_fd_e1).  Queries whose FP32
 // ordering is not provably the exact one (two candidates closer in d2 than the error bound, or a k-th distance
 // too close to the certified radius) are not settled here: they go to the far list with their upper bound.
-// CAND: staged candidates per item.  288 candidates, lists for 4 queries of 32 entries and k = 20 come to 9472
+// CAND: staged candidates per item.  320 candidates, lists for 4 queries of 32 entries and k = 20 come to 9472
 // bytes per warp: 6 blocks of 4 warps per SM.  (Candidates stay 16-byte records: the 4 query groups of a warp read
 // the same 8 candidates per step, one shared-memory wavefront as LDS.128 against three for split x / y / z arrays.)
 template <int CAP, int GS, int CAND> struct pcp_fd_smem {
     static constexpr int NSET = 32 / GS;
     static_assert(CAND % 4 == 0 && CAND < 65536 && (NSET * CAP) % 2 == 0, "pcp_fd_smem: layout");
     float4* cand;    // [CAND]  x, y, z relative to the leaf origin, w = sorted position
-    uint32_t* hist;  // [NSET][PCP_FK_NB]
+    uint32_t* hist;  // [NSET][PCP_FD_NB]
     float* ld2;      // [NSET][CAP]
     uint16_t* lpos;  // [NSET][CAP]  candidate number
     uint32_t* tab;   // [64]  exclusive prefix of the staged runs' lengths (0xffffffff beyond the 27), first points
@@ -408,13 +413,13 @@ template <int CAP, int GS, int CAND> struct pcp_fd_smem {
     float* skd;      // [32]
     static __host__ __device__ size_t bytes(int k)
     {
-        return (size_t)CAND * 16 + (size_t)NSET * PCP_FK_NB * 4 + (size_t)NSET * CAP * 6 + 256 + (size_t)32 * k * 4 + 256;
+        return (size_t)CAND * 16 + (size_t)NSET * PCP_FD_NB * 4 + (size_t)NSET * CAP * 6 + 256 + (size_t)32 * k * 4 + 256;
     }
     __device__ pcp_fd_smem(unsigned char* base, int k)
     {
         cand = reinterpret_cast<float4*>(base);
         hist = reinterpret_cast<uint32_t*>(cand + CAND);
-        ld2 = reinterpret_cast<float*>(hist + NSET * PCP_FK_NB);
+        ld2 = reinterpret_cast<float*>(hist + NSET * PCP_FD_NB);
         lpos = reinterpret_cast<uint16_t*>(ld2 + NSET * CAP);
         tab = reinterpret_cast<uint32_t*>(lpos + NSET * CAP);
         nbr = tab + 64;
@@ -447,14 +452,14 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
                                              float g2, float e1, float& dku)
 {
     constexpr int SL = CAP / G;
-    constexpr int NBL = PCP_FK_NB / G;
+    constexpr int NBL = PCP_FD_NB / G;
     static_assert(NBL == 8 || NBL == 4, "pcp_fd_search: 8 or 16 lanes per query");
     const int gl = lane & (G - 1), gbase = lane & ~(G - 1), set = (G == 32) ? 0 : lane / G;
     const unsigned gmask = (G == 32) ? 0xffffffffu : ((1u << G) - 1u);
-    uint32_t* hist = S.hist + set * PCP_FK_NB;
+    uint32_t* hist = S.hist + set * PCP_FD_NB;
     float* ld2 = S.ld2 + set * CAP;
     uint16_t* lpos = S.lpos + set * CAP;
-    const int key0 = (__float_as_int(top) >> 21) - (PCP_FK_NB - 2);
+    const int key0 = (__float_as_int(top) >> 21) - (PCP_FD_NB - 2);
 #pragma unroll
     for (int i = 0; i < NBL; i++) hist[gl + i * G] = 0;
     __syncwarp();
@@ -466,8 +471,8 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
         const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
         // (the last bucket = beyond `top` is never counted: nothing is decided there, and it is the one address
         // most lanes would collide on)
-        const int b = pcp_fk_bucket(d2, key0);
-        if (i < T && active && b < PCP_FK_NB - 1) atomicAdd(&hist[b], 1u);
+        const int b = pcp_fd_bucket(d2, key0);
+        if (i < T && active && b < PCP_FD_NB - 1) atomicAdd(&hist[b], 1u);
     }
     __syncwarp();
     // ---- scan: bucket b* of the kk-th candidate; hist[b] becomes the write cursor (exclusive prefix) ----
@@ -493,7 +498,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     const unsigned bal = (__ballot_sync(0xffffffffu, incl >= (uint32_t)kk) >> gbase) & gmask;
     if (!bal && active) st = PCP_FD_BEYOND;
     const int L = bal ? __ffs(bal) - 1 : 0;
-    int myb = PCP_FK_NB;
+    int myb = PCP_FD_NB;
     uint32_t mym = 0;
     {
         uint32_t c = incl - tot;
@@ -502,7 +507,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
         for (int i = 0; i < NBL; i++) {
             ex[i] = c;
             c += hb[i];
-            if (myb == PCP_FK_NB && c >= (uint32_t)kk) myb = gl * NBL + i, mym = c;
+            if (myb == PCP_FD_NB && c >= (uint32_t)kk) myb = gl * NBL + i, mym = c;
         }
         uint4 a;
         a.x = ex[0], a.y = ex[1], a.z = ex[2], a.w = ex[3];
@@ -515,7 +520,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     }
     const int bstar = __shfl_sync(0xffffffffu, myb, gbase + L);
     const uint32_t m = __shfl_sync(0xffffffffu, mym, gbase + L); // candidates in buckets <= b*
-    if (st == PCP_FD_OK && (bstar >= PCP_FK_NB - 1 || m > (uint32_t)CAP)) st = PCP_FD_BEYOND;
+    if (st == PCP_FD_OK && (bstar >= PCP_FD_NB - 1 || m > (uint32_t)CAP)) st = PCP_FD_BEYOND;
     const bool live = st == PCP_FD_OK;
     __syncwarp();
     // ---- pass 2: scatter the candidates of buckets <= b* into the list, bucket by bucket ----
@@ -524,7 +529,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
         const float4 c = S.cand[i < T ? i : 0];
         const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
         const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-        const int b = pcp_fk_bucket(d2, key0);
+        const int b = pcp_fd_bucket(d2, key0);
         if (live && i < T && b <= bstar) {
             const uint32_t at = atomicAdd(&hist[b], 1u);
             ld2[at] = d2;
@@ -533,7 +538,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     }
     __syncwarp();
     // ---- rank inside the bucket (hist[b] is now the END of bucket b) ----
-    const float edge = pcp_fk_edge(min(bstar, PCP_FK_NB - 2), key0);
+    const float edge = pcp_fk_edge(min(bstar, PCP_FD_NB - 2), key0);
     const float delta = 4.0f * sqrtf(edge) * e1 + 4.0f * e1 * e1 + 1e-6f * edge;
     const float amb2 = 2.0f * delta;
     bool ambig = false;
@@ -543,7 +548,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
         const int e = s * G + gl;
         if (live && e < (int)m) {
             const float d = ld2[e];
-            const int b = pcp_fk_bucket(d, key0);
+            const int b = pcp_fd_bucket(d, key0);
             const uint32_t lo = b ? hist[b - 1] : 0u, hi = hist[b];
             uint32_t r = lo;
             // bucket edges: an entry this close to one may belong to the other side
