@@ -154,6 +154,43 @@ template <typename PointT> class KdTreeFLANN {
                           "KdTreeFLANN::radiusSearch");
         return (int)off[1];
     }
+    // the (cloud, index) and (index) overloads of kd_tree.h:446-505 / 538-601
+    int nearestKSearch(const PointCloud<PointT>& cloud, int index, int k, std::vector<int>& k_indices,
+                       std::vector<double>& k_sqr_distances) const
+    {
+        return nearestKSearch(cloud.points.at((size_t)index), k, k_indices, k_sqr_distances);
+    }
+    int nearestKSearch(int index, int k, std::vector<int>& k_indices, std::vector<double>& k_sqr_distances) const
+    {
+        return nearestKSearch(input_->points.at((size_t)index), k, k_indices, k_sqr_distances);
+    }
+    int radiusSearch(const PointCloud<PointT>& cloud, int index, double radius, std::vector<int>& k_indices,
+                     std::vector<double>& k_sqr_distances, unsigned int max_nn = 0) const
+    {
+        return radiusSearch(cloud.points.at((size_t)index), radius, k_indices, k_sqr_distances, max_nn);
+    }
+    int radiusSearch(int index, double radius, std::vector<int>& k_indices, std::vector<double>& k_sqr_distances,
+                     unsigned int max_nn = 0) const
+    {
+        return radiusSearch(input_->points.at((size_t)index), radius, k_indices, k_sqr_distances, max_nn);
+    }
+    // One launch for a whole cloud of queries -- what the reference's per-point loops (main_blend.cpp:306-326,
+    // extraction_tree.cpp:413-436: k = 1 closest points) become: row q of k_indices / k_sqr_distances holds the
+    // found[q] <= k neighbours of queries[q] (-1 / +inf padded).
+    void nearestKSearchBatch(const PointCloud<PointT>& queries, int k, std::vector<int>& k_indices,
+                             std::vector<double>& k_sqr_distances, std::vector<int>& found) const
+    {
+        const size_t nq = queries.points.size();
+        k_indices.assign(nq * (size_t)k, -1);
+        k_sqr_distances.assign(nq * (size_t)k, 0.0);
+        found.assign(nq, 0);
+        if (nq == 0 || k <= 0) return;
+        detail::check(detail::context(),
+                      pcp_knn(index_, queries.points.data(), nq, sizeof(PointT), k, k_indices.data(), k_sqr_distances.data(),
+                              found.data()),
+                      "KdTreeFLANN::nearestKSearchBatch");
+    }
+    PointCloudConstPtr getInputCloud() const { return input_; }
     const pcp_index* handle() const { return index_; }
 
   private:

@@ -48,6 +48,14 @@ static void test_kd_tree()
     int n = kdtree.nearestKSearch(q, 10, index, dis);
     printf("knn %d\n", n);
     for (int i = 0; i < n; i++) printf("%d %.17g\n", index[i], dis[i]);
+    // the batched form of main_blend.cpp:306-326's loop (closest point of every query, one launch)
+    std::vector<int> bi, bf;
+    std::vector<double> bd;
+    kdtree.nearestKSearchBatch(*cloud, 1, bi, bd, bf);
+    int self = 0;
+    for (size_t i = 0; i < cloud->size(); i++) self += bf[i] == 1 && bi[i] == (int)i && bd[i] == 0.0;
+    int n5 = kdtree.nearestKSearch(5, 3, index, dis); // (index) overload: point 5 and its two neighbours
+    printf("batch %d of %zu; by index %d: %d %d %d\n", self, cloud->size(), n5, index[0], index[1], index[2]);
     PointCloudHelper::remove_duplicate(cloud, 1.0f);
     printf("dedup %zu\n", cloud->size());
     std::shared_ptr<LAS_POINT_PROPERTY> props = CalculateFeature::calculate_plan_parameter_rpca(cloud, 0.15);

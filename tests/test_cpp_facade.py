@@ -58,6 +58,8 @@ def test_reference_smoke_functions_known_answers(tmp_path):
         idx, d2 = lines[12 + i].split()
         d = 0.1 * i
         assert int(idx) == i and float(d2) == (d * d + d * d) + d * d
+    assert lines[22] == "batch 100 of 100; by index 3: 5 4 6"  # ties by index: 4 before 6
+    lines = lines[:22] + lines[23:]
     # remove_duplicate centres on the centroid first (point_cloud_helper.cpp:42-63); the cell index truncates towards
     # zero (voxel_grid.h:74-86), so the 100 points on [-4.95, 4.95] fall into cells -4..4
     xs = np.array([0.1 * i for i in range(100)])
