@@ -353,13 +353,25 @@ class CalculateFeature {
         detail::check(c, st, "calculate_plan_parameter");
         return out;
     }
-    // calculate_feature.cpp:208: Radius is unused there too and k is 20 (:233).  The randomised hypothesis loop is
-    // not reproduced (it is not reproducible in the reference either); this is the plain PCA of the 20 neighbours.
+    // calculate_feature.cpp:208-368: the robust fit on the 20 nearest neighbours (Radius is unused there too, :233).
+    // The reference's rand() hypotheses are replaced by a counter-based generator keyed by `seed`
+    // (pcp_features_rpca), so the result is reproducible.
     static std::shared_ptr<LAS_POINT_PROPERTY> calculate_plan_parameter_rpca(CloudPtr cloud, double /*Radius*/,
-                                                                             float /*Pr*/ = 0.99f, float /*epi*/ = 0.5f)
+                                                                             float Pr = 0.99f, float epi = 0.5f,
+                                                                             uint64_t seed = 1)
     {
-        return calculate_plan_parameter(cloud, 0.0, 20);
+        std::shared_ptr<LAS_POINT_PROPERTY> out(new LAS_POINT_PROPERTY[cloud->points.size() ? cloud->points.size() : 1],
+                                                std::default_delete<LAS_POINT_PROPERTY[]>());
+        pcp_index* ix = nullptr;
+        pcp_ctx* c = detail::context();
+        detail::check(c, pcp_index_build(c, cloud->points.data(), cloud->points.size(), sizeof(CloudItem), 0.0, &ix),
+                      "calculate_plan_parameter_rpca");
+        int st = pcp_features_rpca(ix, 20, Pr, epi, seed, out.get());
+        pcp_index_free(ix);
+        detail::check(c, st, "calculate_plan_parameter_rpca");
+        return out;
     }
+    static int compute_iteration_number(float Pr, float epi) { return pcp_rpca_iterations(Pr, epi); }
 };
 
 // io::loadPCDFile / savePCDFile* (pcd_helper.h:1343-1497): 0 = ok, -1 = error with the message on stdout, as

@@ -156,6 +156,20 @@ PCP_API int pcp_features_knn_ex(const pcp_index* index, int k, int64_t query_lim
 /* Same with radius neighbourhoods (strict d2 < r*r, max_nn as above); counts (n) optional. */
 PCP_API int pcp_features_radius(const pcp_index* index, double r, uint32_t max_nn, void* props, double* eig3,
                                 float* lps3, int32_t* counts);
+/* CalculateFeature::calculate_plan_parameter_rpca (calculate_feature.cpp:208-368), the robust fit the reference
+ * ships: for every point, its k nearest neighbours (:230-233); `iterations` = compute_iteration_number(Pr, epi, 3)
+ * (:28-33) three-point hypotheses (:243-256); for each the h = (int)(2/3 N) neighbours nearest the hypothesis
+ * plane are refitted through their FLOAT coordinates (LAS_POINT_PROPERTY_sim, :258-275) and the refit with the
+ * smallest lambda3 wins (:277-289); the neighbours whose distance to it passes the MAD test Rz < 2.5 (:291-331)
+ * are fitted once more (:338-355); N <= 3 or <= 3 inliers give the fallback record (:356-363).
+ * The reference draws hypotheses with rand() under OpenMP (srand(time), :210,:249) and is not reproducible; here
+ * draw n of hypothesis i of point j is (splitmix64(seed*0x9E3779B97F4A7C15 + j*0xD1B54A32D192ED03 + 3i+n) >> 33) % N,
+ * so the result is a pure function of (cloud, k, Pr, epi, seed). Ties in the two sorts keep neighbour order and
+ * the first hypothesis with the smallest lambda3 wins (the reference's std::sort leaves both unspecified).
+ * k <= 32 (the reference uses 20). props: n records for the ORIGINAL n points. */
+PCP_API int pcp_features_rpca(const pcp_index* index, int k, float Pr, float epi, uint64_t seed, void* props);
+/* compute_iteration_number(Pr, epi, 3) (calculate_feature.cpp:28-33): 34 for the reference's 0.99 / 0.5. */
+PCP_API int pcp_rpca_iterations(float Pr, float epi);
 
 /* CalculateFeature::calculate_plan_parameter_h_points (calculate_feature.cpp:119-206) for nseg segments:
  * segment s is the points [seg_offsets[s], seg_offsets[s+1]) of pts. */

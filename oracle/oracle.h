@@ -81,6 +81,12 @@ void orc_features_knn(const void* pts, size_t n, size_t stride, int k, orc_las_p
                       double* eig3, float* lps3, int32_t* knn_idx, int threads);
 void orc_features_radius(const void* pts, size_t n, size_t stride, double r, uint32_t max_nn,
                          orc_las_point_property* props, double* eig3, float* lps3, int32_t* counts, int threads);
+/* a7: calculate_plan_parameter_rpca (calculate_feature.cpp:208-368) with a counter-based generator in place of
+ * rand(): 3-point hypotheses, h = 2N/3 subset fits on float-truncated coordinates, MAD inlier test, final fit. */
+int orc_rpca_iterations(float Pr, float epi);
+int orc_rpca_point(const double* nb_xyz, int N, int iterations, uint64_t seed, uint64_t j, orc_plan_segment* out);
+void orc_features_rpca(const void* pts, size_t n, size_t stride, int k, float Pr, float epi, uint64_t seed,
+                       orc_las_point_property* props, int threads);
 
 /* VoxelGrid::applyFilter, voxel_grid.h:811-1056 (no field filter). Returns M, or -1 on error.
  * out_pts has capacity n records of `stride` bytes (x,y,z double @0, rgba u32 @32, stamp_id u32 @36).

@@ -190,6 +190,24 @@ def features_knn(pts, k, want_eig=True, want_lps=True, want_idx=False, threads=0
     return props, eig, lps, idx
 
 
+def features_rpca(pts, k=20, Pr=0.99, epi=0.5, seed=1, threads=0):
+    """calculate_plan_parameter_rpca with the counter-based generator (oracle_knn.cpp); returns props."""
+    a, n, s = _pts(pts)
+    props = np.zeros(n, dtype=PROP_DTYPE)
+    f = lib().orc_features_rpca
+    f.restype = None
+    f.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_float, C.c_float, C.c_uint64, C.c_void_p, C.c_int]
+    f(_p(a), n, s, k, Pr, epi, seed, _p(props), threads)
+    return props
+
+
+def rpca_iterations(Pr=0.99, epi=0.5):
+    f = lib().orc_rpca_iterations
+    f.restype = C.c_int
+    f.argtypes = [C.c_float, C.c_float]
+    return f(Pr, epi)
+
+
 def features_radius(pts, r, max_nn=0, threads=0):
     a, n, s = _pts(pts)
     props = np.zeros(n, dtype=PROP_DTYPE)

@@ -396,6 +396,122 @@ void orc_features_knn(const void* pts, size_t n, size_t stride, int k, orc_las_p
     orc_kdtree_free(t);
 }
 
+// ---- calculate_plan_parameter_rpca, calculate_feature.cpp:208-368, with a counter-based generator -----------------
+// The reference draws its 3-point hypotheses with rand() under OpenMP (srand(time)): not reproducible run to run.
+// Here draw n of hypothesis i of point j is splitmix64(seed, j, i, n) % N; everything else follows the reference:
+// float-truncated neighbour coordinates in the h-subset (LAS_POINT_PROPERTY_sim is float, data_struct.h:181-187),
+// float point-to-plane distances computed from float-truncated coordinates (extraction_tree.cpp:47-64), MAD test.
+// Deviations (stated): the two std::sort calls are unstable in the reference -- ties here keep neighbour order;
+// the best hypothesis is the first with the smallest lambda3; no valid hypothesis (every draw repeated an index,
+// probability ~1e-28 for N = 20) gives the unfitted record instead of planes[0] on an empty vector.
+static inline uint64_t rpca_mix(uint64_t x)
+{
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+static inline int rpca_draw(uint64_t seed, uint64_t j, int i, int n, int N)
+{
+    return (int)((rpca_mix(seed * 0x9E3779B97F4A7C15ull + j * 0xD1B54A32D192ED03ull + (uint64_t)(i * 3 + n)) >> 33) % (uint64_t)N);
+}
+// TreeExtration::compute_distance_from_point_to_plane (extraction_tree.cpp:47-64): float products, double sums
+static inline float rpca_plane_dist(const double* p, float a, float b, float c, float d)
+{
+    const float x1 = (float)p[0], y1 = (float)p[1], z1 = (float)p[2];
+    const float gg = a * a + b * b + c * c;
+    const double g = std::sqrt((double)gg);
+    const double f1 = a * x1, f2 = b * y1, f3 = c * z1, f4 = d;
+    const double f = std::fabs(f1 + f2 + f3 + f4);
+    return (float)(f / g);
+}
+
+extern "C" int orc_rpca_iterations(float Pr, float epi)
+{
+    // compute_iteration_number (calculate_feature.cpp:28-33): log10 of a float, pow(float, int) in double
+    return (int)(std::log10(1 - Pr) / std::log10(1 - std::pow((double)(1 - epi), 3)));
+}
+
+extern "C" int orc_rpca_point(const double* nb, int N, int iterations, uint64_t seed, uint64_t j, orc_plan_segment* out)
+{
+    if (N <= 3) return 0; // :238
+    const int h_free = (int)(2.0 / 3 * N);
+    orc_plan_segment best;
+    bool have = false;
+    std::vector<float> dis(N);
+    std::vector<int> order(N);
+    std::vector<double> sub(3 * (size_t)std::max(h_free, 3));
+    for (int i = 0; i < iterations; i++) {
+        int num[3];
+        for (int n = 0; n < 3; n++) num[n] = rpca_draw(seed, j, i, n, N);
+        if (num[0] == num[1] || num[0] == num[2] || num[1] == num[2]) continue;
+        double p3[9];
+        for (int n = 0; n < 3; n++) std::memcpy(&p3[3 * n], &nb[3 * num[n]], 24);
+        orc_plan_segment a;
+        orc_plane_fit(p3, 3, &a); // calculate_plan_parameter_3points: the same arithmetic with h = 3
+        for (int n = 0; n < N; n++) {
+            dis[n] = rpca_plane_dist(&nb[3 * n], a.normal_x, a.normal_y, a.normal_z, a.Distance);
+            order[n] = n;
+        }
+        std::stable_sort(order.begin(), order.end(), [&](int x, int y) { return dis[x] < dis[y]; });
+        for (int n = 0; n < h_free; n++)
+            for (int c = 0; c < 3; c++) sub[3 * n + c] = (double)(float)nb[3 * order[n] + c]; // float members
+        orc_plane_fit(sub.data(), h_free, &a);
+        if (!have || a.min_value < best.min_value) best = a, have = true;
+    }
+    if (!have) return 0;
+    std::vector<float> d(N), t(N);
+    for (int n = 0; n < N; n++) d[n] = rpca_plane_dist(&nb[3 * n], best.normal_x, best.normal_y, best.normal_z, best.Distance);
+    std::vector<float> srt(d);
+    std::sort(srt.begin(), srt.end());
+    const float median = srt[N / 2];
+    for (int n = 0; n < N; n++) t[n] = std::fabs(d[n] - median);
+    srt = t;
+    std::sort(srt.begin(), srt.end());
+    const float MAD = (float)(1.4826 * srt[N / 2]);
+    std::vector<double> fin;
+    for (int n = 0; n < N; n++) {
+        bool keep = true;
+        if (MAD != 0) {
+            const float Rz = t[n] / MAD;
+            keep = Rz < 2.5;
+        }
+        if (keep) fin.insert(fin.end(), &nb[3 * n], &nb[3 * n] + 3);
+    }
+    const int m = (int)(fin.size() / 3);
+    if (m <= 3) return 0;
+    orc_plane_fit(fin.data(), m, out);
+    return 1;
+}
+
+void orc_features_rpca(const void* pts, size_t n, size_t stride, int k, float Pr, float epi, uint64_t seed,
+                       orc_las_point_property* props, int threads)
+{
+    orc_kdtree* t = orc_kdtree_build(pts, n, stride);
+    int kk = (int)std::min<size_t>((size_t)std::max(k, 0), t->map.size());
+    const int iterations = orc_rpca_iterations(Pr, epi);
+#ifdef _OPENMP
+    if (threads <= 0) threads = omp_get_max_threads();
+#endif
+#pragma omp parallel for schedule(dynamic, 256) num_threads(threads)
+    for (long long j = 0; j < (long long)n; j++) {
+        const double* qp = P(pts, j, stride);
+        std::vector<Cand> s;
+        if (finite3(qp) && kk > 0) {
+            KnnVisitor v(kk, t->map.data());
+            t->search(0, qp, v);
+            v.top.sorted(s);
+        }
+        const int N = (int)s.size();
+        std::vector<double> xyz(3 * (size_t)std::max(N, 1));
+        for (int c = 0; c < N; c++) std::memcpy(&xyz[3 * c], P(pts, s[c].idx, stride), 24);
+        orc_plan_segment pl;
+        const int fitted = orc_rpca_point(xyz.data(), N, iterations, seed, (uint64_t)j, &pl);
+        fill_props(&props[j], (int32_t)j, fitted ? &pl : nullptr);
+    }
+    orc_kdtree_free(t);
+}
+
 void orc_features_radius(const void* pts, size_t n, size_t stride, double r, uint32_t max_nn,
                          orc_las_point_property* props, double* eig3, float* lps3, int32_t* counts, int threads)
 {

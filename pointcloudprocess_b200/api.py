@@ -395,6 +395,18 @@ class Index:
                                                        _ptr(counts)))
         return ret
 
+    def features_rpca(self, k=20, pr=0.99, epi=0.5, seed=1, props=None):
+        """calculate_plan_parameter_rpca (calculate_feature.cpp:208-368) with a counter-based hypothesis
+        generator (include/pcp_cuda.h: pcp_features_rpca).  Returns the props records (host array unless a
+        device array is passed)."""
+        n = self.n_orig
+        ret = props
+        if props is None:
+            props = ret = np.zeros(n, dtype=PROP_DTYPE)
+        self.ctx._check(self.ctx.L.pcp_features_rpca(self.h, int(k), float(pr), float(epi), int(seed) & (2**64 - 1),
+                                                     _ptr(props)))
+        return ret
+
 
 # ---- reference-shaped classes ------------------------------------------------------------------------
 _default_ctx = None
@@ -667,11 +679,22 @@ class CalculateFeature:
         finally:
             ix.free()
 
-    def calculate_plan_parameter_rpca(self, cloud, radius, pr=0.99, epi=0.5):
-        """Signature of calculate_feature.cpp:208; like the reference it ignores `radius` and uses k = 20
-        (:233).  The randomised hypothesis loop is not reproduced (it is not reproducible run to run in the
-        reference either, :210,:249); this is the deterministic plain-PCA result on the 20 neighbours."""
-        return self.calculate_plan_parameter(cloud, None, 20)
+    def calculate_plan_parameter_rpca(self, cloud, radius, pr=0.99, epi=0.5, seed=1):
+        """calculate_feature.cpp:208-368: the robust fit (3-point hypotheses, h-subset refit, MAD inliers) on the
+        20 nearest neighbours; like the reference it ignores `radius` (:233 uses k = 20).  The reference's rand()
+        hypotheses are replaced by a counter-based generator keyed by `seed`, so the result is reproducible and
+        is checked bit for bit by the parity tests."""
+        pts = cloud.points if isinstance(cloud, PointCloud) else cloud
+        ix = Index(self.ctx, pts)
+        try:
+            return ix.features_rpca(20, pr, epi, seed)
+        finally:
+            ix.free()
+
+    @staticmethod
+    def compute_iteration_number(pr, epi, ctx=None):
+        """calculate_feature.cpp:28-33 for 3-point hypotheses."""
+        return (ctx or default_context()).L.pcp_rpca_iterations(float(pr), float(epi))
 
 
 class PointCloudHelper:

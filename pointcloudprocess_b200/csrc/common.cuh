@@ -27,7 +27,7 @@ struct pcp_ctx {
     cudaStream_t stream = nullptr;
     cudaMemPool_t pool = nullptr;
     std::string err;
-    std::mutex mu;
+    std::recursive_mutex mu; // recursive: entry points compose (pcp_features_rpca calls pcp_features_knn_ex)
     bool profile = false;
     std::vector<pcp_stage_rec> stages;
     int64_t launches = 0;

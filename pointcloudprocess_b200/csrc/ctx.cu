@@ -366,7 +366,7 @@ static int lane_open(pcp_ctx* ctx, int lane)
 int pcp_copy_async(pcp_ctx* ctx, int lane, void* dst, const void* src, size_t bytes)
 {
     if (!ctx || (bytes && (!dst || !src))) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_copy_async: bad argument");
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_TRY(lane_open(ctx, lane));
     PCP_CUDA_TRY(ctx, cudaEventRecord(ctx->lane_in[lane], ctx->stream));
     PCP_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->lane[lane], ctx->lane_in[lane], 0));
@@ -382,7 +382,7 @@ int pcp_copy_async(pcp_ctx* ctx, int lane, void* dst, const void* src, size_t by
 int pcp_copy_fence(pcp_ctx* ctx, int lane)
 {
     if (!ctx) return PCP_ERR_INVALID;
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_TRY(lane_open(ctx, lane));
     PCP_CUDA_TRY(ctx, cudaEventRecord(ctx->lane_out[lane], ctx->lane[lane]));
     PCP_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->lane_out[lane], 0));
@@ -394,7 +394,7 @@ int pcp_copy_wait(pcp_ctx* ctx, int lane)
     if (!ctx) return PCP_ERR_INVALID;
     cudaStream_t s = nullptr;
     {
-        std::lock_guard<std::mutex> lock(ctx->mu);
+        std::lock_guard<std::recursive_mutex> lock(ctx->mu);
         PCP_TRY(lane_open(ctx, lane));
         s = ctx->lane[lane];
     }

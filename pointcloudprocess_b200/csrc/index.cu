@@ -546,7 +546,7 @@ extern "C" {
 int pcp_index_build(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double cell_size, pcp_index** out)
 {
     if (!ctx || !out || stride < 24 || (n && !pts)) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_index_build: bad argument");
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in;
     PCP_TRY(in.open(ctx, pts, n * stride));
@@ -556,7 +556,7 @@ int pcp_index_build(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, doub
 void pcp_index_free(pcp_index* index)
 {
     if (!index) return;
-    std::lock_guard<std::mutex> lock(index->ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(index->ctx->mu);
     cudaSetDevice(index->ctx->device);
     index_release(index);
 }

@@ -112,7 +112,7 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
     if (!ix || !props || k < 1) return pcp_fail(ix ? ix->ctx : nullptr, PCP_ERR_INVALID, "pcp_features_knn: bad argument");
     pcp_ctx* ctx = ix->ctx;
     if (k > 128) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_features_knn: k > 128 is not supported");
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const size_t n0 = ix->n_orig, nv = ix->n;
     if (n0 == 0) return PCP_OK;
@@ -291,7 +291,7 @@ extern "C" int pcp_knn(const pcp_index* ix, const void* q, size_t nq, size_t qst
     if (k > 128) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_knn: k > 128 is not supported");
     if (nq > 0xfffffff0ull) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_knn: too many queries in one call");
     if (nq == 0) return PCP_OK;
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in;
     OutStage o_idx, o_d2, o_found;

@@ -58,7 +58,7 @@ extern "C" int pcp_plane_fit(pcp_ctx* ctx, const void* pts, size_t stride, const
     if (!ctx || stride < 24 || (nseg && (!pts || !seg_offsets || !out)))
         return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_plane_fit: bad argument");
     if (nseg == 0) return PCP_OK;
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage off;
     PCP_TRY(off.open(ctx, seg_offsets, (nseg + 1) * 8));

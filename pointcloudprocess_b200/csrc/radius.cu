@@ -240,7 +240,7 @@ extern "C" int pcp_radius_count(const pcp_index* ix, const void* q, size_t nq, s
     if (!ix || !offsets || qstride < 24 || (nq && !q) || !(r >= 0))
         return pcp_fail(ix ? ix->ctx : nullptr, PCP_ERR_INVALID, "pcp_radius_count: bad argument");
     pcp_ctx* ctx = ix->ctx;
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in;
     OutStage out;
@@ -278,7 +278,7 @@ extern "C" int pcp_radius_fill(const pcp_index* ix, const void* q, size_t nq, si
         return pcp_fail(ix ? ix->ctx : nullptr, PCP_ERR_INVALID, "pcp_radius_fill: bad argument");
     pcp_ctx* ctx = ix->ctx;
     if (nq == 0 || ix->n == 0) return PCP_OK;
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in, uoff;
     PCP_TRY(in.open(ctx, q, nq * qstride));
@@ -360,7 +360,7 @@ extern "C" int pcp_features_radius(const pcp_index* ix, double r, uint32_t max_n
     if (max_nn != 0 && max_nn <= ix->n)
         return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_features_radius: a max_nn cap is not supported by the fused path; "
                                               "use pcp_radius_count/fill + pcp_plane_fit");
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     const size_t n0 = ix->n_orig, nv = ix->n;
     if (n0 == 0) return PCP_OK;

@@ -113,7 +113,7 @@ int pcp_bbox_host(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, pcp_b
 extern "C" int pcp_minmax(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double mn[3], double mx[3])
 {
     if (!ctx || !mn || !mx || stride < 24) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_minmax: bad argument");
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in;
     PCP_TRY(in.open(ctx, pts, n * stride));

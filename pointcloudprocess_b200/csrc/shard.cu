@@ -85,7 +85,7 @@ extern "C" int pcp_serial_sum(pcp_ctx* ctx, const void* pts, size_t n, size_t st
 {
     if (!ctx || !sum3 || stride < 24 || (n && !pts)) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_serial_sum: bad argument");
     if (n == 0) return PCP_OK;
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in;
     PCP_TRY(in.open(ctx, pts, n * stride));
@@ -109,7 +109,7 @@ extern "C" int pcp_column_histogram(pcp_ctx* ctx, const void* pts, size_t n, siz
     if (!ctx || !hist_inout || stride < 24 || axis < 0 || axis > 2 || nbins < 1 || cols_per_bin < 1 || (n && !pts))
         return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_column_histogram: bad argument");
     if (n == 0) return PCP_OK;
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in;
     OutStage h;
@@ -129,7 +129,7 @@ static int select_impl(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, c
     *m = 0;
     if (n == 0) return PCP_OK;
     if (n > 0xfffffff0ull) return pcp_fail(ctx, PCP_ERR_RANGE, "select: too many points");
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in;
     OutStage o;
@@ -228,7 +228,7 @@ extern "C" int pcp_select_boundary(pcp_ctx* ctx, const void* pts, size_t m, size
     *count = 0;
     if (m == 0 || (!has_lo && !has_hi)) return PCP_OK;
     if (m > 0x7ffffff0ull) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_select_boundary: too many points");
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in, kin;
     OutStage oi, ox;
@@ -343,7 +343,7 @@ extern "C" int pcp_features_merge(pcp_ctx* ctx, size_t nq, int k, int nlists, co
     if (!ctx || k < 1 || nlists < 1 || nlists > 4 || (nq && (!xyz_lists || !d2_lists || !point_id || !props)))
         return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_features_merge: bad argument");
     if (nq == 0) return PCP_OK;
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     if (pcp_classify(ctx, props) != PCP_PTR_DEVICE || (eig3 && pcp_classify(ctx, eig3) != PCP_PTR_DEVICE) ||
         (lps3 && pcp_classify(ctx, lps3) != PCP_PTR_DEVICE))

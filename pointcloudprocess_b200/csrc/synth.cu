@@ -158,7 +158,7 @@ extern "C" int pcp_synth_cloud(pcp_ctx* ctx, int kind, uint64_t n_total, uint64_
     if (!ctx || kind < 0 || kind > 4 || (n && !out_pts) || first + n > n_total)
         return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_synth_cloud: bad argument");
     if (n == 0) return PCP_OK;
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     OutStage o;
     PCP_TRY(o.open(ctx, out_pts, n * 48));

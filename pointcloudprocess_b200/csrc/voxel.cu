@@ -277,7 +277,7 @@ extern "C" int pcp_voxel_grid(pcp_ctx* ctx, const void* pts, size_t n, size_t st
         return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_voxel_grid: bad argument");
     if (downsample_all && stride < 40)
         return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_voxel_grid: downsample_all needs rgba/stamp_id (stride >= 40)");
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in;
     OutStage out, pc, cc;
@@ -298,7 +298,7 @@ extern "C" int pcp_voxel_grid(pcp_ctx* ctx, const void* pts, size_t n, size_t st
 extern "C" int pcp_centroid(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double c[3], uint64_t* count)
 {
     if (!ctx || !c || stride < 24) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_centroid: bad argument");
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in;
     PCP_TRY(in.open(ctx, pts, n * stride));
@@ -323,7 +323,7 @@ static int remove_duplicate_impl(pcp_ctx* ctx, void* pts_inout, size_t* n_inout,
 {
     size_t n = *n_inout;
     if (n == 0) return PCP_OK;
-    std::lock_guard<std::mutex> lock(ctx->mu);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     OutStage io; // in-place: host clouds are staged in, filtered on the device, staged back
     PCP_TRY(io.open(ctx, pts_inout, n * stride, true));

@@ -62,6 +62,23 @@ static void test_kd_tree()
     printf("props %d %.9g\n", props.get()[0].PointID, props.get()[0].curvature);
 }
 
+// calculate_plan_parameter_rpca (calculate_feature.cpp:208-368) on a jittered plane; the Python side of the test
+// builds the same cloud and compares the FNV-1a hash of the records with the oracle's
+static void test_rpca()
+{
+    CloudPtr cloud(new Cloud);
+    for (int i = 0; i < 2000; i++) {
+        CloudItem p;
+        p.x = 0.01 * (i % 50), p.y = 0.01 * (i / 50), p.z = 0.001 * ((i * 7919) % 13);
+        cloud->push_back(p);
+    }
+    std::shared_ptr<LAS_POINT_PROPERTY> props = CalculateFeature::calculate_plan_parameter_rpca(cloud, 0.15, 0.99f, 0.5f, 4);
+    unsigned long long h = 1469598103934665603ull;
+    const unsigned char* b = reinterpret_cast<const unsigned char*>(props.get());
+    for (size_t i = 0; i < cloud->size() * sizeof(LAS_POINT_PROPERTY); i++) h = (h ^ b[i]) * 1099511628211ull;
+    printf("rpca %d %zu %llu\n", CalculateFeature::compute_iteration_number(0.99f, 0.5f), sizeof(LAS_POINT_PROPERTY), h);
+}
+
 // main_test.cpp:188-208 (test_double_io): ten points at pi*i saved as a binary PCD and loaded back
 static int test_double_io(const char* path)
 {
@@ -87,6 +104,7 @@ int main(int argc, char** argv)
     try {
         test_voxel_grid();
         test_kd_tree();
+        test_rpca();
     } catch (const std::exception& e) {
         printf("error: %s\n", e.what());
         return 3;

@@ -66,3 +66,12 @@ def test_reference_smoke_functions_known_answers(tmp_path):
     cells = np.trunc((xs - xs.mean()) / 1.0)
     assert lines[22] == "dedup %d" % len(np.unique(cells)) == "dedup 9"
     assert lines[23].startswith("props 0 ")
+    # calculate_plan_parameter_rpca through the C++ mirror == the oracle, record bytes hashed (FNV-1a)
+    from oracle import oracle as orc
+    i = np.arange(2000)
+    P = np.c_[0.01 * (i % 50), 0.01 * (i // 50), 0.001 * ((i * 7919) % 13)]
+    ref = orc.features_rpca(P, 20, 0.99, 0.5, 4).tobytes()
+    h = 1469598103934665603
+    for b in ref:
+        h = ((h ^ b) * 1099511628211) & (2**64 - 1)
+    assert lines[24] == "rpca 34 48 %d" % h

@@ -368,3 +368,48 @@ def test_voxel_grid_accessors_and_leaf_layout(ctx):
     vg.setSaveLeafLayout(False)
     vg.filter()
     assert vg.getLeafLayout().size == 0 and vg.getCentroidIndexAt([0, 0, 0]) == -1
+
+
+# ---- calculate_plan_parameter_rpca (calculate_feature.cpp:208-368) ------------------------------------------
+@pytest.mark.parametrize("kind,n,k,seed", [("city", 100000, 20, 1), ("strip", 50000, 20, 7), ("forest", 50000, 20, 3),
+                                           ("uniform_cube", 20000, 12, 1), ("city", 40000, 32, 2**63 + 5)])
+def test_features_rpca_match_oracle_bit_exact(ctx, orc, kind, n, k, seed):
+    import pointcloudprocess_b200 as pcp
+    cloud = ctx.synth_cloud(kind, n, seed=33)
+    ix = pcp.Index(ctx, cloud)
+    got = ix.features_rpca(k, 0.99, 0.5, seed)
+    ref = orc.features_rpca(cloud, k, 0.99, 0.5, seed)
+    assert_props_equal(got, ref)
+    assert got.tobytes() == ref.tobytes()
+    # a different seed gives different hypotheses; the same seed the same bytes
+    assert ix.features_rpca(k, 0.99, 0.5, seed).tobytes() == got.tobytes()
+    assert ix.features_rpca(k, 0.99, 0.5, seed + 1 if seed < 2**63 else 1).tobytes() != got.tobytes()
+    ix.free()
+
+
+def test_features_rpca_other_probabilities_nan_points_and_tiny_clouds(ctx, orc):
+    import pointcloudprocess_b200 as pcp
+    cloud = ctx.synth_cloud("city", 30000, seed=4)
+    cloud["x"][::97] = np.nan  # dropped from the index: fallback record, neighbours renumbered like the reference
+    ix = pcp.Index(ctx, cloud)
+    for pr, epi in ((0.9, 0.5), (0.999, 0.3), (0.99, 0.0)):
+        assert pcp.CalculateFeature.compute_iteration_number(pr, epi, ctx) == orc.rpca_iterations(pr, epi)
+    got = ix.features_rpca(20, 0.9, 0.5, 9)
+    ref = orc.features_rpca(cloud, 20, 0.9, 0.5, 9)
+    assert got.tobytes() == ref.tobytes()
+    assert (got["curvature"][::97] == 1.0).all()
+    ix.free()
+    for n in (1, 3, 4, 5, 19):
+        P = cloud_uniform(n, 8)
+        ix = pcp.Index(ctx, P)
+        assert ix.features_rpca(20).tobytes() == orc.features_rpca(P, 20).tobytes(), n
+        ix.free()
+    with pytest.raises(pcp.PcpError):
+        pcp.Index(ctx, cloud_uniform(100, 1)).features_rpca(33)
+
+
+def test_calculate_plan_parameter_rpca_mirror(ctx, orc):
+    import pointcloudprocess_b200 as pcp
+    cloud = pcp.PointCloud(ctx.synth_cloud("city", 20000, seed=6))
+    props = pcp.CalculateFeature(ctx).calculate_plan_parameter_rpca(cloud, 0.3, 0.99, 0.5, seed=4)
+    assert props.tobytes() == orc.features_rpca(cloud.points, 20, 0.99, 0.5, 4).tobytes()
