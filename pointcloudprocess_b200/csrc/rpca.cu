@@ -77,8 +77,10 @@ __device__ __forceinline__ float rpca_dist(const double* nb, int n, const RpcaPl
 }
 
 // calculate_plan_parameter_h_points (:119-206) over the neighbours ord[0..h), optionally through the float members
-// of LAS_POINT_PROPERTY_sim (:262-266). One call site per use would triple the Jacobi code: not inlined.
-__device__ __noinline__ void rpca_fit(const double* nb, const unsigned char* ord, int h, int as_float, pcp_plane& out)
+// of LAS_POINT_PROPERTY_sim (:262-266). Inlined at its three call sites (the Jacobi solver inside stays one shared
+// function): as a __noinline__ function ptxas 12.9 -O3 produced a kernel whose MAD inlier test kept a point it
+// computed as an outlier (6 % of the records differed from the oracle; the same PTX assembled at -O1 was right).
+__device__ __forceinline__ void rpca_fit(const double* nb, const unsigned char* ord, int h, int as_float, pcp_plane& out)
 {
     double XAve = 0.0, YAve = 0.0, ZAve = 0.0;
     for (int e = 0; e < h; e++) {
