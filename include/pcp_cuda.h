@@ -171,6 +171,24 @@ PCP_API int pcp_features_rpca(const pcp_index* index, int k, float Pr, float epi
 /* compute_iteration_number(Pr, epi, 3) (calculate_feature.cpp:28-33): 34 for the reference's 0.99 / 0.5. */
 PCP_API int pcp_rpca_iterations(float Pr, float epi);
 
+/* TreeExtration::region_growning (extraction_tree.cpp:170-272), the consumer of the records above in
+ * point_segment (static.cpp:8-21: distanceT 0.5, cosfaT 0.94) -- SURVEY 8(f)-1.  Seeds are taken in ascending point
+ * index among the points never touched by an earlier region (curvature < curv_t, 0.005 at :194); a FIFO pops members
+ * and admits the still unsegmented ones among the k (50 at :222) nearest neighbours of each whose normal has
+ * |cos| > cosfaT with the FIRST seed's normal (:25-33, float) and whose float-truncated coordinates lie within
+ * distanceT of the popped member's plane (:47-64); a region of more than min_points (5 at :249) members is kept with
+ * the next label, a smaller one is dissolved (its members can be absorbed later but never seed).  Results are those
+ * of the sequential loop: labels, membership and member order.
+ * index: built over the cloud the records describe.  props: n records, read (normal, Distance, curvature, PointID)
+ * and SegmentID rewritten (-1 = UNSEGMENTATION).  seg_offsets (seg_cap + 1), seg_points (n: the members of kept
+ * regions in PlanSegment::PointID order), seg_plane (seg_cap x 4 floats: PlanSegment normal_x/y/z, Distance = the
+ * first seed's).  PCP_ERR_RANGE when more than seg_cap regions are found (n / (min_points + 1) + 1 always suffices).
+ * stats (optional, 6 values): seeds tried, single-block passes, all-block passes, candidates scanned, members kept,
+ * low-curvature points. */
+PCP_API int pcp_region_growing(const pcp_index* index, void* props, int k, double distanceT, double cosfaT,
+                               double curv_t, int min_points, int64_t* seg_offsets, size_t seg_cap,
+                               int32_t* seg_points, float* seg_plane, size_t* nseg, uint64_t* stats);
+
 /* CalculateFeature::calculate_plan_parameter_h_points (calculate_feature.cpp:119-206) for nseg segments:
  * segment s is the points [seg_offsets[s], seg_offsets[s+1]) of pts. */
 PCP_API int pcp_plane_fit(pcp_ctx* ctx, const void* pts, size_t stride, const int64_t* seg_offsets,

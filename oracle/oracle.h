@@ -88,6 +88,17 @@ int orc_rpca_point(const double* nb_xyz, int N, int iterations, uint64_t seed, u
 void orc_features_rpca(const void* pts, size_t n, size_t stride, int k, float Pr, float epi, uint64_t seed,
                        orc_las_point_property* props, int threads);
 
+/* TreeExtration::compute_distance_from_point_to_plane, extraction_tree.cpp:47-64 (float-truncated coordinates). */
+float orc_point_plane_distance(const double* xyz, float a, float b, float c, float d);
+/* TreeExtration::region_growning, extraction_tree.cpp:170-272 (k = 50, curv_t = 0.005, min_points = 5 there).
+ * props: n records; SegmentID is rewritten (-1 = UNSEGMENTATION, else the label of a kept region).
+ * Kept regions in the order they were found: seg_offsets (capacity n/ (min_points+1) + 2), seg_points (capacity n; the
+ * members in the order the reference pushes them into PlanSegment::PointID), seg_plane (4 floats per region: the
+ * first seed's normal and Distance).  Returns the number of kept regions. */
+int64_t orc_region_growing(const void* pts, size_t n, size_t stride, orc_las_point_property* props, int k,
+                           double distanceT, double cosfaT, double curv_t, int min_points,
+                           int64_t* seg_offsets, int32_t* seg_points, float* seg_plane, int threads);
+
 /* VoxelGrid::applyFilter, voxel_grid.h:811-1056 (no field filter). Returns M, or -1 on error.
  * out_pts has capacity n records of `stride` bytes (x,y,z double @0, rgba u32 @32, stamp_id u32 @36).
  * point_cell (n*3, or NULL): (i,j,k) of each input point, -1 for skipped points.

@@ -83,6 +83,10 @@ def _declare(L):
     L.orc_count_boundary_ties.argtypes = [vp, vp, sz, sz, i32, i32]
     L.orc_features_knn.argtypes = [vp, sz, sz, i32, vp, vp, vp, vp, i32]
     L.orc_features_radius.argtypes = [vp, sz, sz, dbl, C.c_uint32, vp, vp, vp, vp, i32]
+    L.orc_point_plane_distance.restype = C.c_float
+    L.orc_point_plane_distance.argtypes = [vp, C.c_float, C.c_float, C.c_float, C.c_float]
+    L.orc_region_growing.restype = i64
+    L.orc_region_growing.argtypes = [vp, sz, sz, vp, i32, dbl, dbl, dbl, i32, vp, vp, vp, i32]
     L.orc_voxel_grid.restype = i64
     L.orc_voxel_grid.argtypes = [vp, sz, sz, vp, i32, i32, vp, vp, vp, vp, vp, vp]
     L.orc_remove_duplicate.restype = i64
@@ -216,6 +220,21 @@ def features_radius(pts, r, max_nn=0, threads=0):
     counts = np.zeros(n, dtype=np.int32)
     lib().orc_features_radius(_p(a), n, s, float(r), max_nn, _p(props), _p(eig), _p(lps), _p(counts), threads)
     return props, eig, lps, counts
+
+
+def region_growing(pts, props, k=50, distanceT=0.5, cosfaT=0.94, curv_t=0.005, min_points=5, threads=0):
+    """TreeExtration::region_growning (extraction_tree.cpp:170-272).  Returns dict(props (copy with SegmentID),
+    offsets (nseg+1), points (members in PlanSegment::PointID order), planes (nseg x 4: seed normal, Distance))."""
+    a, n, stride = _pts(pts)
+    pr = np.ascontiguousarray(props, dtype=PROP_DTYPE).copy()
+    assert len(pr) == n
+    offsets = np.zeros(n // (max(min_points, 0) + 1) + 2, dtype=np.int64)
+    points = np.zeros(max(n, 1), dtype=np.int32)
+    planes = np.zeros((len(offsets), 4), dtype=np.float32)
+    nseg = lib().orc_region_growing(_p(a), n, stride, _p(pr), k, distanceT, cosfaT, curv_t, min_points, _p(offsets),
+                                    _p(points), _p(planes), threads)
+    return {"props": pr, "offsets": offsets[:nseg + 1].copy(), "points": points[:offsets[nseg]].copy(),
+            "planes": planes[:nseg].copy()}
 
 
 def voxel_grid(cloud, leaf, downsample_all=True, is_dense=True):

@@ -415,15 +415,10 @@ static inline int rpca_draw(uint64_t seed, uint64_t j, int i, int n, int N)
 {
     return (int)((rpca_mix(seed * 0x9E3779B97F4A7C15ull + j * 0xD1B54A32D192ED03ull + (uint64_t)(i * 3 + n)) >> 33) % (uint64_t)N);
 }
-// TreeExtration::compute_distance_from_point_to_plane (extraction_tree.cpp:47-64): float products, double sums
+// TreeExtration::compute_distance_from_point_to_plane (extraction_tree.cpp:47-64): oracle_segment.cpp
 static inline float rpca_plane_dist(const double* p, float a, float b, float c, float d)
 {
-    const float x1 = (float)p[0], y1 = (float)p[1], z1 = (float)p[2];
-    const float gg = a * a + b * b + c * c;
-    const double g = std::sqrt((double)gg);
-    const double f1 = a * x1, f2 = b * y1, f3 = c * z1, f4 = d;
-    const double f = std::fabs(f1 + f2 + f3 + f4);
-    return (float)(f / g);
+    return orc_point_plane_distance(p, a, b, c, d);
 }
 
 extern "C" int orc_rpca_iterations(float Pr, float epi)

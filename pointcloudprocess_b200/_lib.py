@@ -16,7 +16,7 @@ SYMBOLS = [
     "pcp_radius_fill", "pcp_features_knn", "pcp_features_radius", "pcp_plane_fit", "pcp_voxel_grid",
     "pcp_remove_duplicate", "pcp_features_knn_ex", "pcp_remove_duplicate_centred", "pcp_serial_sum",
     "pcp_column_histogram", "pcp_select_range", "pcp_select_columns", "pcp_select_boundary", "pcp_features_merge", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
-    "pcp_features_rpca", "pcp_rpca_iterations",
+    "pcp_features_rpca", "pcp_rpca_iterations", "pcp_region_growing",
     "pcp_pcd_read_header", "pcp_pcd_load", "pcp_pcd_save", "pcp_lzf_compress", "pcp_lzf_decompress",
 ]
 
@@ -85,6 +85,7 @@ def load():
         "pcp_features_radius": (i32, [vp, dbl, u32, vp, vp, vp, vp]),
         "pcp_features_rpca": (i32, [vp, i32, C.c_float, C.c_float, u64, vp]),
         "pcp_rpca_iterations": (i32, [C.c_float, C.c_float]),
+        "pcp_region_growing": (i32, [vp, vp, i32, dbl, dbl, dbl, i32, vp, sz, vp, vp, C.POINTER(sz), vp]),
         "pcp_plane_fit": (i32, [vp, vp, sz, vp, sz, vp]),
         "pcp_voxel_grid": (i32, [vp, vp, sz, sz, vp, i32, vp, C.POINTER(sz), vp, vp, vp, vp]),
         "pcp_remove_duplicate": (i32, [vp, vp, C.POINTER(sz), sz, C.c_float]),

@@ -407,6 +407,28 @@ class Index:
                                                      _ptr(props)))
         return ret
 
+    def region_growing(self, props, k=50, distanceT=0.5, cosfaT=0.94, curv_t=0.005, min_points=5, want_stats=False):
+        """TreeExtration::region_growning (extraction_tree.cpp:170-272) over this index's cloud (include/pcp_cuda.h:
+        pcp_region_growing).  `props` (host records) gets its SegmentID rewritten.  Returns dict(offsets, points,
+        planes[, stats]): the kept regions in the order found, members in PlanSegment::PointID order."""
+        n = self.n_orig
+        assert props.dtype == PROP_DTYPE and len(props) == n and props.flags.c_contiguous
+        cap = n // (max(int(min_points), 0) + 1) + 1
+        offsets = np.zeros(cap + 1, dtype=np.int64)
+        points = np.zeros(max(n, 1), dtype=np.int32)
+        planes = np.zeros((cap, 4), dtype=np.float32)
+        nseg = C.c_size_t(0)
+        stats = np.zeros(6, dtype=np.uint64)
+        self.ctx._check(self.ctx.L.pcp_region_growing(self.h, _ptr(props), int(k), float(distanceT), float(cosfaT),
+                                                      float(curv_t), int(min_points), _ptr(offsets), cap, _ptr(points),
+                                                      _ptr(planes), C.byref(nseg), _ptr(stats)))
+        m = nseg.value
+        ret = {"offsets": offsets[:m + 1].copy(), "points": points[:offsets[m]].copy(), "planes": planes[:m].copy()}
+        if want_stats:
+            ret["stats"] = dict(zip(("seeds", "solo_passes", "wide_passes", "scanned", "members", "candidates"),
+                                    (int(v) for v in stats)))
+        return ret
+
 
 # ---- reference-shaped classes ------------------------------------------------------------------------
 _default_ctx = None
@@ -695,6 +717,37 @@ class CalculateFeature:
     def compute_iteration_number(pr, epi, ctx=None):
         """calculate_feature.cpp:28-33 for 3-point hypotheses."""
         return (ctx or default_context()).L.pcp_rpca_iterations(float(pr), float(epi))
+
+
+class TreeExtration:
+    """extraction_tree.h (the reference spells it this way): region growing over the plane-fit records."""
+
+    def __init__(self, ctx=None):
+        self.ctx = ctx or default_context()
+
+    def region_growning(self, PointProperty, Cloud, distanceT, radius, cosfaT):
+        """extraction_tree.cpp:170-272.  `radius` is not read by the reference either (the search is k = 50, :222).
+        Returns the list of PlanSegment dicts (SegmentID, PointID array, normal_x/y/z, Distance) and rewrites
+        PointProperty[...]['SegmentID'] in place."""
+        pts = Cloud.points if isinstance(Cloud, PointCloud) else Cloud
+        ix = Index(self.ctx, pts)
+        try:
+            r = ix.region_growing(PointProperty, 50, distanceT, cosfaT)
+        finally:
+            ix.free()
+        segs = []
+        for s in range(len(r["planes"])):
+            pl = r["planes"][s]
+            segs.append({"SegmentID": s, "PointID": r["points"][r["offsets"][s]:r["offsets"][s + 1]],
+                         "normal_x": pl[0], "normal_y": pl[1], "normal_z": pl[2], "Distance": pl[3]})
+        return segs
+
+
+def point_segment(src_cloud, ctx=None, seed=1):
+    """static.cpp:8-21: robust plane fit of every point, then region growing with the reference's constants."""
+    ctx = ctx or default_context()
+    props = CalculateFeature(ctx).calculate_plan_parameter_rpca(src_cloud, 0.15, 0.99, 0.5, seed)
+    return TreeExtration(ctx).region_growning(props, src_cloud, 0.5, 0.2, 0.940), props
 
 
 class PointCloudHelper:

@@ -56,14 +56,14 @@ __device__ __forceinline__ int rpca_draw(unsigned long long base, int i, int n, 
 
 struct RpcaPlane {
     float a, b, c, d;
-    double g; // sqrt((double)(a*a + b*b + c*c)), the same for every point of one plane
+    double g; // (double)sqrtf(a*a + b*b + c*c), the same for every point of one plane
 };
 
 __device__ __forceinline__ void rpca_set_plane(RpcaPlane& q, const pcp_plane& pl)
 {
     q.a = pl.nx, q.b = pl.ny, q.c = pl.nz, q.d = pl.Distance;
     const float gg = __fadd_rn(__fadd_rn(__fmul_rn(q.a, q.a), __fmul_rn(q.b, q.b)), __fmul_rn(q.c, q.c));
-    q.g = sqrt((double)gg);
+    q.g = (double)__fsqrt_rn(gg); // sqrt(float): MSVC's float overload, widened (extraction_tree.cpp:57)
 }
 
 // TreeExtration::compute_distance_from_point_to_plane (extraction_tree.cpp:47-64): float coordinates, float
