@@ -6,6 +6,7 @@
 //   VoxelGrid<PointT>::setInputCloud / setLeafSize / filter                   voxel_grid.h:482-549, 429-448
 //   PointCloudHelper::remove_duplicate / getMinMax3D / compute3DCentroid      point_cloud_helper.h:16-90,192-230
 //   CalculateFeature::calculate_plan_parameter[_rpca|_h_points]               calculate_feature.h:11-16
+//   TreeExtration::region_growning, point_segment                             extraction_tree.cpp:170-272, static.cpp:8-21
 //
 // Every method computes on the GPU through libpcp_cuda.so; there is no CPU path behind this header.  Errors of
 // the library surface as std::runtime_error (the reference's own error style -- cout + return code -- is kept
@@ -52,6 +53,7 @@ static_assert(sizeof(PointXYZRGBA) == 48, "PointXYZRGBA must match point_type.h"
 // data_struct.h:161-173 and :188-198
 typedef pcp_point_property LAS_POINT_PROPERTY;
 struct PlanSegment {
+    int SegmentID = 0;
     float normal_x = 0, normal_y = 0, normal_z = 0;
     float min_value = 0, curvature = 0, Distance = 0;
     std::vector<int> PointID;
@@ -373,6 +375,59 @@ class CalculateFeature {
     }
     static int compute_iteration_number(float Pr, float epi) { return pcp_rpca_iterations(Pr, epi); }
 };
+
+// extraction_tree.h (the reference's spelling).  region_growning (extraction_tree.cpp:170-272): plane segments grown
+// over the 50-neighbour graph from seeds in ascending point index; PointProperty[i].SegmentID is rewritten
+// (-1 = UNSEGMENTATION) and the kept segments come back in the order found, members in the reference's FIFO order.
+// `radius` is not read by the reference either.
+class TreeExtration {
+  public:
+    std::vector<PlanSegment> region_growning(std::shared_ptr<LAS_POINT_PROPERTY> PointProperty, CloudPtr& cloud,
+                                             double distanceT, double /*radius*/, double cosfaT)
+    {
+        const size_t n = cloud->points.size();
+        std::vector<PlanSegment> result;
+        if (n == 0) return result;
+        const size_t cap = n / 6 + 1;
+        std::vector<int64_t> off(cap + 1);
+        std::vector<int32_t> members(n);
+        std::vector<float> plane(4 * cap);
+        size_t nseg = 0;
+        pcp_index* ix = nullptr;
+        pcp_ctx* c = detail::context();
+        detail::check(c, pcp_index_build(c, cloud->points.data(), n, sizeof(CloudItem), 0.0, &ix), "region_growning");
+        const int st = pcp_region_growing(ix, PointProperty.get(), 50, distanceT, cosfaT, 0.005, 5, off.data(), cap,
+                                          members.data(), plane.data(), &nseg, nullptr);
+        pcp_index_free(ix);
+        detail::check(c, st, "region_growning");
+        result.resize(nseg);
+        for (size_t s = 0; s < nseg; s++) {
+            PlanSegment& g = result[s];
+            g.SegmentID = (int)s;
+            g.normal_x = plane[4 * s], g.normal_y = plane[4 * s + 1], g.normal_z = plane[4 * s + 2], g.Distance = plane[4 * s + 3];
+            g.PointID.assign(members.begin() + off[s], members.begin() + off[s + 1]);
+        }
+        return result;
+    }
+};
+
+// static.cpp:8-21: robust per-point plane fit, then region growing, with the reference's constants
+inline void point_segment(CloudPtr src_cloud, std::vector<PlanSegment>& Segment, uint64_t seed = 1)
+{
+    std::shared_ptr<LAS_POINT_PROPERTY> PointProperty = CalculateFeature::calculate_plan_parameter_rpca(src_cloud, 0.15, 0.99f, 0.5f, seed);
+    TreeExtration Tree;
+    Segment = Tree.region_growning(PointProperty, src_cloud, 0.5, 0.2, 0.940);
+}
+
+// static.cpp:24-36: the points of the segments with more than 50 members
+inline void tree_filter(CloudPtr src_cloud, CloudPtr dst_cloud, uint64_t seed = 1)
+{
+    std::vector<PlanSegment> Segment;
+    point_segment(src_cloud, Segment, seed);
+    for (size_t i = 0; i < Segment.size(); i++)
+        if (Segment[i].PointID.size() > 50)
+            for (size_t j = 0; j < Segment[i].PointID.size(); j++) dst_cloud->push_back(src_cloud->points[Segment[i].PointID[j]]);
+}
 
 // io::loadPCDFile / savePCDFile* (pcd_helper.h:1343-1497): 0 = ok, -1 = error with the message on stdout, as
 // PCDReader / PCDWriter report.  Host-side code of the library (csrc/pcd_io.cu); no device is needed.

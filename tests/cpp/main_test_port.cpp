@@ -79,6 +79,29 @@ static void test_rpca()
     printf("rpca %d %zu %llu\n", CalculateFeature::compute_iteration_number(0.99f, 0.5f), sizeof(LAS_POINT_PROPERTY), h);
 }
 
+// point_segment / tree_filter (static.cpp:8-36) on two sheets: the Python side runs the oracle on the same cloud
+static void test_segment()
+{
+    CloudPtr cloud(new Cloud);
+    for (int i = 0; i < 6000; i++) {
+        CloudItem p;
+        const int a = i % 3000;
+        p.x = 0.02 * (a % 60) + 1e-4 * ((a * 7919) % 17), p.y = 0.02 * (a / 60), p.z = i < 3000 ? 1e-4 * ((a * 31) % 11) : 2.0 + 0.5 * p.x;
+        cloud->push_back(p);
+    }
+    std::vector<PlanSegment> seg;
+    point_segment(cloud, seg, 4);
+    unsigned long long h = 1469598103934665603ull;
+    size_t members = 0;
+    for (size_t s = 0; s < seg.size(); s++) {
+        members += seg[s].PointID.size();
+        for (size_t j = 0; j < seg[s].PointID.size(); j++) h = (h ^ (unsigned long long)(unsigned)seg[s].PointID[j]) * 1099511628211ull;
+    }
+    CloudPtr kept(new Cloud);
+    tree_filter(cloud, kept, 4);
+    printf("segment %zu %zu %llu %zu\n", seg.size(), members, h, kept->size());
+}
+
 // main_test.cpp:188-208 (test_double_io): ten points at pi*i saved as a binary PCD and loaded back
 static int test_double_io(const char* path)
 {
@@ -105,6 +128,7 @@ int main(int argc, char** argv)
         test_voxel_grid();
         test_kd_tree();
         test_rpca();
+        test_segment();
     } catch (const std::exception& e) {
         printf("error: %s\n", e.what());
         return 3;

@@ -75,3 +75,14 @@ def test_reference_smoke_functions_known_answers(tmp_path):
     for b in ref:
         h = ((h ^ b) * 1099511628211) & (2**64 - 1)
     assert lines[24] == "rpca 34 48 %d" % h
+    # point_segment + tree_filter (static.cpp:8-36) through the C++ mirror == the oracle's region growing
+    a = np.arange(6000) % 3000
+    x = 0.02 * (a % 60) + 1e-4 * ((a * 7919) % 17)
+    Q = np.c_[x, 0.02 * (a // 60), np.where(np.arange(6000) < 3000, 1e-4 * ((a * 31) % 11), 2.0 + 0.5 * x)]
+    rg = orc.region_growing(Q, orc.features_rpca(Q, 20, 0.99, 0.5, 4), 50, 0.5, 0.940)
+    h = 1469598103934665603
+    for v in rg["points"]:
+        h = ((h ^ int(v)) * 1099511628211) & (2**64 - 1)
+    sizes = np.diff(rg["offsets"])
+    assert lines[25] == "segment %d %d %d %d" % (len(sizes), len(rg["points"]), h, sizes[sizes > 50].sum())
+    assert len(sizes) >= 2

@@ -18,7 +18,7 @@ for which in ("knn", "rpca"):
         t = time.time()
         r = ix.region_growing(props.copy(), want_stats=True)
         dt = time.time() - t
-        st = {s[0]: round(s[1], 2) for s in ctx.profile_get() if s[0].startswith("segment") or s[0].startswith("knn")}
+        st = {s["name"]: round(s["ms"], 2) for s in ctx.profile_get() if s["name"].startswith(("segment", "knn"))}
         ctx.profile(False)
     sizes = np.diff(r["offsets"])
     print(which, "wall %.3f s" % dt, "segments", len(sizes), "largest", sorted(sizes)[-3:], "members", len(r["points"]), r["stats"], st)
