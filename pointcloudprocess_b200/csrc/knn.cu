@@ -57,6 +57,7 @@ template <int CAP, int GS, int CAND, bool FLAT> int launch_fknn_t(pcp_ctx* ctx, 
     unsigned blocks = (unsigned)(ctx->sm_count * per_sm);
     const unsigned need = pcp_blocks_for(P.nitem, PCP_FK_WARPS);
     if (blocks > need) blocks = need;
+    if (P.nitem_ptr) blocks = (unsigned)(ctx->sm_count * per_sm); // item count known on the device only
     if (P.dbg) fprintf(stderr, "[pcp knn] dense kernel: %zu bytes of shared memory per block, %d blocks per SM, %u blocks\n", smem, per_sm, blocks);
     knn_fast_kernel<CAP, GS, CAND, FLAT><<<blocks, 32 * PCP_FK_WARPS, smem, ctx->stream>>>(P);
     PCP_LAUNCH_CHECK(ctx);
@@ -70,6 +71,15 @@ int launch_fknn(pcp_ctx* ctx, const pcp_fknn_params& P)
     if (P.kk <= 24) return launch_fknn_t<32, 8, 320, true>(ctx, P);
     if (P.kk <= 52) return launch_fknn_t<64, 8, 480, true>(ctx, P);
     return launch_fknn_t<160, 8, 480, true>(ctx, P);
+}
+
+// the second pass over the items the first one found too dense to stage (k <= 24 only)
+#ifndef PCP_FK_CAND2
+#define PCP_FK_CAND2 800
+#endif
+int launch_fknn_dense2(pcp_ctx* ctx, const pcp_fknn_params& P)
+{
+    return launch_fknn_t<32, 8, PCP_FK_CAND2, true>(ctx, P);
 }
 
 template <int CAP> int launch_far_t(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)
@@ -184,9 +194,28 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 PCP_CUDA_TRY(ctx, cudaMemsetAsync(dbg.p, 0, 24 * 8, ctx->stream));
                 P.dbg = dbg.p;
             }
+            DevBuf<uint32_t> dense_list;
+            const bool two_pass = kk <= 24 && !getenv("PCP_FK_ONEPASS");
+            if (two_pass) {
+                PCP_TRY(dense_list.alloc(ctx, ix->nitem));
+                P.dense_list = dense_list.p;
+                P.dense_count = counters.p + 6;
+            }
             {
                 StageTimer t(ctx, "knn.fast_kernel", 72.0 * nv);
                 PCP_TRY(launch_fknn(ctx, P));
+            }
+            if (two_pass) {
+                // items whose block holds more than 320 points (a sparse leaf beside a dense surface): the same
+                // kernel with room for PCP_FK_CAND2 staged candidates and fewer resident warps
+                StageTimer t(ctx, "knn.fast_kernel_dense", 0);
+                pcp_fknn_params P2 = P;
+                P2.item_list = dense_list.p;
+                P2.nitem_ptr = counters.p + 6;
+                P2.dense_list = nullptr;
+                P2.dense_count = nullptr;
+                P2.work_counter = counters.p + 7;
+                PCP_TRY(launch_fknn_dense2(ctx, P2));
             }
             if (want_dbg) {
                 unsigned long long h[16];

@@ -60,6 +60,13 @@ struct pcp_fknn_params {
     float* fail_u;           // ... and the known upper bound of the k-th squared distance (+inf: none)
     uint32_t* fail_count;
     uint32_t* work_counter;  // item dispenser
+    // second pass over the items whose 3x3x3 block held more points than the first pass stages: the first pass
+    // appends them to dense_list (when set) instead of sending their queries to the far list; the second pass
+    // (a kernel instance with a larger CAND) reads its items from item_list[0 .. *nitem_ptr)
+    const uint32_t* item_list = nullptr;
+    const uint32_t* nitem_ptr = nullptr;
+    uint32_t* dense_list = nullptr;
+    uint32_t* dense_count = nullptr;
     unsigned long long* dbg; // optional counters (PCP_KNN_DEBUG=1), NULL in production
 };
 
@@ -580,7 +587,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
 // others are appended to the "far" list with the best known upper bound of their k-th squared distance
 // (+inf if none) for knn_far_kernel.
 template <int CAP, int GS, int CAND, bool FLAT>
-static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fast_kernel(pcp_fknn_params P)
+static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, (CAND > 480 ? 3 : PCP_FK_MINB)) knn_fast_kernel(pcp_fknn_params P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int NSET = 32 / GS;
@@ -591,11 +598,13 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
     S.sqpos[lane] = 0xffffffffu;
     __syncwarp();
     int fill = 0;
+    const uint32_t nitem = P.nitem_ptr ? *P.nitem_ptr : P.nitem;
     while (true) {
         uint32_t item = 0;
         if (lane == 0) item = atomicAdd(P.work_counter, 1u);
         item = __shfl_sync(0xffffffffu, item, 0);
-        if (item >= P.nitem) break;
+        if (item >= nitem) break;
+        if (P.item_list) item = __ldg(P.item_list + item);
         const uint32_t cell = __ldg(P.item_cell + item);
         const uint32_t first = __ldg(P.item_first + item);
         const uint32_t meta = __ldg(P.item_meta + item);
@@ -649,6 +658,10 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, PCP_FK_MINB) knn_fas
         }
         const uint32_t total = __shfl_sync(0xffffffffu, pre, 31);
         pre -= nb_count;
+        if (P.dense_list && total > (uint32_t)CAND) { // left to the second pass
+            if (lane == 0) P.dense_list[atomicAdd(P.dense_count, 1u)] = item;
+            continue;
+        }
         const bool staged = total <= (uint32_t)CAND && total >= (uint32_t)P.kk;
         PCP_FK_DBG(0, 1);
         PCP_FK_DBG(1, staged ? 1 : 0);
