@@ -466,6 +466,33 @@ template <typename PointT> int loadPCDFile(const std::string& file_name, PointCl
     cloud.width = h.width, cloud.height = h.height, cloud.is_dense = dense != 0;
     return 0;
 }
+// several files into one cloud through the pipelined loader (pcp_pcd_load_many: host threads decode, the device
+// assembles the records); offsets (optional) receives files.size() + 1 record offsets
+template <typename PointT>
+int loadPCDFiles(const std::vector<std::string>& files, PointCloud<PointT>& cloud, std::vector<size_t>* offsets = nullptr, int threads = 0)
+{
+    size_t total = 0;
+    pcp_pcd_header h;
+    for (size_t i = 0; i < files.size(); i++) {
+        if (pcp_pcd_read_header(files[i].c_str(), &h) != PCP_OK) return detail::report(-1);
+        total += (size_t)h.points;
+    }
+    std::vector<const char*> names(files.size());
+    for (size_t i = 0; i < files.size(); i++) names[i] = files[i].c_str();
+    std::vector<size_t> off(files.size() + 1);
+    cloud.points.assign(total, PointT());
+    int dense = 1;
+    pcp_ctx* c = cloud_blend_double::detail::context();
+    const int st = pcp_pcd_load_many(c, names.data(), names.size(), detail::point_kind<PointT>::value, cloud.points.data(), total,
+                                     sizeof(PointT), threads, off.data(), &dense);
+    if (st != PCP_OK) {
+        std::cout << pcp_last_error(c) << std::endl;
+        return -1;
+    }
+    cloud.width = (uint32_t)total, cloud.height = 1, cloud.is_dense = dense != 0;
+    if (offsets) *offsets = off;
+    return 0;
+}
 template <typename PointT> int savePCDFile(const std::string& file_name, const PointCloud<PointT>& cloud, bool binary_mode = true)
 {
     return detail::save(file_name, cloud, binary_mode ? PCP_PCD_BINARY : PCP_PCD_ASCII, 8);

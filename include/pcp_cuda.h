@@ -254,7 +254,7 @@ PCP_API int pcp_minmax(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, d
 PCP_API int pcp_synth_cloud(pcp_ctx* ctx, int kind, uint64_t n_total, uint64_t first, uint64_t n, uint64_t seed,
                             int centred, void* out_pts);
 
-/* ---- PCD v0.7 files and LZF (host side, no device work) ----------------------------------------------------
+/* ---- PCD v0.7 files and LZF (host side; pcp_pcd_load_many assembles records on the device) ----------------------------------------------------
  * Replace io::loadPCDFile / savePCDFile* (pcd_helper.h:1343-1497), PCDReader::readHeader / read
  * (pcd_helper.cpp:71-333, 845-1181), PCDWriter::generateHeader / writeASCII / writeBinary /
  * writeBinaryCompressed (pcd_helper.h:323-371, 489-1090) and lzfCompress / lzfDecompress (lzf.cpp:86-415).
@@ -284,6 +284,15 @@ PCP_API int pcp_pcd_read_header(const char* path, pcp_pcd_header* header);
  * small).  *is_dense = 0 when a binary payload holds a non-finite value (ascii files are not checked, as in the
  * reference). */
 PCP_API int pcp_pcd_load(const char* path, int point_kind, void* pts, size_t cap, size_t stride, size_t* n, int* is_dense);
+/* The pipelined loader: nfiles PCD files into ONE cloud at pts (host or device memory, capacity cap
+ * records of `stride` bytes, a multiple of 8); file f's points become records [offsets[f], offsets[f+1]) (offsets:
+ * nfiles + 1 values).  `threads` host threads (<= 0: one per core) read the payloads and LZF-decode the
+ * binary_compressed ones, one file each; binary and binary_compressed payloads are uploaded as stored (packed records
+ * or field planes: 32 B/point for the reference's clouds instead of 48) and the records are assembled on the device
+ * with the same field matching as pcp_pcd_load; ascii payloads are parsed on the host.  *is_dense = AND over the files.
+ * With pts in device memory the cloud is ready for pcp_remove_duplicate / pcp_index_build without another copy. */
+PCP_API int pcp_pcd_load_many(pcp_ctx* ctx, const char* const* paths, size_t nfiles, int point_kind, void* pts, size_t cap,
+                              size_t stride, int threads, size_t* offsets, int* is_dense);
 /* Writes n records.  width = height = 0 means an unorganised cloud (n x 1).  mode: PCP_PCD_*; precision: significant
  * digits of the ascii writer (the reference's default is 8).  The payload holds the registered fields only, packed;
  * binary_compressed is limited to 4 GiB of them (32-bit size words). */

@@ -17,7 +17,7 @@ SYMBOLS = [
     "pcp_remove_duplicate", "pcp_features_knn_ex", "pcp_remove_duplicate_centred", "pcp_serial_sum",
     "pcp_column_histogram", "pcp_select_range", "pcp_select_columns", "pcp_select_boundary", "pcp_features_merge", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
     "pcp_features_rpca", "pcp_rpca_iterations", "pcp_region_growing",
-    "pcp_pcd_read_header", "pcp_pcd_load", "pcp_pcd_save", "pcp_lzf_compress", "pcp_lzf_decompress",
+    "pcp_pcd_read_header", "pcp_pcd_load", "pcp_pcd_load_many", "pcp_pcd_save", "pcp_lzf_compress", "pcp_lzf_decompress",
 ]
 
 
@@ -99,6 +99,7 @@ def load():
         "pcp_features_merge": (i32, [vp, sz, i32, i32, vp, vp, vp, vp, vp, vp]),
         "pcp_pcd_read_header": (i32, [C.c_char_p, C.POINTER(PcdHeader)]),
         "pcp_pcd_load": (i32, [C.c_char_p, i32, vp, sz, sz, C.POINTER(sz), C.POINTER(i32)]),
+        "pcp_pcd_load_many": (i32, [vp, C.POINTER(C.c_char_p), sz, i32, vp, sz, sz, i32, vp, C.POINTER(i32)]),
         "pcp_pcd_save": (i32, [C.c_char_p, i32, vp, sz, sz, u32, u32, i32, i32]),
         "pcp_lzf_compress": (u32, [vp, u32, vp, u32]),
         "pcp_lzf_decompress": (u32, [vp, u32, vp, u32]),

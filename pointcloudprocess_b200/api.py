@@ -490,6 +490,39 @@ class io:
                 "data_offset": h.data_offset, "viewpoint": list(h.viewpoint)}
 
     @staticmethod
+    def loadPCDFiles(file_names, ctx=None, out=None, threads=0):
+        """The pipelined loader (include/pcp_cuda.h: pcp_pcd_load_many): several files into one cloud; payloads are
+        decoded by host threads, uploaded as stored and assembled into records on the device.  `out`: a DeviceArray
+        to keep the cloud on the GPU (returns (n, offsets, is_dense)), else a host POINT_DTYPE array is returned with
+        (offsets, is_dense).  Returns None after printing the message on error, like the single-file reader."""
+        ctx = ctx or default_context()
+        names = [str(f).encode() for f in file_names]
+        total = 0
+        for f in file_names:
+            h = io.readHeader(f)
+            if h is None:
+                return None
+            total += int(h["points"])
+        arr = (C.c_char_p * len(names))(*names)
+        offsets = np.zeros(len(names) + 1, dtype=np.uintp)
+        dense = C.c_int(1)
+        host = None
+        if out is None:
+            host = np.zeros(total, dtype=POINT_DTYPE)
+            ptr, cap = host.ctypes.data, total
+        else:
+            ptr, cap = _ptr(out), out.nbytes // 48
+        st = ctx.L.pcp_pcd_load_many(ctx.h, arr, len(names), 0, ptr, cap, 48, int(threads), offsets.ctypes.data,
+                                     C.byref(dense))
+        if st != 0:
+            print(ctx.L.pcp_last_error(ctx.h).decode())
+            return None
+        offsets = offsets.astype(np.int64)
+        if out is None:
+            return host, offsets, bool(dense.value)
+        return int(offsets[-1]), offsets, bool(dense.value)
+
+    @staticmethod
     def loadPCDFile(file_name, cloud):
         L = _lib.load()
         h = _lib.PcdHeader()

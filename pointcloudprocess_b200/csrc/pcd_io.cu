@@ -2,15 +2,21 @@
 // binary_compressed payloads, and the LZF codec the compressed payload uses.  Replaces io::loadPCDFile /
 // savePCDFile* (pcd_helper.h:1343-1497), PCDReader::readHeader / read (pcd_helper.cpp:71-333, 845-1181),
 // PCDWriter::generateHeader / writeASCII / writeBinary / writeBinaryCompressed (pcd_helper.h:323-371, 489-1090)
-// and lzfCompress / lzfDecompress (lzf.cpp:86-415).  No device work: files are read into / written from the
-// caller's PointXYZRGBA (or xyz-only) records, which the rest of the library takes as they are.
+// and lzfCompress / lzfDecompress (lzf.cpp:86-415).  Files are read into / written from the caller's PointXYZRGBA
+// (or xyz-only) records on the host; pcp_pcd_load_many is the pipelined loader: payloads are read and
+// LZF-decoded by host threads, uploaded AS STORED (packed records or field planes, 32 B/point instead of 48) and the
+// records are assembled by a kernel.
 #include "common.cuh"
 #include <cerrno>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
+#include <future>
+#include <memory>
 #include <sstream>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -533,3 +539,242 @@ int pcp_pcd_save(const char* path, int point_kind, const void* pts, size_t n, si
 }
 
 } // extern "C"
+
+// ---- pipelined loader ----------------------------------------------------------------------------------------------
+namespace {
+
+// where the values of one file field live in the uploaded payload: value c of point p at
+// raw + off + p * pstride + c * size (packed records: pstride = bytes of a point; planes: pstride = size * count)
+struct PcdDevField {
+    unsigned long long off;
+    unsigned int pstride;
+    int size, count;
+    int dst;      // byte offset of the matched member in the record, -1: not stored
+    int is_float; // checked for is_dense
+};
+struct PcdDevLayout {
+    int nfields;
+    PcdDevField f[PCP_PCD_MAX_FIELDS];
+};
+
+// little-endian value of `size` <= 8 bytes; one load when the address allows it (the layouts the writers produce)
+__device__ __forceinline__ unsigned long long pcd_load_le(const unsigned char* src, int size)
+{
+    if (size == 8 && (reinterpret_cast<size_t>(src) & 7) == 0) return *reinterpret_cast<const unsigned long long*>(src);
+    if (size == 4 && (reinterpret_cast<size_t>(src) & 3) == 0) return *reinterpret_cast<const unsigned int*>(src);
+    unsigned long long v = 0;
+    for (int b = 0; b < size && b < 8; b++) v |= (unsigned long long)src[b] << (8 * b);
+    return v;
+}
+
+__global__ void __launch_bounds__(256) pcd_assemble_kernel(const unsigned char* __restrict__ raw, size_t n, PcdDevLayout L,
+                                                           char* __restrict__ out, size_t stride, int* __restrict__ not_dense)
+{
+    const size_t p = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    char* r = out + p * stride;
+    // PointXYZRGBA(): x = y = z = 0, data[3] = 1, rgba = 0 (point_type.h:86-91)
+    unsigned long long rec[6] = {0ull, 0ull, 0ull, 0x3ff0000000000000ull, 0ull, 0ull};
+    const int words = (int)(stride < 48 ? stride : 48) / 8;
+    bool dense = true;
+    for (int i = 0; i < L.nfields; i++) {
+        const PcdDevField f = L.f[i];
+        const unsigned char* src = raw + f.off + p * (size_t)f.pstride;
+        if (f.dst >= 0) { // count == 1; members are 4 or 8 bytes at aligned offsets of the record
+            const unsigned long long v = pcd_load_le(src, f.size);
+            if (f.size == 8) rec[f.dst >> 3] = v;
+            else if (f.dst & 4) rec[f.dst >> 3] = (rec[f.dst >> 3] & 0xffffffffull) | (v << 32);
+            else rec[f.dst >> 3] = (rec[f.dst >> 3] & ~0xffffffffull) | v;
+        }
+        if (f.is_float)
+            for (int c = 0; c < f.count; c++) {
+                const unsigned long long v = pcd_load_le(src + (size_t)c * f.size, f.size);
+                if (f.size == 8) dense &= isfinite(__longlong_as_double((long long)v));
+                else if (f.size == 4) dense &= isfinite(__uint_as_float((unsigned)v));
+            }
+    }
+    for (int w = 0; w < words; w++) reinterpret_cast<unsigned long long*>(r)[w] = rec[w];
+    if (!dense) *not_dense = 1;
+}
+
+struct PcdLoaded {
+    int status = PCP_OK;
+    std::string error;
+    pcp_pcd_header h;
+    std::vector<unsigned char> raw;   // payload as uploaded (binary: packed records; compressed: planes)
+    std::vector<unsigned char> recs;  // ascii: records parsed on the host
+    PcdDevLayout L;
+};
+
+// host half of one file: payload into memory, decoded if compressed, layout of its fields
+void load_one(const char* path, int point_kind, size_t stride, PcdLoaded& out)
+{
+    auto fail = [&](int code, const char* msg) {
+        out.status = code;
+        out.error = std::string(msg) + " (" + path + ")";
+    };
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(PCP_ERR_IO, "Could not open file");
+    pcp_pcd_header& h = out.h;
+    if (parse_header(f, &h) != PCP_OK) {
+        fclose(f);
+        return fail(PCP_ERR_INVALID, "bad PCD header");
+    }
+    const size_t n = (size_t)h.points;
+    int map[PCP_PCD_MAX_FIELDS];
+    match_fields(h, point_kind, map);
+    size_t fsize = 0;
+    for (int i = 0; i < h.nfields; i++) fsize += (size_t)h.size[i] * h.count[i];
+    fseek(f, (long)h.data_offset, SEEK_SET);
+    if (h.data_type == PCP_PCD_ASCII) { // parsed on the host by the single-file reader
+        fclose(f);
+        out.recs.resize(n * stride);
+        size_t got = 0;
+        int dense = 1;
+        const int st = pcp_pcd_load(path, point_kind, out.recs.data(), n, stride, &got, &dense);
+        if (st != PCP_OK) return fail(st, "ascii payload");
+        return;
+    }
+    PcdDevLayout& L = out.L;
+    L.nfields = 0;
+    if (h.data_type == PCP_PCD_BINARY) {
+        out.raw.resize(n * fsize);
+        const bool ok = !n || fread(out.raw.data(), 1, out.raw.size(), f) == out.raw.size();
+        fclose(f);
+        if (!ok) return fail(PCP_ERR_IO, "PCD binary payload: file shorter than its header says");
+        size_t off = 0;
+        for (int i = 0; i < h.nfields; i++) {
+            const bool pad = !strcmp(h.names[i], "_");
+            if (!pad) {
+                PcdDevField& d = L.f[L.nfields++];
+                d.off = off, d.pstride = (unsigned)fsize, d.size = h.size[i], d.count = h.count[i];
+                d.dst = map[i] >= 0 ? kMembers[map[i]].offset : -1;
+                d.is_float = h.type[i] == 'F';
+            }
+            off += (size_t)h.size[i] * h.count[i];
+        }
+        return;
+    }
+    unsigned int sizes[2];
+    if (fread(sizes, 4, 2, f) != 2) {
+        fclose(f);
+        return fail(PCP_ERR_IO, "PCD binary_compressed payload: missing size words");
+    }
+    std::vector<unsigned char> comp(sizes[0]);
+    const bool ok = !sizes[0] || fread(comp.data(), 1, comp.size(), f) == comp.size();
+    fclose(f);
+    if (!ok) return fail(PCP_ERR_IO, "PCD binary_compressed payload: file shorter than its header says");
+    out.raw.resize(sizes[1]);
+    if (lzf_decode(comp.data(), comp.size(), out.raw.data(), out.raw.size()) != sizes[1])
+        return fail(PCP_ERR_INVALID, "Size of decompressed lzf data does not match value stored in PCD header");
+    size_t plane = 0;
+    for (int i = 0; i < h.nfields; i++) {
+        if (!strcmp(h.names[i], "_")) continue;
+        const size_t bytes = (size_t)h.size[i] * h.count[i];
+        if (plane + bytes * n > out.raw.size()) return fail(PCP_ERR_INVALID, "PCD binary_compressed payload: planes exceed the uncompressed size");
+        PcdDevField& d = L.f[L.nfields++];
+        d.off = plane, d.pstride = (unsigned)bytes, d.size = h.size[i], d.count = h.count[i];
+        d.dst = map[i] >= 0 ? kMembers[map[i]].offset : -1;
+        d.is_float = h.type[i] == 'F';
+        plane += bytes * n;
+    }
+}
+
+} // namespace
+
+extern "C" int pcp_pcd_load_many(pcp_ctx* ctx, const char* const* paths, size_t nfiles, int point_kind, void* pts, size_t cap,
+                                 size_t stride, int threads, size_t* offsets, int* is_dense)
+{
+    if (!ctx || !offsets || (nfiles && !paths) || (cap && !pts) || stride < (size_t)(point_kind == PCP_PCD_POINT_XYZ ? 24 : 40) ||
+        stride % 8)
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_pcd_load_many: bad argument");
+    if (is_dense) *is_dense = 1;
+    offsets[0] = 0;
+    // sizes first: the offsets of every file's records are known before any payload is read
+    for (size_t i = 0; i < nfiles; i++) {
+        pcp_pcd_header h;
+        if (pcp_pcd_read_header(paths[i], &h) != PCP_OK) return pcp_fail(ctx, PCP_ERR_IO, "%s", pcp_last_error(nullptr));
+        offsets[i + 1] = offsets[i] + (size_t)h.points;
+    }
+    const size_t total = offsets[nfiles];
+    if (total > cap) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_pcd_load_many: the files hold %zu points, the buffer %zu", total, cap);
+    if (total == 0) return PCP_OK;
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    OutStage out;
+    PCP_TRY(out.open(ctx, pts, total * stride));
+    DevBuf<int> nd;
+    PCP_TRY(nd.alloc(ctx, 1));
+    PCP_CUDA_TRY(ctx, cudaMemsetAsync(nd.p, 0, sizeof(int), ctx->stream));
+    // host threads take files in order; the calling thread uploads and assembles them in order as they complete
+    if (threads < 1) threads = (int)std::thread::hardware_concurrency();
+    if (threads < 1) threads = 1;
+    if ((size_t)threads > nfiles) threads = (int)nfiles;
+    std::vector<std::unique_ptr<PcdLoaded>> loaded(nfiles);
+    std::vector<std::promise<void>> ready(nfiles);
+    std::atomic<size_t> next(0);
+    std::atomic<bool> stop(false);
+    std::vector<std::thread> pool;
+    for (int t = 0; t < threads; t++)
+        pool.emplace_back([&]() {
+            for (;;) {
+                const size_t i = next.fetch_add(1);
+                if (i >= nfiles) return;
+                loaded[i].reset(new PcdLoaded);
+                if (!stop.load()) load_one(paths[i], point_kind, stride, *loaded[i]);
+                ready[i].set_value();
+            }
+        });
+    int status = PCP_OK;
+    std::string err;
+    for (size_t i = 0; i < nfiles; i++) {
+        ready[i].get_future().wait();
+        std::unique_ptr<PcdLoaded> L = std::move(loaded[i]);
+        if (status != PCP_OK) continue;
+        if (L->status != PCP_OK) {
+            status = L->status, err = L->error;
+            stop.store(true);
+            continue;
+        }
+        const size_t n = (size_t)L->h.points;
+        if (n != offsets[i + 1] - offsets[i]) {
+            status = PCP_ERR_IO, err = std::string("file changed while loading: ") + paths[i];
+            stop.store(true);
+            continue;
+        }
+        if (!n) continue;
+        char* dst = static_cast<char*>(out.dptr) + offsets[i] * stride;
+        cudaError_t e = cudaSuccess;
+        if (!L->recs.empty()) {
+            e = cudaMemcpyAsync(dst, L->recs.data(), n * stride, cudaMemcpyHostToDevice, ctx->stream);
+        } else {
+            void* draw = nullptr;
+            if (pcp_arena_alloc(ctx, L->raw.size(), &draw) != PCP_OK) {
+                status = PCP_ERR_CUDA, err = "device staging allocation failed";
+                stop.store(true);
+                continue;
+            }
+            e = cudaMemcpyAsync(draw, L->raw.data(), L->raw.size(), cudaMemcpyHostToDevice, ctx->stream);
+            if (e == cudaSuccess) {
+                pcd_assemble_kernel<<<pcp_blocks_for(n, 256), 256, 0, ctx->stream>>>(static_cast<const unsigned char*>(draw), n, L->L,
+                                                                                     dst, stride, nd.p);
+                ctx->launches++;
+                e = cudaGetLastError();
+            }
+            pcp_arena_free(ctx, draw); // stream-ordered: after the kernel
+        }
+        if (e != cudaSuccess) {
+            status = PCP_ERR_CUDA, err = cudaGetErrorString(e);
+            stop.store(true);
+        }
+    }
+    for (std::thread& t : pool) t.join();
+    if (status != PCP_OK) {
+        cudaStreamSynchronize(ctx->stream);
+        return pcp_fail(ctx, status, "pcp_pcd_load_many: %s", err.c_str());
+    }
+    int not_dense = 0;
+    PCP_TRY(pcp_readback(ctx, &not_dense, nd.p, sizeof(int)));
+    if (is_dense) *is_dense = not_dense ? 0 : 1;
+    return out.commit(total * stride);
+}
