@@ -125,24 +125,37 @@ template <int KPL> static __global__ void __launch_bounds__(128) knn_warp_kernel
                 for (int nb = 0; nb < 27; nb++) {
                     const uint32_t s0 = __shfl_sync(0xffffffffu, lo, nb);
                     const uint32_t s1 = __shfl_sync(0xffffffffu, hi, nb);
-                    for (uint32_t t0 = s0; t0 < s1; t0 += 32) {
-                        const uint32_t t = t0 + lane;
-                        double d2 = DBL_MAX;
-                        int ci = 0x7fffffff;
-                        if (t < s1) {
-                            const pcp_rec r = pcp_load_rec(P.rec, t);
-                            d2 = pcp_dist2(qx, qy, qz, r.x, r.y, r.z);
-                            ci = (int)r.idx;
+                    // four chunks of 32 points in flight per lane: the scan is bound by the latency of its loads (the
+                    // insertions are rare once the list is warm), and the result does not depend on the order
+                    constexpr int WU = 4;
+                    for (uint32_t c0 = s0; c0 < s1; c0 += 32 * WU) {
+                        pcp_rec r[WU];
+#pragma unroll
+                        for (int u = 0; u < WU; u++) {
+                            const uint32_t t = c0 + 32 * u + lane;
+                            if (t < s1) r[u] = pcp_load_rec(P.rec, t);
                         }
-                        unsigned qual = __ballot_sync(0xffffffffu, t < s1 && pcp_less(d2, ci, kd, ki));
-                        while (qual) {
-                            const int src = __ffs(qual) - 1;
-                            qual &= qual - 1;
-                            const double xd = __shfl_sync(0xffffffffu, d2, src);
-                            const int xi = __shfl_sync(0xffffffffu, ci, src);
-                            if (!pcp_less(xd, xi, kd, ki)) continue; // threshold moved since the ballot
-                            pcp_wlist_insert<KPL>(L, lane, xd, xi, t0 + src);
-                            pcp_wlist_kth<KPL>(L, P.kk, kd, ki);
+#pragma unroll
+                        for (int u = 0; u < WU; u++) {
+                            const uint32_t t0 = c0 + 32 * u;
+                            if (t0 >= s1) break;
+                            const uint32_t t = t0 + lane;
+                            double d2 = DBL_MAX;
+                            int ci = 0x7fffffff;
+                            if (t < s1) {
+                                d2 = pcp_dist2(qx, qy, qz, r[u].x, r[u].y, r[u].z);
+                                ci = (int)r[u].idx;
+                            }
+                            unsigned qual = __ballot_sync(0xffffffffu, t < s1 && pcp_less(d2, ci, kd, ki));
+                            while (qual) {
+                                const int src = __ffs(qual) - 1;
+                                qual &= qual - 1;
+                                const double xd = __shfl_sync(0xffffffffu, d2, src);
+                                const int xi = __shfl_sync(0xffffffffu, ci, src);
+                                if (!pcp_less(xd, xi, kd, ki)) continue; // threshold moved since the ballot
+                                pcp_wlist_insert<KPL>(L, lane, xd, xi, t0 + src);
+                                pcp_wlist_kth<KPL>(L, P.kk, kd, ki);
+                            }
                         }
                     }
                 }

@@ -17,6 +17,11 @@ struct VoxParams {
     double inv[3];
     int min_b[3];
     int div_b[3];
+    // remove_duplicate (point_cloud_helper.cpp:42-63) filters the cloud translated by -centroid and translates the
+    // result back: with use_shift every coordinate is read as fl(p + shift) and every output written as
+    // fl(centroid + unshift) -- the two transformPointCloud passes without a copy of the cloud
+    int use_shift;
+    double shift[3], unshift[3];
 };
 
 template <typename KeyT>
@@ -31,6 +36,7 @@ __global__ void __launch_bounds__(256) voxel_key_kernel(const char* __restrict__
     KeyT key = ~(KeyT)0; // dropped points sort to the end
     int c0 = -1, c1 = -1, c2 = -1;
     if (isfinite(x) && isfinite(y) && isfinite(z)) {
+        if (P.use_shift) x = __dadd_rn(x, P.shift[0]), y = __dadd_rn(y, P.shift[1]), z = __dadd_rn(z, P.shift[2]);
         c0 = (int)__dsub_rn(__dmul_rn(x, P.inv[0]), (double)P.min_b[0]);
         c1 = (int)__dsub_rn(__dmul_rn(y, P.inv[1]), (double)P.min_b[1]);
         c2 = (int)__dsub_rn(__dmul_rn(z, P.inv[2]), (double)P.min_b[2]);
@@ -77,7 +83,7 @@ __global__ void __launch_bounds__(128) voxel_centroid_kernel(const char* __restr
                                                              const uint32_t* __restrict__ cell_start,
                                                              const uint32_t* __restrict__ m_ptr, int downsample_all,
                                                              char* __restrict__ out, size_t out_stride,
-                                                             int32_t* __restrict__ cell_count)
+                                                             int32_t* __restrict__ cell_count, const VoxParams P)
 {
     uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= *m_ptr) return;
@@ -85,7 +91,9 @@ __global__ void __launch_bounds__(128) voxel_centroid_kernel(const char* __restr
     double s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (uint32_t t = b; t < e; t++) {
         const char* rec = pts + (size_t)vals[t] * stride;
-        const double* p = reinterpret_cast<const double*>(rec);
+        const double* pp = reinterpret_cast<const double*>(rec);
+        double p[3] = {pp[0], pp[1], pp[2]};
+        if (P.use_shift) p[0] = __dadd_rn(p[0], P.shift[0]), p[1] = __dadd_rn(p[1], P.shift[1]), p[2] = __dadd_rn(p[2], P.shift[2]);
         double v[8];
         if (downsample_all) {
             uint32_t rgba = *reinterpret_cast<const uint32_t*>(rec + 32);
@@ -115,6 +123,8 @@ __global__ void __launch_bounds__(128) voxel_centroid_kernel(const char* __restr
     for (int f = 0; f < 8; f++) s[f] = __ddiv_rn(s[f], cnt);
     char* o = out + (size_t)c * out_stride;
     double* od = reinterpret_cast<double*>(o);
+    if (P.use_shift && isfinite(s[0]) && isfinite(s[1]) && isfinite(s[2])) // transformPointCloud skips the others
+        s[0] = __dadd_rn(s[0], P.unshift[0]), s[1] = __dadd_rn(s[1], P.unshift[1]), s[2] = __dadd_rn(s[2], P.unshift[2]);
     od[0] = s[0];
     od[1] = s[1];
     od[2] = s[2];
@@ -133,22 +143,6 @@ __global__ void __launch_bounds__(128) voxel_centroid_kernel(const char* __restr
     if (cell_count) cell_count[c] = (int32_t)(e - b);
 }
 
-__global__ void __launch_bounds__(256) shift_kernel(char* __restrict__ pts, size_t n, size_t stride, const double* c3,
-                                                    const unsigned long long* cnt, int sign)
-{
-    size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    double* p = reinterpret_cast<double*>(pts + i * stride);
-    double x = p[0], y = p[1], z = p[2];
-    if (!(isfinite(x) && isfinite(y) && isfinite(z))) return; // transformPointCloud skips them (:116-124)
-    double dn = (double)*cnt;
-    double cx = __ddiv_rn(c3[0], dn), cy = __ddiv_rn(c3[1], dn), cz = __ddiv_rn(c3[2], dn);
-    if (sign < 0) cx = -cx, cy = -cy, cz = -cz;
-    p[0] = __dadd_rn(x, cx);
-    p[1] = __dadd_rn(y, cy);
-    p[2] = __dadd_rn(z, cz);
-}
-
 int ceil_log2_u128(double cells)
 {
     int b = 0;
@@ -164,18 +158,33 @@ int ceil_log2_u128(double cells)
 int pcp_voxel_grid_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, const double leaf[3],
                           int downsample_all, void* dout, size_t out_stride, size_t* m_host, int32_t min_b[3],
                           int32_t div_b[3], int32_t* d_point_cell, int32_t* d_cell_count,
-                          const int32_t* force_min_b = nullptr, const int32_t* force_div_b = nullptr)
+                          const int32_t* force_min_b = nullptr, const int32_t* force_div_b = nullptr,
+                          const double* centre3 = nullptr, const pcp_bbox* known_bb = nullptr)
 {
     *m_host = 0;
     if (n == 0) return PCP_OK;
     if (n > (size_t)0x7fffffff) return pcp_fail(ctx, PCP_ERR_RANGE, "voxel grid: more than 2^31-1 points");
     pcp_bbox bb;
-    {
+    VoxParams P;
+    P.use_shift = 0;
+    for (int d = 0; d < 3; d++) P.shift[d] = P.unshift[d] = 0.0;
+    if (known_bb) {
+        bb = *known_bb;
+    } else {
         StageTimer t(ctx, "voxel.bbox", 24.0 * n);
         PCP_TRY(pcp_bbox_host(ctx, dpts, n, stride, &bb));
     }
     if (bb.count == 0) return PCP_OK;
-    VoxParams P;
+    if (centre3) {
+        // the box of the translated cloud: rounding is monotone, so min fl(x + t) = fl(min x + t)
+        P.use_shift = 1;
+        for (int d = 0; d < 3; d++) {
+            P.shift[d] = -centre3[d];
+            P.unshift[d] = centre3[d];
+            bb.mn[d] = bb.mn[d] + P.shift[d];
+            bb.mx[d] = bb.mx[d] + P.shift[d];
+        }
+    }
     double cells = 1.0;
     for (int d = 0; d < 3; d++) {
         if (!(leaf[d] > 0)) return pcp_fail(ctx, PCP_ERR_INVALID, "voxel grid: leaf size must be positive");
@@ -259,7 +268,7 @@ int pcp_voxel_grid_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t strid
         // grid sized for the worst case M == nv; threads beyond *m_ptr exit
         voxel_centroid_kernel<<<pcp_blocks_for(nv, 128), 128, 0, ctx->stream>>>(
             static_cast<const char*>(dpts), stride, vals, cell_start.p, m_dev.p, downsample_all,
-            static_cast<char*>(dout), out_stride, d_cell_count);
+            static_cast<char*>(dout), out_stride, d_cell_count, P);
         PCP_LAUNCH_CHECK(ctx);
     }
     uint32_t m = 0;
@@ -328,40 +337,34 @@ static int remove_duplicate_impl(pcp_ctx* ctx, void* pts_inout, size_t* n_inout,
     OutStage io; // in-place: host clouds are staged in, filtered on the device, staged back
     PCP_TRY(io.open(ctx, pts_inout, n * stride, true));
     char* d = static_cast<char*>(io.dptr);
-    DevBuf<char> tmp; // cloud_temp2 (point_cloud_helper.cpp:49-50)
+    DevBuf<char> tmp; // the filtered cloud, copied over the input at the end (the gather must not overwrite its source)
     DevBuf<double> s3;
     DevBuf<pcp_bbox> bb;
     PCP_TRY(tmp.alloc(ctx, n * stride));
     PCP_TRY(s3.alloc(ctx, 3));
     PCP_TRY(bb.alloc(ctx, 1));
-    if (centre) {
-        pcp_bbox one;
-        memset(&one, 0, sizeof(one));
-        one.count = 1; // shift_kernel divides the sums by the count
-        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(s3.p, centre, 24, cudaMemcpyHostToDevice, ctx->stream));
-        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(bb.p, &one, sizeof(one), cudaMemcpyHostToDevice, ctx->stream));
-        PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-    } else {
-        StageTimer t(ctx, "dedup.centroid", 24.0 * n);
-        PCP_TRY(pcp_serial_sum_device(ctx, d, n, stride, s3.p));
-        PCP_TRY(pcp_bbox_device(ctx, d, n, stride, bb.p));
-    }
-    const unsigned long long* cnt = &bb.p->count;
+    // the two transformPointCloud passes (point_cloud_helper.cpp:52-53, 60-61) are folded into the voxel kernels:
+    // coordinates are read as fl(p - c) and the cell centroids written as fl(centroid + c)
+    double c3[3];
+    pcp_bbox hb;
     {
-        StageTimer t(ctx, "dedup.centre", 48.0 * n);
-        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(tmp.p, d, n * stride, cudaMemcpyDeviceToDevice, ctx->stream));
-        shift_kernel<<<pcp_blocks_for(n, 256), 256, 0, ctx->stream>>>(tmp.p, n, stride, s3.p, cnt, -1);
-        PCP_LAUNCH_CHECK(ctx);
+        StageTimer t(ctx, "dedup.centroid", 24.0 * n);
+        if (!centre) PCP_TRY(pcp_serial_sum_device(ctx, d, n, stride, s3.p));
+        PCP_TRY(pcp_bbox_device(ctx, d, n, stride, bb.p));
+        double h3[3] = {0, 0, 0};
+        if (!centre) PCP_TRY(pcp_readback(ctx, h3, s3.p, 24));
+        PCP_TRY(pcp_readback(ctx, &hb, bb.p, sizeof(hb)));
+        const double dn = (double)hb.count;
+        for (int a = 0; a < 3; a++) c3[a] = centre ? centre[a] : h3[a] / dn; // compute3DCentroid: sum / count
     }
     double l = (double)leaf; // const float -> setLeafSize(double,double,double), point_cloud_helper.cpp:57
     double leaf3[3] = {l, l, l};
     size_t m = 0;
-    PCP_TRY(pcp_voxel_grid_device(ctx, tmp.p, n, stride, leaf3, 1, d, stride, &m, nullptr, nullptr, nullptr, nullptr,
-                                  min_b, div_b));
+    PCP_TRY(pcp_voxel_grid_device(ctx, d, n, stride, leaf3, 1, tmp.p, stride, &m, nullptr, nullptr, nullptr, nullptr,
+                                  min_b, div_b, c3, &hb));
     if (m) {
-        StageTimer t(ctx, "dedup.uncentre", 48.0 * m);
-        shift_kernel<<<pcp_blocks_for(m, 256), 256, 0, ctx->stream>>>(d, m, stride, s3.p, cnt, +1);
-        PCP_LAUNCH_CHECK(ctx);
+        StageTimer t(ctx, "dedup.copy_back", 96.0 * m);
+        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(d, tmp.p, m * stride, cudaMemcpyDeviceToDevice, ctx->stream));
     }
     *n_inout = m;
     PCP_TRY(io.commit(m * stride));
