@@ -5,6 +5,7 @@
 #include "knn_warp.cuh"
 #include "sort.cuh"
 #include <cub/cub.cuh>
+#include <cstdlib>
 
 namespace {
 
@@ -139,6 +140,107 @@ __global__ void __launch_bounds__(128) radius_moments_kernel(RadParams P, double
             for (int f = 1; f < 10; f++)
                 if (lane == f) v = a[f];
             mom[qi * 10 + lane] = v;
+        }
+    }
+}
+
+// The same moments for the index's own points, cell-cooperative: a warp takes one base cell, lane j holds query j of
+// the cell (chunks of 32).  The balls of all its queries lie inside the block of (2R+1)^3 level-L cells around the
+// cell (R * edge >= r); the block's points are streamed once per chunk through shared memory as FP64 coordinates and
+// every lane runs over them (broadcast reads), accumulating its query's moments under the predicate d2 < r2.
+// Against the warp-per-query kernel: the candidates are loaded once per cell instead of once per query, and no
+// lane idles on the 7/8 of a 3x3x3 block that lies outside the ball of a single query -- it works on its own query.
+constexpr int RC_WARPS = 4;
+constexpr int RC_MAXCELLS = 128; // >= (2R+1)^3, R <= 2
+constexpr int RC_CHUNK = 192;    // candidates staged at a time
+
+struct RadCellParams {
+    RadParams R;
+    const uint4* cinfo; // per base cell: x, y, z, first point
+    int blockR;         // R
+    uint32_t* work_counter;
+};
+
+__global__ void __launch_bounds__(32 * RC_WARPS) radius_moments_cell_kernel(RadCellParams P, double* __restrict__ mom)
+{
+    __shared__ uint32_t s_pre[RC_WARPS][RC_MAXCELLS]; // exclusive prefix of the block cells' point counts
+    __shared__ uint32_t s_lo[RC_WARPS][RC_MAXCELLS];  // first point of each block cell
+    __shared__ double s_xyz[RC_WARPS][3][RC_CHUNK];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t* pre = s_pre[warp];
+    uint32_t* los = s_lo[warp];
+    double* sx = s_xyz[warp][0];
+    double* sy = s_xyz[warp][1];
+    double* sz = s_xyz[warp][2];
+    const RadParams& Q = P.R;
+    const int L = Q.level, R = P.blockR, W = 2 * R + 1, NB = W * W * W;
+    const int mx = (Q.g.dims[0] - 1) >> L, my = (Q.g.dims[1] - 1) >> L, mz = (Q.g.dims[2] - 1) >> L;
+    const double r2 = Q.r2;
+    while (true) {
+        uint32_t cell = 0;
+        if (lane == 0) cell = atomicAdd(P.work_counter, 1u);
+        cell = __shfl_sync(0xffffffffu, cell, 0);
+        if (cell >= Q.ncell) return;
+        const uint4 ce = __ldg(P.cinfo + cell);
+        const uint32_t first = ce.w, nqc = __ldg(Q.cstart + cell + 1) - first;
+        const int cx = (int)ce.x >> L, cy = (int)ce.y >> L, cz = (int)ce.z >> L;
+        // ---- the block's point ranges and their prefix ----
+        uint32_t run = 0;
+        __syncwarp();
+        for (int b0 = 0; b0 < RC_MAXCELLS; b0 += 32) {
+            const int b = b0 + lane;
+            uint32_t lo = 0, hi = 0;
+            if (b < NB) {
+                const int dx = b % W - R, dy = (b / W) % W - R, dz = b / (W * W) - R;
+                const int nx = cx + dx, ny = cy + dy, nz = cz + dz;
+                if (nx >= 0 && ny >= 0 && nz >= 0 && nx <= mx && ny <= my && nz <= mz)
+                    pcp_level_range(Q.ckey, Q.cstart, Q.ncell, L, nx, ny, nz, lo, hi);
+            }
+            uint32_t inc = hi - lo;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += v;
+            }
+            pre[b] = run + inc - (hi - lo);
+            los[b] = lo;
+            run += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        const uint32_t T = run;
+        __syncwarp();
+        for (uint32_t q0 = 0; q0 < nqc; q0 += 32) {
+            const bool have = q0 + lane < nqc;
+            const pcp_rec q = pcp_load_rec(Q.rec, first + (have ? q0 + lane : 0));
+            double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0, a5 = 0, a6 = 0, a7 = 0, a8 = 0, a9 = 0;
+            for (uint32_t c0 = 0; c0 < T; c0 += RC_CHUNK) {
+                const uint32_t n = min((uint32_t)RC_CHUNK, T - c0);
+                __syncwarp();
+                for (uint32_t i = lane; i < n; i += 32) {
+                    const uint32_t f = c0 + i;
+                    int t = 0;
+#pragma unroll
+                    for (int step = RC_MAXCELLS / 2; step; step >>= 1)
+                        if (pre[t + step] <= f) t += step;
+                    const pcp_rec r = pcp_load_rec(Q.rec, los[t] + (f - pre[t]));
+                    sx[i] = r.x, sy[i] = r.y, sz[i] = r.z;
+                }
+                __syncwarp();
+#pragma unroll 4
+                for (uint32_t i = 0; i < n; i++) {
+                    const double dx = sx[i] - q.x, dy = sy[i] - q.y, dz = sz[i] - q.z;
+                    const double xx = dx * dx, yy = dy * dy, zz = dz * dz;
+                    const double d2 = (xx + yy) + zz; // == pcp_dist2: (q - p)^2 == (p - q)^2 exactly
+                    if (d2 < r2) {
+                        a0 += 1.0, a1 += dx, a2 += dy, a3 += dz;
+                        a4 += xx, a5 += dx * dy, a6 += dx * dz, a7 += yy, a8 += dy * dz, a9 += zz;
+                    }
+                }
+            }
+            if (have) {
+                double* m = mom + (size_t)(first + q0 + lane) * 10;
+                m[0] = a0, m[1] = a1, m[2] = a2, m[3] = a3, m[4] = a4;
+                m[5] = a5, m[6] = a6, m[7] = a7, m[8] = a8, m[9] = a9;
+            }
         }
     }
 }
@@ -384,7 +486,27 @@ extern "C" int pcp_features_radius(const pcp_index* ix, double r, uint32_t max_n
         P.nq = nv;
         DevBuf<double> mom;
         PCP_TRY(mom.alloc(ctx, nv * 10));
-        {
+        // the level whose block of (2R+1)^3 cells, R <= 2, covers every ball of a base cell's queries
+        int L = 0;
+        while (L < ix->grid.top_level && !(r / ldexp(ix->grid.h, L) < 1.999)) L++;
+        const int blockR = (int)floor(r / ldexp(ix->grid.h, L)) + 1;
+        if (blockR <= 2 && !getenv("PCP_RADIUS_WARP")) {
+            StageTimer t(ctx, "radius.moments_kernel", 72.0 * nv);
+            DevBuf<uint32_t> counter;
+            PCP_TRY(counter.alloc(ctx, 1));
+            PCP_CUDA_TRY(ctx, cudaMemsetAsync(counter.p, 0, 4, ctx->stream));
+            RadCellParams C;
+            C.R = P;
+            C.R.level = L;
+            C.cinfo = ix->cinfo;
+            C.blockR = blockR;
+            C.work_counter = counter.p;
+            int per_sm = 0;
+            PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radius_moments_cell_kernel, 32 * RC_WARPS, 0));
+            if (per_sm < 1) per_sm = 1;
+            radius_moments_cell_kernel<<<ctx->sm_count * per_sm, 32 * RC_WARPS, 0, ctx->stream>>>(C, mom.p);
+            PCP_LAUNCH_CHECK(ctx);
+        } else { // the whole grid is smaller than the ball: warp per query over the 3x3x3 block of the covering level
             StageTimer t(ctx, "radius.moments_kernel", 72.0 * nv);
             radius_moments_kernel<<<ctx->sm_count * 16, 128, 0, ctx->stream>>>(P, mom.p);
             PCP_LAUNCH_CHECK(ctx);
