@@ -144,38 +144,55 @@ __global__ void __launch_bounds__(128) radius_moments_kernel(RadParams P, double
     }
 }
 
-// The same moments for the index's own points, cell-cooperative: a warp takes one base cell, lane j holds query j of
-// the cell (chunks of 32).  The balls of all its queries lie inside the block of (2R+1)^3 level-L cells around the
-// cell (R * edge >= r); the block's points are streamed once per chunk through shared memory as FP64 coordinates and
-// every lane runs over them (broadcast reads), accumulating its query's moments under the predicate d2 < r2.
-// Against the warp-per-query kernel: the candidates are loaded once per cell instead of once per query, and no
-// lane idles on the 7/8 of a 3x3x3 block that lies outside the ball of a single query -- it works on its own query.
+// The same moments for the index's own points, cell-cooperative: a warp takes one base cell.
+//   stage    the balls of all the cell's queries lie inside the block of (2R+1)^3 level-L cells around it
+//            (R * edge >= r); the block's points are read once, those farther than r from the cell's box are dropped
+//            (no query of the cell can reach them: 3.5x fewer at r = 0.5, h = 0.37), the rest are compacted into shared
+//            memory as FP32 and FP64 coordinates relative to the cell origin o;
+//   search   8 lanes per query, four queries of the cell in flight per warp; a lane runs over every 8th staged
+//            candidate.  The predicate d2 < r2 is decided in FP32 wherever the FP32 distance is farther from r2 than
+//            its error bound (`margin`, from the block extent); the few pairs inside the band are decided by the exact
+//            FP64 expression of the reference (FLANN L2_Simple on the original coordinates): the neighbour SETS are exact;
+//   moments  accumulated about o in FP64 (u = p - o) and moved to the query at the end: sum (p-q) = m1 - n t,
+//            sum (p-q)(p-q)^T = m2 - m1 t^T - t m1^T + n t t^T, t = q - o; three xor-shuffle levels reduce a group.
+// Against the warp-per-query kernel: the candidates are loaded once per cell instead of once per query, from a
+// tighter region, and the FP64 work is confined to the accumulation.
 constexpr int RC_WARPS = 4;
 constexpr int RC_MAXCELLS = 128; // >= (2R+1)^3, R <= 2
-constexpr int RC_CHUNK = 192;    // candidates staged at a time
+constexpr int RC_CHUNK = 256;    // staged candidates at a time
+constexpr int RC_G = 8;          // lanes per query
 
 struct RadCellParams {
     RadParams R;
     const uint4* cinfo; // per base cell: x, y, z, first point
+    const pcp_hslot* htab; // base cell -> (first point, count)
+    uint32_t hmask;
+    const pcp_hslot* ltab; // (level, cell) -> run of base cells
+    uint32_t lmask;
     int blockR;         // R
+    float r2f, margin;  // FP32 decision band: |d2f - r2f| <= margin goes to the exact test
+    float rstage2;      // squared reach of the staging filter: (r + slack)^2
     uint32_t* work_counter;
+};
+
+struct RadCellSmem {
+    float4 f[RC_CHUNK];     // u as floats, w = sorted position
+    double ux[RC_CHUNK], uy[RC_CHUNK], uz[RC_CHUNK];
+    uint32_t pre[RC_MAXCELLS]; // exclusive prefix of the block cells' point counts
+    uint32_t lo[RC_MAXCELLS];  // first point of each block cell
 };
 
 __global__ void __launch_bounds__(32 * RC_WARPS) radius_moments_cell_kernel(RadCellParams P, double* __restrict__ mom)
 {
-    __shared__ uint32_t s_pre[RC_WARPS][RC_MAXCELLS]; // exclusive prefix of the block cells' point counts
-    __shared__ uint32_t s_lo[RC_WARPS][RC_MAXCELLS];  // first point of each block cell
-    __shared__ double s_xyz[RC_WARPS][3][RC_CHUNK];
+    extern __shared__ __align__(16) unsigned char rc_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t* pre = s_pre[warp];
-    uint32_t* los = s_lo[warp];
-    double* sx = s_xyz[warp][0];
-    double* sy = s_xyz[warp][1];
-    double* sz = s_xyz[warp][2];
+    RadCellSmem& S = reinterpret_cast<RadCellSmem*>(rc_smem)[warp];
     const RadParams& Q = P.R;
     const int L = Q.level, R = P.blockR, W = 2 * R + 1, NB = W * W * W;
     const int mx = (Q.g.dims[0] - 1) >> L, my = (Q.g.dims[1] - 1) >> L, mz = (Q.g.dims[2] - 1) >> L;
     const double r2 = Q.r2;
+    const float r2f = P.r2f, margin = P.margin, hf = (float)Q.g.h;
+    const int gl = lane & (RC_G - 1), grp = lane / RC_G;
     while (true) {
         uint32_t cell = 0;
         if (lane == 0) cell = atomicAdd(P.work_counter, 1u);
@@ -184,6 +201,8 @@ __global__ void __launch_bounds__(32 * RC_WARPS) radius_moments_cell_kernel(RadC
         const uint4 ce = __ldg(P.cinfo + cell);
         const uint32_t first = ce.w, nqc = __ldg(Q.cstart + cell + 1) - first;
         const int cx = (int)ce.x >> L, cy = (int)ce.y >> L, cz = (int)ce.z >> L;
+        const double ox = Q.g.org[0] + (double)ce.x * Q.g.h, oy = Q.g.org[1] + (double)ce.y * Q.g.h,
+                     oz = Q.g.org[2] + (double)ce.z * Q.g.h;
         // ---- the block's point ranges and their prefix ----
         uint32_t run = 0;
         __syncwarp();
@@ -193,8 +212,19 @@ __global__ void __launch_bounds__(32 * RC_WARPS) radius_moments_cell_kernel(RadC
             if (b < NB) {
                 const int dx = b % W - R, dy = (b / W) % W - R, dz = b / (W * W) - R;
                 const int nx = cx + dx, ny = cy + dy, nz = cz + dz;
-                if (nx >= 0 && ny >= 0 && nz >= 0 && nx <= mx && ny <= my && nz <= mz)
-                    pcp_level_range(Q.ckey, Q.cstart, Q.ncell, L, nx, ny, nz, lo, hi);
+                if (nx >= 0 && ny >= 0 && nz >= 0 && nx <= mx && ny <= my && nz <= mz) {
+                    // hash lookups (one or two probes) instead of two binary searches over the cell keys
+                    if (L == 0) {
+                        uint32_t cs = 0, cc = 0;
+                        if (pcp_hash_find(P.htab, P.hmask, pcp_morton(nx, ny, nz), cs, cc)) lo = cs, hi = cs + cc;
+                    } else if (L < PCP_HLEVELS) {
+                        uint32_t a = 0, cn = 0;
+                        if (pcp_hash_find(P.ltab, P.lmask, PCP_LKEY(L, pcp_morton(nx, ny, nz)), a, cn))
+                            lo = __ldg(Q.cstart + a), hi = __ldg(Q.cstart + a + cn);
+                    } else {
+                        pcp_level_range(Q.ckey, Q.cstart, Q.ncell, L, nx, ny, nz, lo, hi);
+                    }
+                }
             }
             uint32_t inc = hi - lo;
 #pragma unroll
@@ -202,46 +232,112 @@ __global__ void __launch_bounds__(32 * RC_WARPS) radius_moments_cell_kernel(RadC
                 const uint32_t v = __shfl_up_sync(0xffffffffu, inc, o);
                 if (lane >= o) inc += v;
             }
-            pre[b] = run + inc - (hi - lo);
-            los[b] = lo;
+            S.pre[b] = run + inc - (hi - lo);
+            S.lo[b] = lo;
             run += __shfl_sync(0xffffffffu, inc, 31);
         }
         const uint32_t T = run;
         __syncwarp();
-        for (uint32_t q0 = 0; q0 < nqc; q0 += 32) {
-            const bool have = q0 + lane < nqc;
-            const pcp_rec q = pcp_load_rec(Q.rec, first + (have ? q0 + lane : 0));
-            double a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0, a5 = 0, a6 = 0, a7 = 0, a8 = 0, a9 = 0;
-            for (uint32_t c0 = 0; c0 < T; c0 += RC_CHUNK) {
-                const uint32_t n = min((uint32_t)RC_CHUNK, T - c0);
-                __syncwarp();
-                for (uint32_t i = lane; i < n; i += 32) {
-                    const uint32_t f = c0 + i;
+        uint32_t next = 0; // next block point to stage
+        bool first_chunk = true;
+        while (next < T) {
+            // ---- stage: up to RC_CHUNK points within reach of the cell's box ----
+            uint32_t n = 0;
+            __syncwarp();
+            while (next < T && n + 32 <= RC_CHUNK) {
+                const uint32_t f = next + lane;
+                bool keep = false;
+                double ux = 0, uy = 0, uz = 0;
+                uint32_t pos = 0;
+                if (f < T) {
                     int t = 0;
 #pragma unroll
                     for (int step = RC_MAXCELLS / 2; step; step >>= 1)
-                        if (pre[t + step] <= f) t += step;
-                    const pcp_rec r = pcp_load_rec(Q.rec, los[t] + (f - pre[t]));
-                    sx[i] = r.x, sy[i] = r.y, sz[i] = r.z;
+                        if (S.pre[t + step] <= f) t += step;
+                    pos = S.lo[t] + (f - S.pre[t]);
+                    const pcp_rec r = pcp_load_rec(Q.rec, pos);
+                    ux = r.x - ox, uy = r.y - oy, uz = r.z - oz;
+                    // distance to the box [0,h]^3 (the cell's queries lie in it up to rounding: covered by the slack)
+                    const float fx = (float)ux, fy = (float)uy, fz = (float)uz;
+                    const float ex = fmaxf(fmaxf(-fx, fx - hf), 0.f), ey = fmaxf(fmaxf(-fy, fy - hf), 0.f),
+                                ez = fmaxf(fmaxf(-fz, fz - hf), 0.f);
+                    keep = __fmaf_rn(ez, ez, __fmaf_rn(ey, ey, ex * ex)) <= P.rstage2;
                 }
-                __syncwarp();
-#pragma unroll 4
-                for (uint32_t i = 0; i < n; i++) {
-                    const double dx = sx[i] - q.x, dy = sy[i] - q.y, dz = sz[i] - q.z;
-                    const double xx = dx * dx, yy = dy * dy, zz = dz * dz;
-                    const double d2 = (xx + yy) + zz; // == pcp_dist2: (q - p)^2 == (p - q)^2 exactly
-                    if (d2 < r2) {
-                        a0 += 1.0, a1 += dx, a2 += dy, a3 += dz;
-                        a4 += xx, a5 += dx * dy, a6 += dx * dz, a7 += yy, a8 += dy * dz, a9 += zz;
+                const unsigned mask = __ballot_sync(0xffffffffu, keep);
+                if (keep) {
+                    const uint32_t at = n + __popc(mask & ((1u << lane) - 1u));
+                    S.f[at] = make_float4((float)ux, (float)uy, (float)uz, __uint_as_float(pos));
+                    S.ux[at] = ux, S.uy[at] = uy, S.uz[at] = uz;
+                }
+                n += __popc(mask);
+                next += 32;
+            }
+            __syncwarp();
+            // ---- the cell's queries, four at a time ----
+            for (uint32_t q0 = 0; q0 < nqc; q0 += 32 / RC_G) {
+                const uint32_t qj = q0 + grp;
+                const bool have = qj < nqc;
+                const pcp_rec q = pcp_load_rec(Q.rec, first + (have ? qj : 0));
+                const double tx = q.x - ox, ty = q.y - oy, tz = q.z - oz;
+                const float qfx = (float)tx, qfy = (float)ty, qfz = (float)tz;
+                double a1 = 0, a2 = 0, a3 = 0, a4 = 0, a5 = 0, a6 = 0, a7 = 0, a8 = 0, a9 = 0;
+                unsigned cnt = 0;
+#pragma unroll 2
+                for (uint32_t i = gl; i < n; i += RC_G) {
+                    const float4 cf = S.f[i];
+                    const float dx = cf.x - qfx, dy = cf.y - qfy, dz = cf.z - qfz;
+                    const float d2f = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+                    bool in = d2f < r2f - margin;
+                    if (!in && d2f <= r2f + margin) { // inside the FP32 error band: the reference's own expression decides
+                        const pcp_rec r = pcp_load_rec(Q.rec, __float_as_uint(cf.w));
+                        in = pcp_dist2(q.x, q.y, q.z, r.x, r.y, r.z) < r2;
+                    }
+                    if (in && have) {
+                        const double ux = S.ux[i], uy = S.uy[i], uz = S.uz[i];
+                        cnt++;
+                        a1 += ux, a2 += uy, a3 += uz;
+                        a4 += ux * ux, a5 += ux * uy, a6 += ux * uz, a7 += uy * uy, a8 += uy * uz, a9 += uz * uz;
+                    }
+                }
+#pragma unroll
+                for (int o = 1; o < RC_G; o <<= 1) {
+                    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+                    a1 += __shfl_xor_sync(0xffffffffu, a1, o), a2 += __shfl_xor_sync(0xffffffffu, a2, o);
+                    a3 += __shfl_xor_sync(0xffffffffu, a3, o), a4 += __shfl_xor_sync(0xffffffffu, a4, o);
+                    a5 += __shfl_xor_sync(0xffffffffu, a5, o), a6 += __shfl_xor_sync(0xffffffffu, a6, o);
+                    a7 += __shfl_xor_sync(0xffffffffu, a7, o), a8 += __shfl_xor_sync(0xffffffffu, a8, o);
+                    a9 += __shfl_xor_sync(0xffffffffu, a9, o);
+                }
+                if (have) {
+                    // about the query: d = p - q = u - t; lane k of the group owns value k (lanes 0, 1 also 8, 9)
+                    const double nn = (double)cnt;
+                    double v[10];
+                    v[0] = nn;
+                    v[1] = a1 - nn * tx, v[2] = a2 - nn * ty, v[3] = a3 - nn * tz;
+                    v[4] = a4 - 2.0 * a1 * tx + nn * tx * tx;
+                    v[5] = a5 - a1 * ty - a2 * tx + nn * tx * ty;
+                    v[6] = a6 - a1 * tz - a3 * tx + nn * tx * tz;
+                    v[7] = a7 - 2.0 * a2 * ty + nn * ty * ty;
+                    v[8] = a8 - a2 * tz - a3 * ty + nn * ty * tz;
+                    v[9] = a9 - 2.0 * a3 * tz + nn * tz * tz;
+                    double* m = mom + (size_t)(first + qj) * 10;
+                    double mine = v[0], extra = gl == 0 ? v[8] : v[9];
+#pragma unroll
+                    for (int k = 1; k < RC_G; k++)
+                        if (gl == k) mine = v[k];
+                    if (first_chunk) {
+                        m[gl] = mine;
+                        if (gl < 2) m[8 + gl] = extra;
+                    } else {
+                        m[gl] += mine;
+                        if (gl < 2) m[8 + gl] += extra;
                     }
                 }
             }
-            if (have) {
-                double* m = mom + (size_t)(first + q0 + lane) * 10;
-                m[0] = a0, m[1] = a1, m[2] = a2, m[3] = a3, m[4] = a4;
-                m[5] = a5, m[6] = a6, m[7] = a7, m[8] = a8, m[9] = a9;
-            }
+            first_chunk = false;
         }
+        if (T == 0 && lane < 10) // cannot happen for an occupied cell (it holds its own points); keep mom defined
+            for (uint32_t qj = 0; qj < nqc; qj++) mom[(size_t)(first + qj) * 10 + lane] = 0.0;
     }
 }
 
@@ -499,12 +595,29 @@ extern "C" int pcp_features_radius(const pcp_index* ix, double r, uint32_t max_n
             C.R = P;
             C.R.level = L;
             C.cinfo = ix->cinfo;
+            C.htab = ix->htab, C.hmask = ix->hmask, C.ltab = ix->ltab, C.lmask = ix->lmask;
             C.blockR = blockR;
             C.work_counter = counter.p;
+            {
+                // FP32 error of d2 near the boundary: coordinates relative to the cell origin reach (R + 2) level-L edges;
+                // each float coordinate carries one rounding of that magnitude (2^-24 relative), the difference another,
+                // plus the rounding of the double subtraction p - o (epsd); the three products and two sums of d2 add
+                // 2^-22 relative.  Doubled for safety.
+                const double ext = (double)(blockR + 2) * ldexp(ix->grid.h, L);
+                const double ec = 3.0 * 5.97e-8 * ext + 2.0 * ix->epsd;
+                const double band = 2.0 * (2.0 * sqrt(3.0) * r * ec + 3.0 * ec * ec + 2.4e-7 * r * r);
+                C.r2f = (float)(r * r);
+                C.margin = (float)(band + 1.2e-7 * r * r) * 1.001f; // + the rounding of r2 to float
+                // staging filter: a query may sit a rounding outside its cell's box and the box distance is FP32
+                const double reach = r * (1.0 + 1e-5) + 4.0 * ec + 1e-6 * ext;
+                C.rstage2 = (float)(reach * reach) * 1.0001f;
+            }
+            const size_t smem = (size_t)RC_WARPS * sizeof(RadCellSmem);
+            PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(radius_moments_cell_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int per_sm = 0;
-            PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radius_moments_cell_kernel, 32 * RC_WARPS, 0));
+            PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radius_moments_cell_kernel, 32 * RC_WARPS, smem));
             if (per_sm < 1) per_sm = 1;
-            radius_moments_cell_kernel<<<ctx->sm_count * per_sm, 32 * RC_WARPS, 0, ctx->stream>>>(C, mom.p);
+            radius_moments_cell_kernel<<<ctx->sm_count * per_sm, 32 * RC_WARPS, smem, ctx->stream>>>(C, mom.p);
             PCP_LAUNCH_CHECK(ctx);
         } else { // the whole grid is smaller than the ball: warp per query over the 3x3x3 block of the covering level
             StageTimer t(ctx, "radius.moments_kernel", 72.0 * nv);

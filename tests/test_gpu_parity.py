@@ -206,6 +206,34 @@ def test_features_radius_match_oracle(ctx, orc):
     ix.free()
 
 
+@pytest.mark.parametrize("kind,n,r", [("city", 60000, 0.3), ("uniform_cube", 20000, 1.0), ("strip", 50000, 2.5),
+                                      ("forest", 30000, 0.05)])
+def test_features_radius_other_radii(ctx, orc, kind, n, r):
+    """the cell-cooperative kernel (block radius 1 and 2), and the warp-per-query kernel when the ball outgrows it"""
+    import pointcloudprocess_b200 as pcp
+    cloud = ctx.synth_cloud(kind, n, seed=6)
+    ix = pcp.Index(ctx, cloud)
+    got = ix.features_radius(r)
+    props, eig, lps, counts = orc.features_radius(cloud, r)
+    assert np.array_equal(got["counts"], counts)
+    check_features_tolerance(got["props"], got["eig"], props, eig)
+    ix.free()
+
+
+def test_features_radius_exact_boundary_on_a_lattice(ctx, orc):
+    """distances that equal r exactly (strict d2 < r2, kd_tree.h:888) and pairs inside the FP32 decision band"""
+    import pointcloudprocess_b200 as pcp
+    g = np.arange(24) * 0.125  # exactly representable spacing: d2 == r2 happens exactly
+    X, Y, Z = np.meshgrid(g, g, g, indexing="ij")
+    P = np.c_[X.ravel(), Y.ravel(), Z.ravel()] + np.array([483189.0, 3371741.5, 430.0])
+    for r in (0.25, 0.375, 0.2500001, np.nextafter(0.25, 0)):
+        ix = pcp.Index(ctx, P)
+        got = ix.features_radius(r)
+        counts = orc.features_radius(P, r)[3]
+        assert np.array_equal(got["counts"], counts), r
+        ix.free()
+
+
 # ---- voxel grid -------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("kind,n,leaf,centred", [("strip", 100000, 0.05, True), ("strip", 100000, 0.04, True),
                                                  ("city", 200000, 0.02, True), ("forest", 50000, 1.0, True),
