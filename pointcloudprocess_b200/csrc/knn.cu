@@ -36,6 +36,13 @@ __global__ void __launch_bounds__(256) knn_export_kernel(const pcp_rec* __restri
     }
 }
 
+// deferred-feature rows start as "not written"
+__global__ void __launch_bounds__(256) mark_rows_kernel(uint32_t* __restrict__ rows, size_t n, int k)
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i < n) rows[i * (size_t)k] = 0xffffffffu;
+}
+
 template <int KPL> int launch_wknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint32_t expected)
 {
     int blocks = ctx->sm_count * 4;
@@ -46,12 +53,15 @@ template <int KPL> int launch_wknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint3
     return PCP_OK;
 }
 
-template <int CAP, int GS, int CAND, bool FLAT> int launch_fknn_t(pcp_ctx* ctx, const pcp_fknn_params& P)
+template <int CAP, int GS, int CAND, bool FLAT, bool DEFER = false> int launch_fknn_t(pcp_ctx* ctx, const pcp_fknn_params& P)
 {
+    if constexpr (!DEFER) {
+        if (P.nbr_out) return launch_fknn_t<CAP, GS, CAND, FLAT, true>(ctx, P);
+    }
     const size_t smem = PCP_FK_WARPS * pcp_fd_smem<CAP, GS, CAND>::bytes(P.k);
-    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_fast_kernel<CAP, GS, CAND, FLAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_fast_kernel<CAP, GS, CAND, FLAT, DEFER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_fast_kernel<CAP, GS, CAND, FLAT>, 32 * PCP_FK_WARPS, smem));
+    PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_fast_kernel<CAP, GS, CAND, FLAT, DEFER>, 32 * PCP_FK_WARPS, smem));
     if (per_sm < 1) per_sm = 1;
     // persistent warps: every resident slot of every SM is filled once, items come from the work counter
     unsigned blocks = (unsigned)(ctx->sm_count * per_sm);
@@ -59,7 +69,7 @@ template <int CAP, int GS, int CAND, bool FLAT> int launch_fknn_t(pcp_ctx* ctx, 
     if (blocks > need) blocks = need;
     if (P.nitem_ptr) blocks = (unsigned)(ctx->sm_count * per_sm); // item count known on the device only
     if (P.dbg) fprintf(stderr, "[pcp knn] dense kernel: %zu bytes of shared memory per block, %d blocks per SM, %u blocks\n", smem, per_sm, blocks);
-    knn_fast_kernel<CAP, GS, CAND, FLAT><<<blocks, 32 * PCP_FK_WARPS, smem, ctx->stream>>>(P);
+    knn_fast_kernel<CAP, GS, CAND, FLAT, DEFER><<<blocks, 32 * PCP_FK_WARPS, smem, ctx->stream>>>(P);
     PCP_LAUNCH_CHECK(ctx);
     return PCP_OK;
 }
@@ -82,14 +92,17 @@ int launch_fknn_dense2(pcp_ctx* ctx, const pcp_fknn_params& P)
     return launch_fknn_t<32, 8, PCP_FK_CAND2, true>(ctx, P);
 }
 
-template <int CAP> int launch_far_t(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)
+template <int CAP, bool DEFER = false> int launch_far_t(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)
 {
+    if constexpr (!DEFER) {
+        if (P.nbr_out) return launch_far_t<CAP, true>(ctx, P, A);
+    }
     const size_t smem = PCP_FK_WARPS * pcp_far_smem<CAP>::bytes(P.k);
-    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_far_kernel<CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_far_kernel<CAP, DEFER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_far_kernel<CAP>, 32 * PCP_FK_WARPS, smem));
+    PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_far_kernel<CAP, DEFER>, 32 * PCP_FK_WARPS, smem));
     if (per_sm < 1) per_sm = 1;
-    knn_far_kernel<CAP><<<ctx->sm_count * per_sm, 32 * PCP_FK_WARPS, smem, ctx->stream>>>(P, A);
+    knn_far_kernel<CAP, DEFER><<<ctx->sm_count * per_sm, 32 * PCP_FK_WARPS, smem, ctx->stream>>>(P, A);
     PCP_LAUNCH_CHECK(ctx);
     return PCP_OK;
 }
@@ -194,6 +207,15 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 PCP_CUDA_TRY(ctx, cudaMemsetAsync(dbg.p, 0, 24 * 8, ctx->stream));
                 P.dbg = dbg.p;
             }
+            // deferred features: the search kernels only write neighbour rows; one thread-per-query kernel fits the planes
+            DevBuf<uint32_t> rows;
+            const bool defer = !getenv("PCP_FK_FUSED");
+            if (defer) {
+                PCP_TRY(rows.alloc(ctx, nv * (size_t)k));
+                mark_rows_kernel<<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(rows.p, nv, k);
+                PCP_LAUNCH_CHECK(ctx);
+                P.nbr_out = rows.p;
+            }
             DevBuf<uint32_t> dense_list;
             const bool two_pass = kk <= 24 && !getenv("PCP_FK_ONEPASS");
             if (two_pass) {
@@ -237,6 +259,13 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 A.fail_count = counters.p + 4;
                 StageTimer t(ctx, "knn.far_kernel");
                 PCP_TRY(launch_far(ctx, P, A));
+            }
+            if (defer) {
+                StageTimer t(ctx, "knn.features_kernel", 72.0 * nv);
+                features_from_list_kernel<<<pcp_blocks_for(nv, 128), 128, 0, ctx->stream>>>(
+                    ix->rec, nullptr, nullptr, rows.p, k, kk, o_props.dptr, (double*)o_eig.dptr, (float*)o_lps.dptr,
+                    (int32_t*)o_idx.dptr, (float*)o_kth.dptr, (uint32_t)nv);
+                PCP_LAUNCH_CHECK(ctx);
             }
             uint32_t hc[5];
             PCP_TRY(pcp_readback(ctx, hc, counters.p, 20));

@@ -156,7 +156,7 @@ struct pcp_far_args {
     uint32_t* fail_count;
 };
 
-template <int CAP>
+template <int CAP, bool DEFER = false>
 static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pcp_fknn_params P, pcp_far_args A)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -194,7 +194,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
             Q.h = (float)P.g.h;
         }
         if (fill == 32) {
-            pcp_fk_flush(P, S, lane);
+            pcp_fk_flush<pcp_far_smem<CAP>, DEFER>(P, S, lane);
             fill = 0;
         }
         const int slot = fill;
@@ -380,5 +380,5 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
             if (lane == 0) A.fail_list[atomicAdd(A.fail_count, 1u)] = qpos;
         }
     }
-    pcp_fk_flush(P, S, lane);
+    pcp_fk_flush<pcp_far_smem<CAP>, DEFER>(P, S, lane);
 }

@@ -67,6 +67,12 @@ struct pcp_fknn_params {
     const uint32_t* nitem_ptr = nullptr;
     uint32_t* dense_list = nullptr;
     uint32_t* dense_count = nullptr;
+    // deferred features (kernel instances with DEFER): the flush writes the neighbour POSITIONS of the settled queries
+    // to nbr_out[sorted position * k ...] and a separate thread-per-query kernel fits the planes.  The fused flush
+    // (gathers + FP64 scatter + Jacobi, ~2200 instructions = 35 KB) shares no code with the search loops, and warps
+    // of one SM sit in both at once: the instruction working set exceeded the 32 KB L1.5 instruction cache and
+    // 'no instruction' was the top stall of the fused kernels (6.5 cycles per issue).
+    uint32_t* nbr_out = nullptr;
     unsigned long long* dbg; // optional counters (PCP_KNN_DEBUG=1), NULL in production
 };
 
@@ -355,10 +361,24 @@ __device__ __forceinline__ int pcp_fk_search(const Src& src, const pcp_fk_smem<C
 }
 
 // features of the parked queries: lane = slot
-template <class SM> __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_params& P, const SM& S, int lane)
+template <class SM, bool DEFER = false>
+__device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_params& P, const SM& S, int lane)
 {
     __syncwarp();
     const uint32_t qpos = S.sqpos[lane];
+    if constexpr (DEFER) {
+        // rows of k positions, one slot after the other: lanes = entries, so a row is written as one segment
+        for (int sl = 0; sl < 32; sl++) {
+            const uint32_t qp = S.sqpos[sl];
+            if (qp == 0xffffffffu) continue;
+            for (int e = lane; e < P.k; e += 32)
+                P.nbr_out[(size_t)qp * P.k + e] = e < P.kk ? S.nbr[e * 32 + sl] : 0xffffffffu;
+        }
+        __syncwarp(); // (kth_d2: the features kernel writes the exact k-th distance, a tighter bound than S.skd)
+        S.sqpos[lane] = 0xffffffffu;
+        __syncwarp();
+        return;
+    }
     if (qpos != 0xffffffffu) {
         const size_t jq = (size_t)P.rec[qpos].idx;
         const int N = P.kk;
@@ -586,7 +606,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
 // Settles every query whose k nearest provably lie inside the 3x3x3 block of base cells around its cell; the
 // others are appended to the "far" list with the best known upper bound of their k-th squared distance
 // (+inf if none) for knn_far_kernel.
-template <int CAP, int GS, int CAND, bool FLAT>
+template <int CAP, int GS, int CAND, bool FLAT, bool DEFER = false>
 static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, (CAND > 480 ? 3 : PCP_FK_MINB)) knn_fast_kernel(pcp_fknn_params P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -622,7 +642,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, (CAND > 480 ? 3 : PC
         if (!want) continue;
         const int nwant = __popc(want);
         if (fill + nwant > 32) {
-            pcp_fk_flush(P, S, lane);
+            pcp_fk_flush<pcp_fd_smem<CAP, GS, CAND>, DEFER>(P, S, lane);
             fill = 0;
         }
         int cx, cy, cz;
@@ -785,5 +805,5 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, (CAND > 480 ? 3 : PC
             }
         }
     }
-    pcp_fk_flush(P, S, lane);
+    pcp_fk_flush<pcp_fd_smem<CAP, GS, CAND>, DEFER>(P, S, lane);
 }

@@ -188,13 +188,16 @@ static __global__ void __launch_bounds__(128) features_from_list_kernel(const pc
                                                                  const uint32_t* __restrict__ qcount_dev,
                                                                  const uint32_t* __restrict__ nbr_pos, int k, int kk,
                                                                  void* props, double* eig3, float* lps3,
-                                                                 int32_t* knn_idx, float* kth_d2)
+                                                                 int32_t* knn_idx, float* kth_d2, uint32_t all_rows = 0)
 {
     const uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (qi >= *qcount_dev) return;
-    const uint32_t qpos = qlist[qi] & 0x7fffffffu;
-    const size_t jq = (size_t)rec[qpos].idx;
+    // qlist == NULL: one row per sorted position (the deferred features of the dense / far kernels); a row that was
+    // never written starts with 0xffffffff (its query is settled elsewhere, or the point is not a query)
+    if (qi >= (qlist ? *qcount_dev : all_rows)) return;
+    const uint32_t qpos = qlist ? (qlist[qi] & 0x7fffffffu) : qi;
     const uint32_t* row = nbr_pos + (size_t)qi * k;
+    if (!qlist && row[0] == 0xffffffffu) return;
+    const size_t jq = (size_t)rec[qpos].idx;
     int N = 0;
     for (int e = 0; e < kk; e++)
         if (row[e] != 0xffffffffu) N++;
