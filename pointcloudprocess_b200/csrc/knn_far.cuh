@@ -34,6 +34,40 @@ template <int CAP> struct pcp_far_smem : pcp_fk_smem<CAP, 32> {
     }
 };
 
+// One staging round of the far kernel: candidates c0 .. c0+CAND of the selected cells' points, as floats relative to
+// the query.  A function of its own taking scalars (not a member: `this` would pin the source struct in local
+// memory): it has three call sites, and the far kernel's code has to stay near the instruction cache's size.
+static __device__ __noinline__ void pcp_far_stage(const pcp_rec* __restrict__ rec, float4* cand, const uint32_t* selpre,
+                                                  const uint32_t* selstart, uint32_t T, double qx, double qy, double qz,
+                                                  uint32_t c0, int lane)
+{
+    __syncwarp();
+#pragma unroll 1
+    for (int part = 0; part < PCP_FK_CAND / 64 && c0 + part * 64 < T; part++) {
+        pcp_rec r[2];
+        uint32_t ps[2];
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+            const uint32_t fl = c0 + part * 64 + lane + 32 * i;
+            ps[i] = 0;
+            if (fl < T) {
+                int c = 0;
+#pragma unroll
+                for (int step = PCP_FAR_NSEL / 2; step; step >>= 1)
+                    if (selpre[c + step] <= fl) c += step;
+                ps[i] = selstart[c] + (fl - selpre[c]);
+                r[i] = pcp_load_rec(rec, ps[i]);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 2; i++)
+            if (c0 + part * 64 + lane + 32 * i < T)
+                cand[part * 64 + lane + 32 * i] = make_float4((float)(r[i].x - qx), (float)(r[i].y - qy),
+                                                               (float)(r[i].z - qz), __uint_as_float(ps[i]));
+    }
+    __syncwarp();
+}
+
 // candidates = the points of the selected cells, staged CAND at a time as floats relative to the query
 struct pcp_far_src {
     const pcp_rec* rec;
@@ -46,31 +80,7 @@ struct pcp_far_src {
 
     __device__ __forceinline__ void stage(uint32_t c0, int lane) const
     {
-        __syncwarp();
-#pragma unroll 1
-        for (int part = 0; part < PCP_FK_CAND / 64 && c0 + part * 64 < T; part++) {
-            pcp_rec r[2];
-            uint32_t ps[2];
-#pragma unroll
-            for (int i = 0; i < 2; i++) {
-                const uint32_t fl = c0 + part * 64 + lane + 32 * i;
-                ps[i] = 0;
-                if (fl < T) {
-                    int c = 0;
-#pragma unroll
-                    for (int step = PCP_FAR_NSEL / 2; step; step >>= 1)
-                        if (selpre[c + step] <= fl) c += step;
-                    ps[i] = selstart[c] + (fl - selpre[c]);
-                    r[i] = pcp_load_rec(rec, ps[i]);
-                }
-            }
-#pragma unroll
-            for (int i = 0; i < 2; i++)
-                if (c0 + part * 64 + lane + 32 * i < T)
-                    cand[part * 64 + lane + 32 * i] = make_float4((float)(r[i].x - qx), (float)(r[i].y - qy),
-                                                                   (float)(r[i].z - qz), __uint_as_float(ps[i]));
-        }
-        __syncwarp();
+        pcp_far_stage(rec, cand, selpre, selstart, T, qx, qy, qz, c0, lane);
     }
     template <class F> __device__ __forceinline__ void for_each(int lane, F f) const
     {

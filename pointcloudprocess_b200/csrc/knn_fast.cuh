@@ -368,6 +368,7 @@ __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_params& P, const SM&
     const uint32_t qpos = S.sqpos[lane];
     if constexpr (DEFER) {
         // rows of k positions, one slot after the other: lanes = entries, so a row is written as one segment
+#pragma unroll 1
         for (int sl = 0; sl < 32; sl++) {
             const uint32_t qp = S.sqpos[sl];
             if (qp == 0xffffffffu) continue;
@@ -570,7 +571,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     const float amb2 = 2.0f * delta;
     bool ambig = false;
     float dkl = -1.0f;
-#pragma unroll
+#pragma unroll 1 // code size: the body holds a loop of its own, and the kernel has to stay inside the instruction cache
     for (int s = 0; s < SL; s++) {
         const int e = s * G + gl;
         if (live && e < (int)m) {
