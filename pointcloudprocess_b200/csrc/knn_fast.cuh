@@ -552,13 +552,15 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     const bool live = st == PCP_FD_OK;
     __syncwarp();
     // ---- pass 2: scatter the candidates of buckets <= b* into the list, bucket by bucket ----
+    const int lim = (key0 + min(bstar, PCP_FD_NB - 2) + 1) << 21;
     for (int f0 = 0; f0 < T; f0 += G) {
         const int i = f0 + gl;
         const float4 c = S.cand[i < T ? i : 0];
         const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
         const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-        const int b = pcp_fd_bucket(d2, key0);
-        if (live && i < T && b <= bstar) {
+        // bucket(d2) <= b*  <=>  the bits of d2 lie below the upper edge of b* (one compare for the ~90 % left out)
+        if (live && i < T && __float_as_int(d2) < lim) {
+            const int b = pcp_fd_bucket(d2, key0);
             const uint32_t at = atomicAdd(&hist[b], 1u);
             ld2[at] = d2;
             lpos[at] = (uint16_t)i;
