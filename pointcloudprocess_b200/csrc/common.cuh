@@ -40,6 +40,11 @@ struct pcp_ctx {
     std::vector<cudaEvent_t> ev_free;
     // copy lanes (pcp_copy_async): streams created on first use, one reusable event per direction
     void* rb_host = nullptr; // mapped pinned scratch of pcp_readback
+    // one grow-only device buffer kept between calls (pcp_scratch_get): the neighbour rows of the kNN kernels.  A
+    // 2 GB block allocated and freed on every call made the pool's other allocations slow and erratic (sharded
+    // steps: 4 ms -> 7..37 ms for the same remove_duplicate); kept here it is allocated once.
+    void* scratch = nullptr;
+    size_t scratch_bytes = 0;
     double hint_h = 0, hint_areal = 0; // index.cu: cell size and areal density of the previous index
     cudaStream_t lane[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t lane_in[4] = {nullptr, nullptr, nullptr, nullptr};  // compute -> lane
@@ -77,6 +82,8 @@ void pcp_set_global_error(const char* msg);
 
 // ---- stream-ordered arena ----------------------------------------------------------------------------
 int pcp_arena_alloc(pcp_ctx* ctx, size_t bytes, void** out);
+// the context's persistent scratch, grown to at least `bytes` (contents undefined; valid until the next call)
+int pcp_scratch_get(pcp_ctx* ctx, size_t bytes, void** out);
 void pcp_arena_free(pcp_ctx* ctx, void* p);
 
 // RAII device buffer from the arena (freed stream-ordered at scope exit)

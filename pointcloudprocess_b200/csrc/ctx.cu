@@ -37,6 +37,28 @@ void pcp_arena_free(pcp_ctx* ctx, void* p)
     if (p) cudaFreeAsync(p, ctx->stream);
 }
 
+int pcp_scratch_get(pcp_ctx* ctx, size_t bytes, void** out)
+{
+    if (bytes > ctx->scratch_bytes) {
+        if (ctx->scratch) {
+            cudaStreamSynchronize(ctx->stream);
+            cudaFree(ctx->scratch);
+            ctx->scratch = nullptr, ctx->scratch_bytes = 0;
+        }
+        const size_t want = bytes + bytes / 8;
+        cudaError_t e = cudaMalloc(&ctx->scratch, want);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            ctx->scratch = nullptr;
+            return pcp_fail(ctx, e == cudaErrorMemoryAllocation ? PCP_ERR_NOMEM : PCP_ERR_CUDA,
+                            "device allocation of %zu bytes failed: %s", want, cudaGetErrorString(e));
+        }
+        ctx->scratch_bytes = want;
+    }
+    *out = ctx->scratch;
+    return PCP_OK;
+}
+
 pcp_ptr_kind pcp_classify(pcp_ctx* ctx, const void* p)
 {
     cudaPointerAttributes at;
@@ -214,6 +236,7 @@ void pcp_destroy(pcp_ctx* ctx)
         cudaEventDestroy(ctx->lane_out[l]);
     }
     if (ctx->rb_host) cudaFreeHost(ctx->rb_host);
+    if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
@@ -241,6 +264,8 @@ int pcp_trim(pcp_ctx* ctx)
     if (!ctx) return PCP_ERR_INVALID;
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     PCP_CUDA_TRY(ctx, cudaMemPoolTrimTo(ctx->pool, 0));
+    if (ctx->scratch) cudaFree(ctx->scratch);
+    ctx->scratch = nullptr, ctx->scratch_bytes = 0;
     return PCP_OK;
 }
 

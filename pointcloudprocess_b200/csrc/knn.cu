@@ -208,10 +208,14 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 P.dbg = dbg.p;
             }
             // deferred features: the search kernels only write neighbour rows; one thread-per-query kernel fits the planes
-            DevBuf<uint32_t> rows;
+            struct {
+                uint32_t* p = nullptr;
+            } rows;
             const bool defer = !getenv("PCP_FK_FUSED");
             if (defer) {
-                PCP_TRY(rows.alloc(ctx, nv * (size_t)k));
+                void* q = nullptr;
+                PCP_TRY(pcp_scratch_get(ctx, nv * (size_t)k * 4, &q)); // kept by the context between calls
+                rows.p = static_cast<uint32_t*>(q);
                 mark_rows_kernel<<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(rows.p, nv, k);
                 PCP_LAUNCH_CHECK(ctx);
                 P.nbr_out = rows.p;

@@ -19,6 +19,7 @@ torch.distributed (NCCL / gloo) and, for single-GPU parity tests, with all ranks
 import ctypes as C
 import math
 import os
+import sys
 
 import numpy as np
 
@@ -235,6 +236,21 @@ class ShardedPipeline:
         except StopIteration as e:
             return e.value
 
+    def _mark(self, name):
+        """PCP_SHARD_TRACE=1: wall clock between the phases of a step (synchronises: a debugging aid)."""
+        if not os.environ.get("PCP_SHARD_TRACE"):
+            return
+        import time
+        self.torch.cuda.synchronize()
+        now = time.perf_counter()
+        if name == "start":
+            self._trace = []
+        else:
+            self._trace.append("%s %.1f" % (name, (now - self._t_last) * 1e3))
+        self._t_last = now
+        if name == "end" and self.rank == 0:
+            sys.stderr.write("[shard trace] " + ", ".join(self._trace) + "\n")
+
     def _step_gen(self, src_ptr):
         """Generator: yields (send_left, send_right) uint8 tensors at each exchange, receives (from_left,
         from_right); returns the number of featured points.  src_ptr: this rank's input cloud (device or pinned
@@ -252,6 +268,7 @@ class ShardedPipeline:
             self.last_m = m
             return m
         t, P, H = self.torch, self.plan, self.halo
+        self._mark("start")
         m = ctx.remove_duplicate_centred((wp, self.n, 48), P.leaf, P.centre, P.min_b, P.div_b)
         xlo, xhi = P.face_x(P.bounds[self.rank]), P.face_x(P.bounds[self.rank + 1])
         has_l, has_r = self.rank > 0, self.rank < self.world - 1
@@ -265,7 +282,9 @@ class ShardedPipeline:
             buf = t.empty(m * 48, dtype=t.uint8, device="cuda")
             c = ctx.select_range((wp, m, 48), 0, xhi - H, math.inf, buf.data_ptr())
             send_r = buf[:c * 48]
+        self._mark("dedup+select")
         recv_l, recv_r = yield (send_l, send_r)
+        self._mark("exchange1")
         nl = 0 if recv_l is None else recv_l.numel() // 48
         nr = 0 if recv_r is None else recv_r.numel() // 48
         ntot = m + nl + nr
@@ -279,6 +298,7 @@ class ShardedPipeline:
         try:
             ix.features_knn(k, props=self._p(self.props), want_eig=False, want_lps=False, query_limit=m,
                             kth_d2=self._p(self.kth))
+            self._mark("index+features")
             # ---- queries whose k-th neighbour may lie beyond the halo ----
             pts = self.work[:ntot * 48].view(t.float64).view(ntot, 6)
             while True:
@@ -313,7 +333,9 @@ class ShardedPipeline:
                     assert 0 <= c <= nF and int(sub[:c].min()) >= 0 and int(sub[:c].max()) < nF, \
                         ("side", self.rank, c, nF, int(sub[:c].min()), int(sub[:c].max()))
             # ---- exchange 2: the flagged queries ----
+            self._mark("boundary select")
             q_l, q_r = yield tuple(None if sd is None else sd[1].view(t.uint8).view(-1) for sd in side)
+            self._mark("exchange2")
             answers = []
             for q in (q_l, q_r):
                 if q is None or q.numel() == 0:
@@ -329,7 +351,9 @@ class ShardedPipeline:
                 xyz = pts[idx.view(-1).long().clamp(min=0), :3].contiguous()  # padded entries carry d2 = +inf
                 answers.append(t.cat([xyz.view(t.uint8).view(-1), d2.view(t.uint8).view(-1)]))
             # ---- exchange 3: candidate lists back to the owners ----
+            self._mark("answers")
             a_l, a_r = yield (answers[0], answers[1])
+            self._mark("exchange3")
             if nF:
                 idx = t.empty((nF, k), dtype=t.int32, device="cuda")
                 d2o = t.empty((nF, k), dtype=t.float64, device="cuda")
@@ -358,6 +382,8 @@ class ShardedPipeline:
                 del xyz_all, d2_all, pid
         finally:
             ix.free()
+        self._mark("merge")
+        self._mark("end")
         self.stats = {"halo_m": H, "own": int(m), "halo_points": int(nl + nr), "boundary_queries": nF,
                       "sent": [0 if sd is None else int(sd[0].numel()) for sd in side]}
         self.last_m = m

@@ -22,3 +22,13 @@ for s in ctx.profile_get():
     if s["ms"] > 1.0:
         print("%-28s %9.3f ms  %d" % (s["name"], s["ms"], s["launches"]))
 print([j.stats for j in jobs])
+# warm passes: wall clock against the sum of the library's stages (the rest is the driver: torch ops, syncs)
+for rep in range(3):
+    ctx.profile_reset()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    sharded.run_lockstep([j._step_gen(j._p(j.cloud)) for j in jobs])
+    torch.cuda.synchronize()
+    wall = (time.perf_counter() - t0) * 1e3
+    st = ctx.profile_get()
+    print("warm pass %d: %.1f ms wall over %d ranks, library stages %.1f ms" % (rep, wall, world, sum(s["ms"] for s in st)))
