@@ -304,6 +304,7 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
             W.cstart = ix->cstart;
             W.ncell = ix->ncell;
             W.g = ix->grid;
+    W.htab = ix->htab, W.hmask = ix->hmask, W.ltab = ix->ltab, W.lmask = ix->lmask;
             W.k = k;
             W.kk = kk;
             W.qcount = nfail;
@@ -372,6 +373,7 @@ extern "C" int pcp_knn(const pcp_index* ix, const void* q, size_t nq, size_t qst
     W.cstart = ix->cstart;
     W.ncell = ix->ncell;
     W.g = ix->grid;
+    W.htab = ix->htab, W.hmask = ix->hmask, W.ltab = ix->ltab, W.lmask = ix->lmask;
     W.k = k;
     W.kk = (int)(ix->n < (size_t)k ? ix->n : (size_t)k);
     W.qcount = (uint32_t)nq;

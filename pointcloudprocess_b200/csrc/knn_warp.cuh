@@ -12,6 +12,12 @@ struct pcp_wknn_params {
     const unsigned long long* ckey;
     const uint32_t* cstart;
     uint32_t ncell;
+    // hash tables of the index (may be NULL): cell ranges by one or two probes instead of two binary searches over the
+    // cell keys (46 dependent loads per level at 6 M cells -- the latency that bounded this kernel)
+    const pcp_hslot* htab;
+    uint32_t hmask;
+    const pcp_hslot* ltab;
+    uint32_t lmask;
     pcp_grid g;
     int k, kk;
     // queries: either sorted positions (qlist, with count in *qcount_dev or qcount) or external points
@@ -117,8 +123,18 @@ template <int KPL> static __global__ void __launch_bounds__(128) knn_warp_kernel
                     const int nx = cx + dx, ny = cy + dy, nz = cz + dz;
                     const int mx = (P.g.dims[0] - 1) >> level, my = (P.g.dims[1] - 1) >> level,
                               mz = (P.g.dims[2] - 1) >> level;
-                    if (nx >= 0 && ny >= 0 && nz >= 0 && nx <= mx && ny <= my && nz <= mz)
-                        pcp_level_range(P.ckey, P.cstart, P.ncell, level, nx, ny, nz, lo, hi);
+                    if (nx >= 0 && ny >= 0 && nz >= 0 && nx <= mx && ny <= my && nz <= mz) {
+                        if (P.htab && level == 0) {
+                            uint32_t cs = 0, cc = 0;
+                            if (pcp_hash_find(P.htab, P.hmask, pcp_morton(nx, ny, nz), cs, cc)) lo = cs, hi = cs + cc;
+                        } else if (P.ltab && level < PCP_HLEVELS) {
+                            uint32_t a = 0, cn = 0;
+                            if (pcp_hash_find(P.ltab, P.lmask, PCP_LKEY(level, pcp_morton(nx, ny, nz)), a, cn))
+                                lo = __ldg(P.cstart + a), hi = __ldg(P.cstart + a + cn);
+                        } else {
+                            pcp_level_range(P.ckey, P.cstart, P.ncell, level, nx, ny, nz, lo, hi);
+                        }
+                    }
                 }
                 double kd = DBL_MAX;
                 int ki = 0x7fffffff;
