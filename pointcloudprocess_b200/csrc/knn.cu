@@ -83,13 +83,14 @@ int launch_fknn(pcp_ctx* ctx, const pcp_fknn_params& P)
     return launch_fknn_t<160, 8, 480, true>(ctx, P);
 }
 
-// the second pass over the items the first one found too dense to stage (k <= 24 only)
+// the second pass over the items the first one found too dense to stage (k <= 52)
 #ifndef PCP_FK_CAND2
 #define PCP_FK_CAND2 800
 #endif
 int launch_fknn_dense2(pcp_ctx* ctx, const pcp_fknn_params& P)
 {
-    return launch_fknn_t<32, 8, PCP_FK_CAND2, true>(ctx, P);
+    if (P.kk <= 24) return launch_fknn_t<32, 8, PCP_FK_CAND2, true>(ctx, P);
+    return launch_fknn_t<64, 8, 1000, true>(ctx, P); // k <= 52: the first pass stages 480
 }
 
 template <int CAP, bool DEFER = false> int launch_far_t(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)
@@ -221,7 +222,7 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 P.nbr_out = rows.p;
             }
             DevBuf<uint32_t> dense_list;
-            const bool two_pass = kk <= 24 && !getenv("PCP_FK_ONEPASS");
+            const bool two_pass = kk <= 52 && !getenv("PCP_FK_ONEPASS");
             if (two_pass) {
                 PCP_TRY(dense_list.alloc(ctx, ix->nitem));
                 P.dense_list = dense_list.p;
