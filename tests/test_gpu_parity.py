@@ -441,3 +441,35 @@ def test_calculate_plan_parameter_rpca_mirror(ctx, orc):
     cloud = pcp.PointCloud(ctx.synth_cloud("city", 20000, seed=6))
     props = pcp.CalculateFeature(ctx).calculate_plan_parameter_rpca(cloud, 0.3, 0.99, 0.5, seed=4)
     assert props.tobytes() == orc.features_rpca(cloud.points, 20, 0.99, 0.5, 4).tobytes()
+
+
+# ---- alternative code paths must agree bit for bit -----------------------------------------------------------
+def test_fused_and_single_pass_variants_equal_the_default_path(ctx):
+    """PCP_FK_FUSED (plane fit inside the search kernels), PCP_FK_ONEPASS (no second dense pass) and the default
+    (deferred fit, two passes) are the same function; PCP_RADIUS_WARP is the warp-per-query radius kernel."""
+    import os
+    import pointcloudprocess_b200 as pcp
+    cloud = ctx.synth_cloud("city", 300000, seed=12)
+    ix = pcp.Index(ctx, cloud)
+    ref = ix.features_knn(20, want_idx=True)
+    ref32 = ix.features_knn(32, want_idx=True)
+    rad = ix.features_radius(0.3)
+    try:
+        for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS"):
+            os.environ[env] = "1"
+            got = ix.features_knn(20, want_idx=True)
+            got32 = ix.features_knn(32, want_idx=True)
+            del os.environ[env]
+            for a, b in ((got, ref), (got32, ref32)):
+                assert np.array_equal(a["knn_idx"], b["knn_idx"]), env
+                assert a["props"].tobytes() == b["props"].tobytes(), env
+                assert a["eig"].tobytes() == b["eig"].tobytes() and a["lps"].tobytes() == b["lps"].tobytes(), env
+        os.environ["PCP_RADIUS_WARP"] = "1"
+        radw = ix.features_radius(0.3)
+        del os.environ["PCP_RADIUS_WARP"]
+        assert np.array_equal(radw["counts"], rad["counts"])
+        check_features_tolerance(radw["props"], radw["eig"], rad["props"], rad["eig"])
+    finally:
+        for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS", "PCP_RADIUS_WARP"):
+            os.environ.pop(env, None)
+        ix.free()
