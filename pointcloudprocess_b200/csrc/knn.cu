@@ -58,7 +58,7 @@ template <int CAP, int GS, int CAND, bool FLAT, bool DEFER = false> int launch_f
     if constexpr (!DEFER) {
         if (P.nbr_out) return launch_fknn_t<CAP, GS, CAND, FLAT, true>(ctx, P);
     }
-    const size_t smem = PCP_FK_WARPS * pcp_fd_smem<CAP, GS, CAND>::bytes(P.k);
+    const size_t smem = PCP_FK_WARPS * pcp_fd_smem<CAP, GS, CAND, DEFER>::bytes(P.k);
     PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_fast_kernel<CAP, GS, CAND, FLAT, DEFER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_fast_kernel<CAP, GS, CAND, FLAT, DEFER>, 32 * PCP_FK_WARPS, smem));

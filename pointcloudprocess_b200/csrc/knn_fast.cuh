@@ -428,7 +428,7 @@ __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_params& P, const SM&
 // CAND: staged candidates per item.  320 candidates, lists for 4 queries of 32 entries and k = 20 come to 9472
 // bytes per warp: 6 blocks of 4 warps per SM.  (Candidates stay 16-byte records: the 4 query groups of a warp read
 // the same 8 candidates per step, one shared-memory wavefront as LDS.128 against three for split x / y / z arrays.)
-template <int CAP, int GS, int CAND> struct pcp_fd_smem {
+template <int CAP, int GS, int CAND, bool DEFER = false> struct pcp_fd_smem {
     static constexpr int NSET = 32 / GS;
     static_assert(CAND % 4 == 0 && CAND < 65536 && (NSET * CAP) % 2 == 0, "pcp_fd_smem: layout");
     float4* cand;    // [CAND]  x, y, z relative to the leaf origin, w = sorted position
@@ -436,12 +436,13 @@ template <int CAP, int GS, int CAND> struct pcp_fd_smem {
     float* ld2;      // [NSET][CAP]
     uint16_t* lpos;  // [NSET][CAP]  candidate number
     uint32_t* tab;   // [64]  exclusive prefix of the staged runs' lengths (0xffffffff beyond the 27), first points
-    uint32_t* nbr;   // [k][32]
+    uint32_t* nbr;   // [k][32]  (DEFER: none of the three -- the rows go straight to global memory)
     uint32_t* sqpos; // [32]
     float* skd;      // [32]
     static __host__ __device__ size_t bytes(int k)
     {
-        return (size_t)CAND * 16 + (size_t)NSET * PCP_FD_NB * 4 + (size_t)NSET * CAP * 6 + 256 + (size_t)32 * k * 4 + 256;
+        return (size_t)CAND * 16 + (size_t)NSET * PCP_FD_NB * 4 + (size_t)NSET * CAP * 6 + 256 +
+               (DEFER ? 0 : (size_t)32 * k * 4 + 256);
     }
     __device__ pcp_fd_smem(unsigned char* base, int k)
     {
@@ -474,10 +475,11 @@ template <int CAP, int GS, int CAND> struct pcp_fd_smem {
 
 // Every group of G lanes searches the staged block for its own query.  dku: upper bound of the k-th squared
 // distance (valid for OK and AMBIG).
-template <int G, int CAP, int CAND>
-__device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CAND>& S, int lane,
-                                             bool active, int slot, int kk, float qfx, float qfy, float qfz, float top,
-                                             float g2, float e1, float& dku)
+// The kk nearest go to nbr_dst[rank * nbr_stride] (a column of the parked lists, or the query's row in global memory).
+template <int G, int CAP, int CAND, bool DEFER>
+__device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CAND, DEFER>& S, int lane, bool active,
+                                             uint32_t* nbr_dst, int nbr_stride, int kk, float qfx, float qfy, float qfz,
+                                             float top, float g2, float e1, float& dku)
 {
     constexpr int SL = CAP / G;
     constexpr int NBL = PCP_FD_NB / G;
@@ -589,7 +591,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
                 r += dj < d ? 1u : 0u;
                 if (j != (uint32_t)e && fabsf(dj - d) <= amb2) ambig = true;
             }
-            if (r < (uint32_t)kk) S.nbr[r * 32 + slot] = __float_as_uint(S.cand[lpos[e]].w);
+            if (r < (uint32_t)kk) nbr_dst[r * nbr_stride] = __float_as_uint(S.cand[lpos[e]].w);
             if (r == (uint32_t)kk - 1u) dkl = d;
         }
     }
@@ -605,20 +607,28 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     return st;
 }
 
+// resident blocks per SM the kernel is compiled for = what its shared memory allows (deferred rows: 26 KB per block
+// at 320 candidates -> 8 blocks, 64 registers; 14.1 ms against 15.7 at 6 blocks on the 25 M-point shard)
+__host__ __device__ constexpr int pcp_fd_min_blocks(int cand, bool defer)
+{
+    return !defer ? (cand > 480 ? 3 : PCP_FK_MINB) : cand <= 320 ? 8 : cand <= 480 ? 5 : cand <= 800 ? 4 : 3;
+}
+
 // CAP: list capacity per query (>= k + room for the boundary bucket); GS: lanes per query.
 // Settles every query whose k nearest provably lie inside the 3x3x3 block of base cells around its cell; the
 // others are appended to the "far" list with the best known upper bound of their k-th squared distance
 // (+inf if none) for knn_far_kernel.
 template <int CAP, int GS, int CAND, bool FLAT, bool DEFER = false>
-static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, (CAND > 480 ? 3 : PCP_FK_MINB)) knn_fast_kernel(pcp_fknn_params P)
+static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CAND, DEFER)) knn_fast_kernel(pcp_fknn_params P)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     constexpr int NSET = 32 / GS;
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const pcp_fd_smem<CAP, GS, CAND> S(smem_raw + pcp_fd_smem<CAP, GS, CAND>::bytes(P.k) * warp, P.k);
+    using Smem = pcp_fd_smem<CAP, GS, CAND, DEFER>;
+    const Smem S(smem_raw + Smem::bytes(P.k) * warp, P.k);
     const int set = lane / GS;
-    S.sqpos[lane] = 0xffffffffu;
+    if constexpr (!DEFER) S.sqpos[lane] = 0xffffffffu;
     __syncwarp();
     int fill = 0;
     const uint32_t nitem = P.nitem_ptr ? *P.nitem_ptr : P.nitem;
@@ -644,9 +654,11 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, (CAND > 480 ? 3 : PC
         const unsigned want = __ballot_sync(0xffffffffu, lane < nq && myq.idx < P.query_limit);
         if (!want) continue;
         const int nwant = __popc(want);
-        if (fill + nwant > 32) {
-            pcp_fk_flush<pcp_fd_smem<CAP, GS, CAND>, DEFER>(P, S, lane);
-            fill = 0;
+        if constexpr (!DEFER) {
+            if (fill + nwant > 32) {
+                pcp_fk_flush<Smem, false>(P, S, lane);
+                fill = 0;
+            }
         }
         int cx, cy, cz;
         pcp_demorton(__ldg(P.ckey + cell) >> (3 * level), cx, cy, cz);
@@ -767,10 +779,21 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, (CAND > 480 ? 3 : PC
                 if (cz + 1 < dimz) dout = fminf(dout, 2.0f * hf - qfz);
                 dout = fmaxf(dout - (4.0f * e1 + 1e-6f * hf), 0.0f);
                 const float g2 = dout * dout * 0.999999f;
-                const int slot = fill + __popc(want & ((1u << sj) - 1u));
+                // DEFER: the neighbour row of the query in global memory; a row whose query is not settled here is
+                // marked unwritten again (the far kernel writes it whole)
+                uint32_t* nbr_dst;
+                int nbr_stride;
+                if constexpr (DEFER) {
+                    nbr_dst = P.nbr_out + (size_t)(first + sj) * P.k, nbr_stride = 1;
+                } else {
+                    nbr_dst = S.nbr + fill + __popc(want & ((1u << sj) - 1u)), nbr_stride = 32;
+                }
                 float dku;
-                const int st = pcp_fd_search<GS, CAP, CAND>((int)total, S, lane, active, slot, P.kk, qfx, qfy, qfz,
-                                                      top0, g2, e1, dku);
+                const int st = pcp_fd_search<GS, CAP, CAND, DEFER>((int)total, S, lane, active, nbr_dst, nbr_stride, P.kk,
+                                                                   qfx, qfy, qfz, top0, g2, e1, dku);
+                if constexpr (DEFER) {
+                    if (active && st != PCP_FD_OK && (lane & (GS - 1)) == 0) nbr_dst[0] = 0xffffffffu;
+                }
                 // collect the group results as query bits
 #pragma unroll
                 for (int g = 0; g < NSET; g++) {
@@ -788,12 +811,14 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, (CAND > 480 ? 3 : PC
             PCP_FK_DBG(5, __popc(okmask));
         }
         // ---- park the finished queries; the rest go to the far list ----
-        if ((okmask >> lane) & 1u) {
-            const int sl = fill + __popc(want & ((1u << lane) - 1u));
-            S.sqpos[sl] = first + lane;
-            S.skd[sl] = myU;
+        if constexpr (!DEFER) {
+            if ((okmask >> lane) & 1u) {
+                const int sl = fill + __popc(want & ((1u << lane) - 1u));
+                S.sqpos[sl] = first + lane;
+                S.skd[sl] = myU;
+            }
+            fill += nwant;
         }
-        fill += nwant;
         {
             const unsigned fm = want & ~okmask;
             if (fm) {
@@ -808,5 +833,5 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, (CAND > 480 ? 3 : PC
             }
         }
     }
-    pcp_fk_flush<pcp_fd_smem<CAP, GS, CAND>, DEFER>(P, S, lane);
+    if constexpr (!DEFER) pcp_fk_flush<Smem, false>(P, S, lane);
 }
