@@ -220,7 +220,19 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
                 pcp_nb_offset(lane, dx, dy, dz);
                 const int nx = lx + dx, ny = ly + dy, nz = lz + dz;
                 const int mx = (P.g.dims[0] - 1) >> level, my = (P.g.dims[1] - 1) >> level, mz = (P.g.dims[2] - 1) >> level;
-                if (nx >= 0 && ny >= 0 && nz >= 0 && nx <= mx && ny <= my && nz <= mz) {
+                bool take = nx >= 0 && ny >= 0 && nz >= 0 && nx <= mx && ny <= my && nz <= mz;
+                if (take && U != INF) {
+                    // a level cell the bound sphere does not reach holds no neighbour: its base cells need not be
+                    // enumerated at all (a query near the middle of its cell keeps a few of the 27)
+                    const double H = ldexp(P.g.h, level), sl = 1e-6 * H; // sl: rounding of the cell assignment
+                    const double ax = P.g.org[0] + (double)nx * H, ay = P.g.org[1] + (double)ny * H,
+                                 az = P.g.org[2] + (double)nz * H;
+                    const double ex = fmax(fmax(ax - q.x, q.x - (ax + H)) - sl, 0.0),
+                                 ey = fmax(fmax(ay - q.y, q.y - (ay + H)) - sl, 0.0),
+                                 ez = fmax(fmax(az - q.z, q.z - (az + H)) - sl, 0.0);
+                    take = ex * ex + ey * ey + ez * ez <= (double)U * 1.000001;
+                }
+                if (take) {
                     if (level < PCP_HLEVELS) {
                         uint32_t cn = 0;
                         if (pcp_hash_find(P.ltab, P.lmask, PCP_LKEY(level, pcp_morton(nx, ny, nz)), ca, cn)) cb = ca + cn;
