@@ -295,14 +295,20 @@ def run_gpu(args):
         s = kst[0]
         achieved = s["bytes"] / (s["ms"] * 1e-3) / 1e9
         traffic = None
+        issue = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "knn_fast_traffic.json"))).get("dram_bytes_per_launch")
+            cap = json.load(open(os.path.join(ROOT, "profiles", "knn_fast_traffic.json")))
+            traffic = cap.get("dram_bytes_per_launch")
+            issue = cap.get("issue_active_pct")
         except Exception:
             pass
         roof = {"bound": "hbm", "kernel": "knn_fast_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "kernel_ms_per_launch": s["ms"] / s["launches"], "algorithmic_bytes_per_launch": s["bytes"] / s["launches"],
-                "kernel_share_of_step": s["ms"] / (ms_total if world == 1 else e0.elapsed_time(e1))}
+                "kernel_share_of_step": s["ms"] / (ms_total if world == 1 else e0.elapsed_time(e1)),
+                # what actually limits the kernel (ncu capture under profiles/): issue slots busy, % of peak
+                "limiter": {"what": "instruction issue", "issue_slots_busy_pct": issue,
+                            "source": "profiles/knn_fast_traffic.json (ncu --set full)"}}
 
     # ---- end to end through the C ABI with host buffers ----
     e2e_ms, h2d, d2h, e2e_feat = job.time_e2e(max(1, args.steps), barrier, torch.cuda.synchronize)
