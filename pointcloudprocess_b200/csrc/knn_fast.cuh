@@ -430,7 +430,7 @@ __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_params& P, const SM&
 // the same 8 candidates per step, one shared-memory wavefront as LDS.128 against three for split x / y / z arrays.)
 template <int CAP, int GS, int CAND, bool DEFER = false> struct pcp_fd_smem {
     static constexpr int NSET = 32 / GS;
-    static_assert(CAND % 4 == 0 && CAND < 65536 && (NSET * CAP) % 2 == 0, "pcp_fd_smem: layout");
+    static_assert(CAND % GS == 0 && CAND % 4 == 0 && CAND < 65536 && (NSET * CAP) % 2 == 0, "pcp_fd_smem: layout");
     float4* cand;    // [CAND]  x, y, z relative to the leaf origin, w = sorted position
     uint32_t* hist;  // [NSET][PCP_FD_NB]
     float* ld2;      // [NSET][CAP]
@@ -494,15 +494,26 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     for (int i = 0; i < NBL; i++) hist[gl + i * G] = 0;
     __syncwarp();
     // ---- pass 1: histogram of FP32 squared distances ----
-    for (int f0 = 0; f0 < T; f0 += G) {
-        const int i = f0 + gl;
-        const float4 c = S.cand[i < T ? i : 0];
-        const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
-        const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-        // (the last bucket = beyond `top` is never counted: nothing is decided there, and it is the one address
-        // most lanes would collide on)
-        const int b = pcp_fd_bucket(d2, key0);
-        if (i < T && active && b < PCP_FD_NB - 1) atomicAdd(&hist[b], 1u);
+    // The staged block is padded to a multiple of G with points at "infinity" (beyond `top` for every query), so
+    // the loops carry no bounds test; the increment is one predicated instruction, not a divergent region (some
+    // lane of the warp takes it at almost every step, so a branch around it saves nothing and costs three).
+    const int Tpad = (T + G - 1) & ~(G - 1);
+    const float4* cp = S.cand + gl;
+    {
+        const uint32_t hist_s = (uint32_t)__cvta_generic_to_shared(hist);
+        for (int f0 = 0; f0 < Tpad; f0 += G) {
+            const float4 c = cp[f0];
+            const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
+            const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+            // (the last bucket = beyond `top` is never counted: nothing is decided there, and it is the one address
+            // most lanes would collide on)
+            const int b = (__float_as_int(d2) >> 21) - key0;
+            const unsigned take = (active && b < PCP_FD_NB - 1) ? 1u : 0u;
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p red.shared.add.u32 [%0], 1;\n\t}"
+                         :
+                         : "r"(hist_s + 4u * (uint32_t)max(b, 0)), "r"(take)
+                         : "memory");
+        }
     }
     __syncwarp();
     // ---- scan: bucket b* of the kk-th candidate; hist[b] becomes the write cursor (exclusive prefix) ----
@@ -555,17 +566,17 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     __syncwarp();
     // ---- pass 2: scatter the candidates of buckets <= b* into the list, bucket by bucket ----
     const int lim = (key0 + min(bstar, PCP_FD_NB - 2) + 1) << 21;
-    for (int f0 = 0; f0 < T; f0 += G) {
-        const int i = f0 + gl;
-        const float4 c = S.cand[i < T ? i : 0];
+    for (int f0 = 0; f0 < Tpad; f0 += G) {
+        const float4 c = cp[f0];
         const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
         const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-        // bucket(d2) <= b*  <=>  the bits of d2 lie below the upper edge of b* (one compare for the ~90 % left out)
-        if (live && i < T && __float_as_int(d2) < lim) {
+        // bucket(d2) <= b*  <=>  the bits of d2 lie below the upper edge of b* (one compare for the ~90 % left out;
+        // the padding lies beyond every edge)
+        if (live && __float_as_int(d2) < lim) {
             const int b = pcp_fd_bucket(d2, key0);
             const uint32_t at = atomicAdd(&hist[b], 1u);
             ld2[at] = d2;
-            lpos[at] = (uint16_t)i;
+            lpos[at] = (uint16_t)(f0 + gl);
         }
     }
     __syncwarp();
@@ -586,6 +597,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
             // bucket edges: an entry this close to one may belong to the other side
             if (b > 0 && d - pcp_fk_edge(b - 1, key0) <= amb2 && lo > 0) ambig = true;
             if (b < bstar && pcp_fk_edge(b, key0) - d <= amb2) ambig = true;
+#pragma unroll 1 // a bucket holds a handful of entries: unrolled by 8 the remainder code is what runs
             for (uint32_t j = lo; j < hi; j++) {
                 const float dj = ld2[j];
                 r += dj < d ? 1u : 0u;
@@ -753,6 +765,9 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
                     }
                 }
             }
+            // padding up to a multiple of GS: points no query can reach (pcp_fd_search)
+            if (lane < (int)(((total + GS - 1) & ~(uint32_t)(GS - 1)) - total))
+                S.cand[total + lane] = make_float4(1e18f, 1e18f, 1e18f, __uint_as_float(0u));
             __syncwarp();
             for (unsigned rest = want; rest;) {
                 // group g takes the g-th remaining query
