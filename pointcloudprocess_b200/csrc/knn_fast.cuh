@@ -501,6 +501,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     const float4* cp = S.cand + gl;
     {
         const uint32_t hist_s = (uint32_t)__cvta_generic_to_shared(hist);
+        const uint32_t dummy_s = (uint32_t)__cvta_generic_to_shared(S.tab + lane); // free once the block is staged
         for (int f0 = 0; f0 < Tpad; f0 += G) {
             const float4 c = cp[f0];
             const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
@@ -508,11 +509,8 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
             // (the last bucket = beyond `top` is never counted: nothing is decided there, and it is the one address
             // most lanes would collide on)
             const int b = (__float_as_int(d2) >> 21) - key0;
-            const unsigned take = (active && b < PCP_FD_NB - 1) ? 1u : 0u;
-            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %1, 0;\n\t@p red.shared.add.u32 [%0], 1;\n\t}"
-                         :
-                         : "r"(hist_s + 4u * (uint32_t)max(b, 0)), "r"(take)
-                         : "memory");
+            const bool take = active && b < PCP_FD_NB - 1;
+            asm volatile("red.shared.add.u32 [%0], 1;" : : "r"(take ? hist_s + 4u * (uint32_t)max(b, 0) : dummy_s) : "memory");
         }
     }
     __syncwarp();
