@@ -90,7 +90,7 @@ int launch_fknn(pcp_ctx* ctx, const pcp_fknn_params& P)
 int launch_fknn_dense2(pcp_ctx* ctx, const pcp_fknn_params& P)
 {
     if (P.kk <= 24) return launch_fknn_t<32, 8, PCP_FK_CAND2, true>(ctx, P);
-    return launch_fknn_t<64, 8, 1000, true>(ctx, P); // k <= 52: the first pass stages 480
+    return launch_fknn_t<64, 8, 1008, true>(ctx, P); // k <= 52: the first pass stages 480
 }
 
 template <int CAP, bool DEFER = false> int launch_far_t(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)

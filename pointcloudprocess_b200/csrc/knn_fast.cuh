@@ -430,8 +430,19 @@ __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_params& P, const SM&
 // the same 8 candidates per step, one shared-memory wavefront as LDS.128 against three for split x / y / z arrays.)
 template <int CAP, int GS, int CAND, bool DEFER = false> struct pcp_fd_smem {
     static constexpr int NSET = 32 / GS;
-    static_assert(CAND % GS == 0 && CAND % 4 == 0 && CAND < 65536 && (NSET * CAP) % 2 == 0, "pcp_fd_smem: layout");
-    float4* cand;    // [CAND]  x, y, z relative to the leaf origin, w = sorted position
+    static_assert(CAND % (2 * GS) == 0 && CAND < 65536 && (NSET * CAP) % 2 == 0, "pcp_fd_smem: layout");
+    __device__ __forceinline__ void put(uint32_t i, float x, float y, float z, uint32_t pos) const
+    {
+        float* a = reinterpret_cast<float*>(cand) + 4 * (i >> 1) + (i & 1u);
+        a[0] = x, a[2] = y, a[2 * CAND] = z, a[2 * CAND + 2] = __uint_as_float(pos);
+    }
+    __device__ __forceinline__ uint32_t pos_of(uint32_t i) const
+    {
+        return __float_as_uint(reinterpret_cast<const float*>(cand)[2 * CAND + 4 * (i >> 1) + 2 + (i & 1u)]);
+    }
+    float4* cand;    // [CAND]  candidates in PAIRS for the packed FP32 pipe: cand[p] = (x0, x1, y0, y1) and
+                     //         cand[CAND/2 + p] = (z0, z1, pos0, pos1) of candidates 2p, 2p+1; x, y, z relative to the
+                     //         leaf origin, pos = sorted position
     uint32_t* hist;  // [NSET][PCP_FD_NB]
     float* ld2;      // [NSET][CAP]
     uint16_t* lpos;  // [NSET][CAP]  candidate number
@@ -497,20 +508,27 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     // The staged block is padded to a multiple of G with points at "infinity" (beyond `top` for every query), so
     // the loops carry no bounds test; the increment is one predicated instruction, not a divergent region (some
     // lane of the warp takes it at almost every step, so a branch around it saves nothing and costs three).
-    const int Tpad = (T + G - 1) & ~(G - 1);
-    const float4* cp = S.cand + gl;
+    // Two candidates per lane and step, their distances on the packed FP32 pipe (half the FP instructions of an
+    // issue-bound loop).  (c - q)^2 here, (q - c)^2 in the reference order: the same value bit for bit.
+    const int Tpad = (T + 2 * G - 1) & ~(2 * G - 1);
+    const float4* cpa = S.cand + gl;
+    const float4* cpb = S.cand + CAND / 2 + gl;
+    const float2 nqx = make_float2(-qfx, -qfx), nqy = make_float2(-qfy, -qfy), nqz = make_float2(-qfz, -qfz);
     {
         const uint32_t hist_s = (uint32_t)__cvta_generic_to_shared(hist);
         const uint32_t dummy_s = (uint32_t)__cvta_generic_to_shared(S.tab + lane); // free once the block is staged
-        for (int f0 = 0; f0 < Tpad; f0 += G) {
-            const float4 c = cp[f0];
-            const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
-            const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+        const int key1 = active ? key0 : -0x40000000; // an idle group counts nothing: every bucket number "beyond"
+        for (int p0 = 0; p0 < Tpad / 2; p0 += G) {
+            const float4 a = cpa[p0], bb = cpb[p0];
+            const float2 dx = __fadd2_rn(make_float2(a.x, a.y), nqx), dy = __fadd2_rn(make_float2(a.z, a.w), nqy),
+                         dz = __fadd2_rn(make_float2(bb.x, bb.y), nqz);
+            const float2 d2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
             // (the last bucket = beyond `top` is never counted: nothing is decided there, and it is the one address
-            // most lanes would collide on)
-            const int b = (__float_as_int(d2) >> 21) - key0;
-            const bool take = active && b < PCP_FD_NB - 1;
-            asm volatile("red.shared.add.u32 [%0], 1;" : : "r"(take ? hist_s + 4u * (uint32_t)max(b, 0) : dummy_s) : "memory");
+            // most lanes would collide on; lanes with nothing to count hit a word of their own)
+            const int b0 = (__float_as_int(d2.x) >> 21) - key1, b1 = (__float_as_int(d2.y) >> 21) - key1;
+            const bool t0 = b0 < PCP_FD_NB - 1, t1 = b1 < PCP_FD_NB - 1;
+            asm volatile("red.shared.add.u32 [%0], 1;" : : "r"(t0 ? hist_s + 4u * (uint32_t)max(b0, 0) : dummy_s) : "memory");
+            asm volatile("red.shared.add.u32 [%0], 1;" : : "r"(t1 ? hist_s + 4u * (uint32_t)max(b1, 0) : dummy_s) : "memory");
         }
     }
     __syncwarp();
@@ -564,17 +582,24 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     __syncwarp();
     // ---- pass 2: scatter the candidates of buckets <= b* into the list, bucket by bucket ----
     const int lim = (key0 + min(bstar, PCP_FD_NB - 2) + 1) << 21;
-    for (int f0 = 0; f0 < Tpad; f0 += G) {
-        const float4 c = cp[f0];
-        const float dx = qfx - c.x, dy = qfy - c.y, dz = qfz - c.z;
-        const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
+    for (int p0 = 0; p0 < Tpad / 2; p0 += G) {
+        const float4 a = cpa[p0], bb = cpb[p0];
+        const float2 dx = __fadd2_rn(make_float2(a.x, a.y), nqx), dy = __fadd2_rn(make_float2(a.z, a.w), nqy),
+                     dz = __fadd2_rn(make_float2(bb.x, bb.y), nqz);
+        const float2 d2 = __ffma2_rn(dz, dz, __ffma2_rn(dy, dy, __fmul2_rn(dx, dx)));
         // bucket(d2) <= b*  <=>  the bits of d2 lie below the upper edge of b* (one compare for the ~90 % left out;
         // the padding lies beyond every edge)
-        if (live && __float_as_int(d2) < lim) {
-            const int b = pcp_fd_bucket(d2, key0);
-            const uint32_t at = atomicAdd(&hist[b], 1u);
-            ld2[at] = d2;
-            lpos[at] = (uint16_t)(f0 + gl);
+        if (live && min(__float_as_int(d2.x), __float_as_int(d2.y)) < lim) {
+#pragma unroll
+            for (int h = 0; h < 2; h++) {
+                const float d = h ? d2.y : d2.x;
+                if (__float_as_int(d) < lim) {
+                    const int b = pcp_fd_bucket(d, key0);
+                    const uint32_t at = atomicAdd(&hist[b], 1u);
+                    ld2[at] = d;
+                    lpos[at] = (uint16_t)(2 * (p0 + gl) + h);
+                }
+            }
         }
     }
     __syncwarp();
@@ -601,7 +626,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
                 r += dj < d ? 1u : 0u;
                 if (j != (uint32_t)e && fabsf(dj - d) <= amb2) ambig = true;
             }
-            if (r < (uint32_t)kk) nbr_dst[r * nbr_stride] = __float_as_uint(S.cand[lpos[e]].w);
+            if (r < (uint32_t)kk) nbr_dst[r * nbr_stride] = S.pos_of(lpos[e]);
             if (r == (uint32_t)kk - 1u) dkl = d;
         }
     }
@@ -746,8 +771,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
                     for (int u = 0; u < PCP_FK_STAGE_U; u++) {
                         const uint32_t f = f0 + 32 * u + lane;
                         if (f < total)
-                            S.cand[f] = make_float4((float)(r[u].x - ox), (float)(r[u].y - oy), (float)(r[u].z - oz),
-                                                    __uint_as_float(ps[u]));
+                            S.put(f, (float)(r[u].x - ox), (float)(r[u].y - oy), (float)(r[u].z - oz), ps[u]);
                     }
                 }
             } else {
@@ -758,14 +782,13 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
                     const uint32_t p = __shfl_sync(0xffffffffu, pre, nb);
                     for (uint32_t t = lane; t < c; t += 32) {
                         const pcp_rec r = pcp_load_rec(P.rec, s + t);
-                        S.cand[p + t] = make_float4((float)(r.x - ox), (float)(r.y - oy), (float)(r.z - oz),
-                                                    __uint_as_float(s + t));
+                        S.put(p + t, (float)(r.x - ox), (float)(r.y - oy), (float)(r.z - oz), s + t);
                     }
                 }
             }
-            // padding up to a multiple of GS: points no query can reach (pcp_fd_search)
-            if (lane < (int)(((total + GS - 1) & ~(uint32_t)(GS - 1)) - total))
-                S.cand[total + lane] = make_float4(1e18f, 1e18f, 1e18f, __uint_as_float(0u));
+            // padding up to a multiple of 2 GS: points no query can reach (pcp_fd_search)
+            if (lane < (int)(((total + 2 * GS - 1) & ~(uint32_t)(2 * GS - 1)) - total))
+                S.put(total + lane, 1e18f, 1e18f, 1e18f, 0u);
             __syncwarp();
             for (unsigned rest = want; rest;) {
                 // group g takes the g-th remaining query
