@@ -15,9 +15,12 @@
 //     certify  edge(b*+1) + 2*delta must lie inside the distance from the query to the faces of the
 //              scanned block, otherwise the query moves up one level (cell edge doubles) and scans point
 //              ranges straight from global memory with the whole warp;
-//   features finished queries are parked in 32 shared-memory slots; when the slots are full every lane takes
-//            one query and runs calculate_plan_parameter_h_points (calculate_feature.cpp:119-206) on its k
-//            neighbours in ascending-distance order -- neighbour lists never leave the SM.
+//   features default (DEFER): the neighbour positions of a settled query are written as a row of a scratch in
+//            global memory and features_from_list_kernel (knn_warp.cuh) fits the planes afterwards -- the search
+//            kernels stay small enough for the instruction cache and need no parked lists in shared memory.
+//            Fused variant (PCP_FK_FUSED=1, kept for comparison): finished queries are parked in 32 shared-memory
+//            slots; when the slots are full every lane takes one query and runs calculate_plan_parameter_h_points
+//            (calculate_feature.cpp:119-206) on its k neighbours in ascending-distance order.
 // Queries that overflow the list (mass ties / duplicates) go to the streaming FP64 kernel in knn_warp.cuh.
 #pragma once
 #include "knn_cell.cuh"
@@ -425,9 +428,10 @@ __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_params& P, const SM&
 // FP32 only, coordinates relative to the item's cell origin (error ~1e-7 h, see pcp_fd_e1).  Queries whose FP32
 // ordering is not provably the exact one (two candidates closer in d2 than the error bound, or a k-th distance
 // too close to the certified radius) are not settled here: they go to the far list with their upper bound.
-// CAND: staged candidates per item.  320 candidates, lists for 4 queries of 32 entries and k = 20 come to 9472
-// bytes per warp: 6 blocks of 4 warps per SM.  (Candidates stay 16-byte records: the 4 query groups of a warp read
-// the same 8 candidates per step, one shared-memory wavefront as LDS.128 against three for split x / y / z arrays.)
+// CAND: staged candidates per item.  320 candidates and lists for 4 queries of 32 entries come to 6656 bytes per
+// warp when the neighbour rows go straight to global memory (DEFER): 8 blocks of 4 warps per SM; with the parked
+// lists of the fused variant (k = 20) 9472 bytes and 6 blocks.  (The 4 query groups of a warp read the same 8
+// candidate pairs per step: two 128-byte wavefronts, LDS.128 + LDS.64, for 16 candidates.)
 template <int CAP, int GS, int CAND, bool DEFER = false> struct pcp_fd_smem {
     static constexpr int NSET = 32 / GS;
     static_assert(CAND % (2 * GS) == 0 && CAND < 65536 && (NSET * CAP) % 2 == 0, "pcp_fd_smem: layout");
