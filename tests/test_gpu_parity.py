@@ -445,8 +445,8 @@ def test_calculate_plan_parameter_rpca_mirror(ctx, orc):
 
 # ---- alternative code paths must agree bit for bit -----------------------------------------------------------
 def test_fused_and_single_pass_variants_equal_the_default_path(ctx):
-    """PCP_FK_FUSED (plane fit inside the search kernels), PCP_FK_ONEPASS (no second dense pass) and the default
-    (deferred fit, two passes) are the same function; PCP_RADIUS_WARP is the warp-per-query radius kernel."""
+    """PCP_FK_FUSED (plane fit inside the search kernels), PCP_FK_ONEPASS (no second dense pass), PCP_FK_NOFLAT (the
+    block staged cell by cell) and the default (deferred fit, two passes, flat staging) are the same function; PCP_RADIUS_WARP is the warp-per-query radius kernel."""
     import os
     import pointcloudprocess_b200 as pcp
     cloud = ctx.synth_cloud("city", 300000, seed=12)
@@ -455,7 +455,7 @@ def test_fused_and_single_pass_variants_equal_the_default_path(ctx):
     ref32 = ix.features_knn(32, want_idx=True)
     rad = ix.features_radius(0.3)
     try:
-        for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS"):
+        for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS", "PCP_FK_NOFLAT"):
             os.environ[env] = "1"
             got = ix.features_knn(20, want_idx=True)
             got32 = ix.features_knn(32, want_idx=True)
@@ -470,6 +470,6 @@ def test_fused_and_single_pass_variants_equal_the_default_path(ctx):
         assert np.array_equal(radw["counts"], rad["counts"])
         check_features_tolerance(radw["props"], radw["eig"], rad["props"], rad["eig"])
     finally:
-        for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS", "PCP_RADIUS_WARP"):
+        for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS", "PCP_FK_NOFLAT", "PCP_RADIUS_WARP"):
             os.environ.pop(env, None)
         ix.free()
