@@ -434,22 +434,23 @@ __device__ __forceinline__ void pcp_fk_flush(const pcp_fknn_params& P, const SM&
 // candidate pairs per step: two 128-byte wavefronts, LDS.128 + LDS.64, for 16 candidates.)
 template <int CAP, int GS, int CAND, bool DEFER = false> struct pcp_fd_smem {
     static constexpr int NSET = 32 / GS;
-    static_assert(CAND % (2 * GS) == 0 && CAND < 65536 && (NSET * CAP) % 2 == 0, "pcp_fd_smem: layout");
+    static_assert(CAND % (2 * GS) == 0 && 2 * CAND + 4 < 65536 && (NSET * CAP) % 2 == 0, "pcp_fd_smem: layout");
     __device__ __forceinline__ void put(uint32_t i, float x, float y, float z, uint32_t pos) const
     {
         float* a = reinterpret_cast<float*>(cand) + 4 * (i >> 1) + (i & 1u);
         a[0] = x, a[2] = y, a[2 * CAND] = z, a[2 * CAND + 2] = __uint_as_float(pos);
     }
-    __device__ __forceinline__ uint32_t pos_of(uint32_t i) const
+    // the list keeps a candidate as the word offset of its position inside the second half: 4 * pair + 2 + (0 | 1)
+    __device__ __forceinline__ uint32_t pos_at(uint32_t word) const
     {
-        return __float_as_uint(reinterpret_cast<const float*>(cand)[2 * CAND + 4 * (i >> 1) + 2 + (i & 1u)]);
+        return __float_as_uint(reinterpret_cast<const float*>(cand)[2 * CAND + word]);
     }
     float4* cand;    // [CAND]  candidates in PAIRS for the packed FP32 pipe: cand[p] = (x0, x1, y0, y1) and
                      //         cand[CAND/2 + p] = (z0, z1, pos0, pos1) of candidates 2p, 2p+1; x, y, z relative to the
                      //         leaf origin, pos = sorted position
     uint32_t* hist;  // [NSET][PCP_FD_NB]
     float* ld2;      // [NSET][CAP]
-    uint16_t* lpos;  // [NSET][CAP]  candidate number
+    uint16_t* lpos;  // [NSET][CAP]  candidate (see pos_at)
     uint32_t* tab;   // [64]  exclusive prefix of the staged runs' lengths (0xffffffff beyond the 27), first points
     uint32_t* nbr;   // [k][32]  (DEFER: none of the three -- the rows go straight to global memory)
     uint32_t* sqpos; // [32]
@@ -487,6 +488,15 @@ template <int CAP, int GS, int CAND, bool DEFER = false> struct pcp_fd_smem {
 #define PCP_FD_BEYOND 1 // fewer than kk candidates inside `top`, or list overflow: no bound known
 #define PCP_FD_AMBIG 2  // kk nearest found among the staged candidates but order / certification not provable in FP32
 #define PCP_FD_IDLE 4
+
+// acc + (x < 0): the sign bit as the increment (PTX, so that the compiler does not turn it back into a compare, a
+// select and two moves)
+__device__ __forceinline__ uint32_t pcp_add_sign(uint32_t acc, int x)
+{
+    uint32_t r;
+    asm("{\n\t.reg .u32 t;\n\tshr.u32 t, %1, 31;\n\tadd.u32 %0, %2, t;\n\t}" : "=r"(r) : "r"(x), "r"(acc));
+    return r;
+}
 
 // Every group of G lanes searches the staged block for its own query.  dku: upper bound of the k-th squared
 // distance (valid for OK and AMBIG).
@@ -601,7 +611,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
                     const int b = pcp_fd_bucket(d, key0);
                     const uint32_t at = atomicAdd(&hist[b], 1u);
                     ld2[at] = d;
-                    lpos[at] = (uint16_t)(2 * (p0 + gl) + h);
+                    lpos[at] = (uint16_t)(4 * (p0 + gl) + 2 + h);
                 }
             }
         }
@@ -620,17 +630,25 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
             const float d = ld2[e];
             const int b = pcp_fd_bucket(d, key0);
             const uint32_t lo = b ? hist[b - 1] : 0u, hi = hist[b];
-            uint32_t r = lo;
             // bucket edges: an entry this close to one may belong to the other side
             if (b > 0 && d - pcp_fk_edge(b - 1, key0) <= amb2 && lo > 0) ambig = true;
             if (b < bstar && pcp_fk_edge(b, key0) - d <= amb2) ambig = true;
+            // rank = entries of the earlier buckets + smaller entries of this one; `near` = entries within the error
+            // bound of d, the entry itself included.  Counted on the bit patterns (non-negative floats order like
+            // their bits; a difference of two such patterns, or of |x|'s and amb2's, cannot overflow): the sign bit
+            // of the difference is the increment, two instructions per count instead of compare + select + move.
+            const int dbits = __float_as_int(d), abits = __float_as_int(amb2) + 1;
+            uint32_t less = 0, near = 0;
+            const float* pj = ld2 + lo;
 #pragma unroll 1 // a bucket holds a handful of entries: unrolled by 8 the remainder code is what runs
-            for (uint32_t j = lo; j < hi; j++) {
-                const float dj = ld2[j];
-                r += dj < d ? 1u : 0u;
-                if (j != (uint32_t)e && fabsf(dj - d) <= amb2) ambig = true;
+            for (const float* const pe = ld2 + hi; pj != pe; pj++) {
+                const float dj = *pj;
+                less = pcp_add_sign(less, __float_as_int(dj) - dbits);            // dj < d
+                near = pcp_add_sign(near, __float_as_int(fabsf(dj - d)) - abits); // |dj - d| <= amb2
             }
-            if (r < (uint32_t)kk) nbr_dst[r * nbr_stride] = S.pos_of(lpos[e]);
+            const uint32_t r = lo + less;
+            if (near > 1u) ambig = true;
+            if (r < (uint32_t)kk) nbr_dst[r * nbr_stride] = S.pos_at(lpos[e]);
             if (r == (uint32_t)kk - 1u) dkl = d;
         }
     }
