@@ -212,7 +212,8 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
             struct {
                 uint32_t* p = nullptr;
             } rows;
-            const bool defer = !getenv("PCP_FK_FUSED");
+            // (the search kernels address a row by a 32-bit offset)
+            const bool defer = !getenv("PCP_FK_FUSED") && nv * (unsigned long long)k < (1ull << 32);
             if (defer) {
                 void* q = nullptr;
                 PCP_TRY(pcp_scratch_get(ctx, nv * (size_t)k * 4, &q)); // kept by the context between calls

@@ -500,10 +500,12 @@ __device__ __forceinline__ uint32_t pcp_add_sign(uint32_t acc, int x)
 
 // Every group of G lanes searches the staged block for its own query.  dku: upper bound of the k-th squared
 // distance (valid for OK and AMBIG).
-// The kk nearest go to nbr_dst[rank * nbr_stride] (a column of the parked lists, or the query's row in global memory).
+// The kk nearest go to nbr_base[nbr_off + rank * nbr_stride] (a column of the parked lists, or the query's row in
+// global memory: a 32-bit offset from the uniform base, not a pointer of its own to keep in registers).
 template <int G, int CAP, int CAND, bool DEFER>
 __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CAND, DEFER>& S, int lane, bool active,
-                                             uint32_t* nbr_dst, int nbr_stride, int kk, float qfx, float qfy, float qfz,
+                                             uint32_t* nbr_base, uint32_t nbr_off, int nbr_stride, int kk, float qfx,
+                                             float qfy, float qfz,
                                              float top, float g2, float e1, float& dku)
 {
     constexpr int SL = CAP / G;
@@ -648,7 +650,7 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
             }
             const uint32_t r = lo + less;
             if (near > 1u) ambig = true;
-            if (r < (uint32_t)kk) nbr_dst[r * nbr_stride] = S.pos_at(lpos[e]);
+            if (r < (uint32_t)kk) nbr_base[nbr_off + r * (uint32_t)nbr_stride] = S.pos_at(lpos[e]);
             if (r == (uint32_t)kk - 1u) dkl = d;
         }
     }
@@ -839,18 +841,19 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
                 const float g2 = dout * dout * 0.999999f;
                 // DEFER: the neighbour row of the query in global memory; a row whose query is not settled here is
                 // marked unwritten again (the far kernel writes it whole)
-                uint32_t* nbr_dst;
+                uint32_t* nbr_base;
+                uint32_t nbr_off;
                 int nbr_stride;
                 if constexpr (DEFER) {
-                    nbr_dst = P.nbr_out + (size_t)(first + sj) * P.k, nbr_stride = 1;
+                    nbr_base = P.nbr_out, nbr_off = (first + (uint32_t)sj) * (uint32_t)P.k, nbr_stride = 1; // < 2^32: host
                 } else {
-                    nbr_dst = S.nbr + fill + __popc(want & ((1u << sj) - 1u)), nbr_stride = 32;
+                    nbr_base = S.nbr, nbr_off = (uint32_t)(fill + __popc(want & ((1u << sj) - 1u))), nbr_stride = 32;
                 }
                 float dku;
-                const int st = pcp_fd_search<GS, CAP, CAND, DEFER>((int)total, S, lane, active, nbr_dst, nbr_stride, P.kk,
+                const int st = pcp_fd_search<GS, CAP, CAND, DEFER>((int)total, S, lane, active, nbr_base, nbr_off, nbr_stride, P.kk,
                                                                    qfx, qfy, qfz, top0, g2, e1, dku);
                 if constexpr (DEFER) {
-                    if (active && st != PCP_FD_OK && (lane & (GS - 1)) == 0) nbr_dst[0] = 0xffffffffu;
+                    if (active && st != PCP_FD_OK && (lane & (GS - 1)) == 0) nbr_base[nbr_off] = 0xffffffffu;
                 }
                 // collect the group results as query bits
 #pragma unroll
