@@ -247,6 +247,15 @@ PCP_API int pcp_features_merge(pcp_ctx* ctx, size_t nq, int k, int nlists, const
 PCP_API int pcp_centroid(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double c[3], uint64_t* count);
 PCP_API int pcp_minmax(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double mn[3], double mx[3]);
 
+/* ---- the key sort ---------------------------------------------------------------------------------------
+ * The stable LSD radix sort (csrc/sort.cu, hand-written for sm_100a) that stands where the reference sorts its cell
+ * indices (std::sort, voxel_grid.h:948) and FLANN builds its tree (kd_tree.h:795-797); exported for callers that
+ * bring their own keys and for the parity tests.  Sorts n (key, value) pairs in place by the low `bits` bits of the
+ * key (key_bytes 4 or 8); equal keys keep their order.  vals == NULL: keys only.  n < 2^30. */
+PCP_API int pcp_sort_pairs(pcp_ctx* ctx, void* keys, uint32_t* vals, size_t n, int key_bytes, int bits);
+/* Exclusive prefix sums of n uint32 values (out may equal in). */
+PCP_API int pcp_exclusive_sum_u32(pcp_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n);
+
 /* ---- synthetic clouds (bench / tests) ----------------------------------------------------
  * Fills n PointXYZRGBA records (stride 48) of the named kind; point i is a pure function of
  * (kind, n_total, seed, first + i).  kind: 0 uniform_cube, 1 strip, 2 forest, 3 city, 4 lattice.

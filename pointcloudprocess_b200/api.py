@@ -290,6 +290,22 @@ class Context:
         self._check(self.L.pcp_features_merge(self.h, int(nq), int(k), int(nlists), _ptr(xyz_lists), _ptr(d2_lists),
                                               _ptr(point_id), _ptr(props), _ptr(eig), _ptr(lps)))
 
+    def sort_pairs(self, keys, vals=None, bits=None):
+        """In-place stable sort of (key, value) pairs by the low `bits` bits of the key (pcp_sort_pairs).
+        keys: uint32 / uint64 numpy array (or device pointer tuple (ptr, n, key_bytes)); vals: uint32 or None."""
+        if isinstance(keys, tuple):
+            kp, n, kb = keys
+        else:
+            assert keys.dtype in (np.uint32, np.uint64) and keys.flags.c_contiguous
+            kp, n, kb = keys.ctypes.data, keys.shape[0], keys.dtype.itemsize
+        self._check(self.L.pcp_sort_pairs(self.h, _ptr(kp), _ptr(vals), int(n), int(kb), int(bits or 8 * kb)))
+
+    def exclusive_sum(self, a, out=None):
+        a = np.ascontiguousarray(a, dtype=np.uint32)
+        out = np.empty_like(a) if out is None else out
+        self._check(self.L.pcp_exclusive_sum_u32(self.h, a.ctypes.data, out.ctypes.data, a.shape[0]))
+        return out
+
     def centroid(self, cloud):
         p, n, s, keep = _pts(cloud)
         c = np.zeros(3)

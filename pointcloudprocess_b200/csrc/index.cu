@@ -25,7 +25,7 @@ __global__ void __launch_bounds__(256) morton_key_kernel(const char* __restrict_
         key = pcp_morton(cx, cy, cz);
     }
     keys[i] = key;
-    vals[i] = (uint32_t)i;
+    if (vals) vals[i] = (uint32_t)i;
 }
 
 __global__ void __launch_bounds__(256) gather_rec_kernel(const char* __restrict__ pts, size_t stride,
@@ -401,7 +401,7 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
         {
             StageTimer t(ctx, "index.keys", 24.0 * n);
             morton_key_kernel<<<pcp_blocks_for(n, 256), 256, 0, ctx->stream>>>(static_cast<const char*>(dpts), n,
-                                                                             stride, ix->grid, keys, vals);
+                                                                             stride, ix->grid, keys, nullptr); // values: the sort's iota
             ctx->launches++;
             IX_CUDA(cudaGetLastError());
         }
@@ -409,7 +409,7 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
             StageTimer t(ctx, "index.sort");
             int bits = 3 * ix->grid.nbits + (nv < n ? 1 : 0);
             if (nv < n && bits < 64) bits = 64; // the all-ones key of dropped points must sort last
-            IX_TRY(pcp_sort_pairs_u64(ctx, &keys, &keys_alt, &vals, &vals_alt, n, bits > 64 ? 64 : bits));
+            IX_TRY(pcp_sort_pairs_u64(ctx, &keys, &keys_alt, &vals, &vals_alt, n, bits > 64 ? 64 : bits, true));
         }
         {
             StageTimer t(ctx, "index.cells");

@@ -1,57 +1,518 @@
-// sort.cu -- round-1 implementation: CUB's onesweep radix sort and decoupled-lookback scan (library code,
-// counted as such in DESIGN.md); the hand-written sm_100a radix sort replaces it in a later round.
+// sort.cu -- the key sort that rebuilds the voxel order (voxel_grid.h:948, std::sort of the cell indices) and the
+// Morton search structure (kd_tree.h:795-797, FLANN's tree build), hand-written for sm_100a: a stable LSD radix sort
+// of (key, u32 value) pairs in the "onesweep" shape -- ONE read of the keys for the digit histograms of every pass,
+// then one read + one write of the pairs per pass with a chained (decoupled look-back) scan of the per-tile digit
+// counts -- plus the exclusive prefix sums the callers need.
+//
+// What it knows about its keys (cell keys and Morton codes):
+//   * the caller passes the number of significant key bits; the passes split them EVENLY (42 bits -> 6 x 7, not
+//     5 x 8 + 2), so every pass ranks against as few bins as possible;
+//   * a pass whose histogram is a single bin (the high cell / Morton bits of a slab of a larger cloud, a flat cloud's
+//     z bits) permutes nothing and is skipped outright -- the histograms of all passes are known before the first one;
+//   * values are the point indices 0..n-1 on entry of every caller, so the first executed pass generates them instead
+//     of reading them (4 of 24 bytes per pair and pass).
+// A pass: 256 threads rank a tile of 4096 pairs.  Keys are loaded warp-striped, every warp counts its digits in its
+// own shared histogram, thread d turns column d into warp offsets, publishes the tile's count of digit d and looks
+// back over the earlier tiles' counts (32-bit words: 2 flag bits + 30 value bits, hence n < 2^30); ranks come from
+// __match_any_sync in load order (stable); pairs are exchanged through shared memory so that the global writes are
+// runs of consecutive addresses per digit.  Tiles are handed out by an atomic counter, so a tile only ever waits for
+// tiles that are already running.
+//
+// PCP_SORT_CUB=1 routes the same calls to CUB (sort_cub.cu), kept as the A/B reference of tests/test_gpu_sort.py.
 #include "sort.cuh"
-#include <cub/cub.cuh>
+#include <cstdlib>
+
+int pcp_cub_sort_pairs_u64(pcp_ctx* ctx, unsigned long long** keys, unsigned long long** keys_alt, uint32_t** vals,
+                           uint32_t** vals_alt, size_t n, int bits);
+int pcp_cub_sort_pairs_u32(pcp_ctx* ctx, uint32_t** keys, uint32_t** keys_alt, uint32_t** vals, uint32_t** vals_alt, size_t n,
+                           int bits);
+
+namespace {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_ITEMS = 16;
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS; // 4096 pairs
+constexpr int RS_MAXPASS = 8;
+constexpr uint32_t RS_AGG = 1u << 30, RS_PRE = 2u << 30, RS_VAL = (1u << 30) - 1u;
+
+struct RsPlan {
+    int npass;
+    int shift[RS_MAXPASS];
+    int bits[RS_MAXPASS];
+};
+
+__device__ __forceinline__ uint32_t ld_relaxed(const uint32_t* p)
+{
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v)
+{
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" : : "l"(p), "r"(v) : "memory");
+}
+
+// ---- digit histograms of every pass: one read of the keys ---------------------------------------------------
+// Equal digits of neighbouring keys are the rule here (sorted or nearly sorted input, constant high bits), so a
+// warp first groups its lanes by digit (__match_any_sync) and one lane adds the group's size.
+template <typename K>
+__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const K* __restrict__ keys, uint32_t n, RsPlan plan,
+                                                             uint32_t* __restrict__ ghist)
+{
+    __shared__ uint32_t sh[RS_MAXPASS * 256];
+    for (int i = threadIdx.x; i < plan.npass * 256; i += RS_THREADS) sh[i] = 0;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31;
+    constexpr int U = 4;
+    const uint32_t stride = gridDim.x * RS_THREADS;
+    const uint32_t nround = (n + 31u) & ~31u; // whole warps stay in the loop together
+    for (uint32_t i0 = blockIdx.x * RS_THREADS + threadIdx.x; i0 < nround; i0 += U * stride) {
+        K key[U];
+        bool valid[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const uint32_t i = i0 + u * stride;
+            valid[u] = i < n;
+            key[u] = valid[u] ? keys[i] : (K)0;
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (i0 + u * stride >= nround) break; // uniform per warp
+#pragma unroll
+            for (int p = 0; p < RS_MAXPASS; p++) { // unrolled: the plan stays in the parameter bank
+                if (p >= plan.npass) break;
+                const uint32_t d = (uint32_t)(key[u] >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u);
+                const unsigned peers = __match_any_sync(0xffffffffu, valid[u] ? d : 0xffffffffu);
+                if (valid[u] && lane == (uint32_t)(__ffs(peers) - 1)) atomicAdd(&sh[p * 256 + d], (uint32_t)__popc(peers));
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < plan.npass * 256; i += RS_THREADS)
+        if (sh[i]) atomicAdd(&ghist[i], sh[i]);
+}
+
+// exclusive scan of each pass's 256 bins (in place) and the mask of the passes that a single bin makes trivial
+__global__ void __launch_bounds__(256) rs_scan_kernel(uint32_t* __restrict__ ghist, int npass, uint32_t n,
+                                                      uint32_t* __restrict__ skipmask)
+{
+    __shared__ uint32_t ws[8];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t mask = 0;
+    for (int p = 0; p < npass; p++) {
+        const uint32_t c = ghist[p * 256 + threadIdx.x];
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= (uint32_t)o) incl += v;
+        }
+        if (lane == 31) ws[warp] = incl;
+        __syncthreads();
+        uint32_t wpre = 0;
+        for (uint32_t w = 0; w < warp; w++) wpre += ws[w];
+        ghist[p * 256 + threadIdx.x] = wpre + incl - c;
+        if (__syncthreads_or(c == n)) mask |= 1u << p;
+    }
+    if (threadIdx.x == 0) *skipmask = mask;
+}
+
+// ---- one pass --------------------------------------------------------------------------------------------------
+// IOTA: the values are 0..n-1 in order (not read).
+template <typename K, bool IOTA>
+__global__ void __launch_bounds__(RS_THREADS, 2)
+    rs_pass_kernel(const K* __restrict__ kin, const uint32_t* __restrict__ vin, K* __restrict__ kout,
+                   uint32_t* __restrict__ vout, uint32_t n, int shift, int bits, const uint32_t* __restrict__ digit_base,
+                   uint32_t* __restrict__ lookback, uint32_t* __restrict__ tile_counter)
+{
+    __shared__ uint32_t s_hist[RS_WARPS][256];
+    __shared__ uint32_t s_goff[256];
+    __shared__ uint32_t s_wsum[RS_WARPS];
+    __shared__ uint32_t s_tile;
+    __shared__ __align__(16) K s_ex[RS_TILE];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
+#pragma unroll
+    for (int i = 0; i < 256 / 32; i++) s_hist[warp][lane + 32 * i] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t base = tile * (uint32_t)RS_TILE;
+    const uint32_t cnt = min((uint32_t)RS_TILE, n - base);
+    const uint32_t dmask = (1u << bits) - 1u;
+    // warp-striped: item i of lane l is element warp*512 + 32*i + l of the tile.  Elements beyond the input are
+    // all-ones keys: they fall into the last bin behind every real key (the ranking is stable), i.e. at tile
+    // positions >= cnt of the digit-sorted tile, and are never written.
+    K key[RS_ITEMS];
+    uint32_t val[RS_ITEMS];
+    const uint32_t t0 = warp * (32u * RS_ITEMS) + lane;
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+        const uint32_t t = t0 + 32u * i;
+        key[i] = t < cnt ? kin[base + t] : ~(K)0;
+    }
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+        const uint32_t t = t0 + 32u * i;
+        if constexpr (IOTA) val[i] = base + t;
+        else val[i] = t < cnt ? vin[base + t] : 0u;
+    }
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) atomicAdd(&s_hist[warp][(uint32_t)(key[i] >> shift) & dmask], 1u);
+    __syncthreads();
+    {
+        // thread = bin: offsets of the warps inside the bin, the tile's count, the bins' starts, the look-back
+        uint32_t c[RS_WARPS], tot = 0;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) {
+            const uint32_t v = s_hist[w][tid];
+            c[w] = tot;
+            tot += v;
+        }
+        const uint32_t pub = tot - (tid == dmask ? (uint32_t)RS_TILE - cnt : 0u); // the padding is not data
+        st_relaxed(lookback + (size_t)tile * 256 + tid, pub | (tile ? RS_AGG : RS_PRE));
+        uint32_t incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= (uint32_t)o) incl += v;
+        }
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        uint32_t wpre = 0;
+        for (uint32_t w = 0; w < warp; w++) wpre += s_wsum[w];
+        const uint32_t bin_start = wpre + incl - tot;
+#pragma unroll
+        for (int w = 0; w < RS_WARPS; w++) s_hist[w][tid] = bin_start + c[w];
+        uint32_t ex = 0;
+        if (tile) {
+            uint32_t t = tile - 1;
+            while (true) {
+                uint32_t v;
+                do {
+                    v = ld_relaxed(lookback + (size_t)t * 256 + tid);
+                } while ((v >> 30) == 0u);
+                ex += v & RS_VAL;
+                if (v & RS_PRE) break;
+                t--; // tile 0 always publishes a prefix
+            }
+            st_relaxed(lookback + (size_t)tile * 256 + tid, (ex + pub) | RS_PRE);
+        }
+        s_goff[tid] = digit_base[tid] + ex - bin_start; // + tile position = global position (mod 2^32 arithmetic)
+    }
+    __syncthreads();
+    // ranks in load order: peers with the same digit take consecutive places after the warp's running offset
+    uint32_t rank[RS_ITEMS];
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+        const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        const uint32_t b = s_hist[warp][d];
+        __syncwarp();
+        rank[i] = b + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+        if (lane == (uint32_t)(31 - __clz(peers))) s_hist[warp][d] = b + (uint32_t)__popc(peers);
+        __syncwarp();
+    }
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) s_ex[rank[i]] = key[i];
+    __syncthreads();
+    uint32_t gpos[RS_ITEMS];
+#pragma unroll
+    for (int j = 0; j < RS_ITEMS; j++) {
+        const uint32_t p = (uint32_t)j * RS_THREADS + tid;
+        const K kk = s_ex[p];
+        gpos[j] = s_goff[(uint32_t)(kk >> shift) & dmask] + p;
+        if (p < cnt) kout[gpos[j]] = kk;
+    }
+    __syncthreads();
+    uint32_t* s_v = reinterpret_cast<uint32_t*>(s_ex);
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) s_v[rank[i]] = val[i];
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < RS_ITEMS; j++) {
+        const uint32_t p = (uint32_t)j * RS_THREADS + tid;
+        if (p < cnt) vout[gpos[j]] = s_v[p];
+    }
+}
+
+__global__ void __launch_bounds__(256) rs_iota_kernel(uint32_t* __restrict__ v, uint32_t n)
+{
+    const uint32_t i = blockIdx.x * 256u + threadIdx.x;
+    if (i < n) v[i] = i;
+}
 
 template <typename K>
-static int sort_pairs(pcp_ctx* ctx, K** keys, K** keys_alt, uint32_t** vals, uint32_t** vals_alt, size_t n, int bits)
+int sort_pairs(pcp_ctx* ctx, K** keys, K** keys_alt, uint32_t** vals, uint32_t** vals_alt, size_t n, int bits, bool iota)
 {
     if (n == 0) return PCP_OK;
-    if (n > (size_t)INT32_MAX) return pcp_fail(ctx, PCP_ERR_RANGE, "sort: more than 2^31-1 items");
+    if (n >= ((size_t)1 << 30)) return pcp_fail(ctx, PCP_ERR_RANGE, "sort: 2^30 or more items in one call");
     if (bits < 1) bits = 1;
-    cub::DoubleBuffer<K> dk(*keys, *keys_alt);
-    cub::DoubleBuffer<uint32_t> dv(*vals, *vals_alt);
-    size_t tmp_bytes = 0;
-    PCP_CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, dk, dv, (int)n, 0, bits, ctx->stream));
-    DevBuf<char> tmp;
-    PCP_TRY(tmp.alloc(ctx, tmp_bytes));
-    PCP_CUDA_TRY(ctx, cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, dk, dv, (int)n, 0, bits, ctx->stream));
-    ctx->launches += 1 + (bits + 7) / 8;
-    K* kc = dk.Current();
-    uint32_t* vc = dv.Current();
-    if (kc != *keys) {
-        *keys_alt = *keys;
-        *keys = kc;
+    if (bits > (int)(8 * sizeof(K))) bits = (int)(8 * sizeof(K));
+    RsPlan plan;
+    plan.npass = (bits + 7) / 8;
+    for (int p = 0, at = 0; p < plan.npass; p++) { // even split: the first (bits % npass) passes take one bit more
+        plan.bits[p] = bits / plan.npass + (p < bits % plan.npass ? 1 : 0);
+        plan.shift[p] = at;
+        at += plan.bits[p];
     }
-    if (vc != *vals) {
-        *vals_alt = *vals;
-        *vals = vc;
+    const uint32_t nn = (uint32_t)n;
+    const uint32_t ntile = (nn + RS_TILE - 1) / RS_TILE;
+    // [npass][256] histograms, [8] tile counters, [8] skip mask and spare, [npass][ntile][256] look-back words
+    const size_t head = (size_t)plan.npass * 256 + 16;
+    const size_t words = head + (size_t)plan.npass * ntile * 256;
+    DevBuf<uint32_t> work;
+    PCP_TRY(work.alloc(ctx, words));
+    PCP_CUDA_TRY(ctx, cudaMemsetAsync(work.p, 0, words * 4, ctx->stream));
+    uint32_t* ghist = work.p;
+    uint32_t* counters = work.p + (size_t)plan.npass * 256;
+    uint32_t* skip_dev = counters + 8;
+    uint32_t* lookback = work.p + head;
+    int hb = ctx->sm_count * 8;
+    const int need = (int)((nn + RS_THREADS * 4 - 1) / (RS_THREADS * 4));
+    if (hb > need) hb = need;
+    rs_hist_kernel<K><<<hb, RS_THREADS, 0, ctx->stream>>>(*keys, nn, plan, ghist);
+    PCP_LAUNCH_CHECK(ctx);
+    rs_scan_kernel<<<1, 256, 0, ctx->stream>>>(ghist, plan.npass, nn, skip_dev);
+    PCP_LAUNCH_CHECK(ctx);
+    uint32_t skip = 0;
+    PCP_TRY(pcp_readback(ctx, &skip, skip_dev, 4));
+    K *kin = *keys, *kout = *keys_alt;
+    uint32_t *vin = *vals, *vout = *vals_alt;
+    bool first = true;
+    for (int p = 0; p < plan.npass; p++) {
+        if (skip & (1u << p)) continue;
+        if (first && iota)
+            rs_pass_kernel<K, true><<<ntile, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, nn, plan.shift[p], plan.bits[p],
+                                                                         ghist + p * 256, lookback + (size_t)p * ntile * 256,
+                                                                         counters + p);
+        else
+            rs_pass_kernel<K, false><<<ntile, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, nn, plan.shift[p], plan.bits[p],
+                                                                          ghist + p * 256, lookback + (size_t)p * ntile * 256,
+                                                                          counters + p);
+        PCP_LAUNCH_CHECK(ctx);
+        first = false;
+        K* tk = kin;
+        kin = kout, kout = tk;
+        uint32_t* tv = vin;
+        vin = vout, vout = tv;
     }
+    if (first && iota) { // nothing moved (every pass trivial): the values still have to exist
+        rs_iota_kernel<<<pcp_blocks_for(nn, 256), 256, 0, ctx->stream>>>(vin, nn);
+        PCP_LAUNCH_CHECK(ctx);
+    }
+    *keys = kin, *keys_alt = kout, *vals = vin, *vals_alt = vout;
     return PCP_OK;
 }
 
-int pcp_sort_pairs_u64(pcp_ctx* ctx, unsigned long long** keys, unsigned long long** keys_alt, uint32_t** vals, uint32_t** vals_alt,
-                       size_t n, int bits)
+// ---- exclusive prefix sums: per-tile sums, one block over the tile sums, per-tile scan ---------------------------
+constexpr int SC_THREADS = 256;
+constexpr int SC_ITEMS = 16;
+constexpr int SC_TILE = SC_THREADS * SC_ITEMS;
+
+template <typename T> __device__ __forceinline__ T sc_shfl_up(T v, int o) { return __shfl_up_sync(0xffffffffu, v, o); }
+template <typename T> __device__ __forceinline__ T sc_shfl(T v, int l) { return __shfl_sync(0xffffffffu, v, l); }
+
+// exclusive scan over the block of one value per thread; total returned to every thread
+template <typename T> __device__ __forceinline__ T sc_block_exclusive(T v, T* s_w /*[8]*/, T& total)
 {
-    return sort_pairs<unsigned long long>(ctx, keys, keys_alt, vals, vals_alt, n, bits);
-}
-int pcp_sort_pairs_u32(pcp_ctx* ctx, uint32_t** keys, uint32_t** keys_alt, uint32_t** vals, uint32_t** vals_alt,
-                       size_t n, int bits)
-{
-    return sort_pairs<uint32_t>(ctx, keys, keys_alt, vals, vals_alt, n, bits);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    T incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const T u = sc_shfl_up(incl, o);
+        if (lane >= o) incl += u;
+    }
+    __syncthreads(); // s_w may still be read from an earlier call
+    if (lane == 31) s_w[warp] = incl;
+    __syncthreads();
+    T wpre = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < SC_THREADS / 32; w++) {
+        const T u = s_w[w];
+        if (w < warp) wpre += u;
+        tot += u;
+    }
+    total = tot;
+    return wpre + incl - v;
 }
 
-template <typename T> static int excl_scan(pcp_ctx* ctx, const T* in, T* out, size_t n)
+template <typename T>
+__global__ void __launch_bounds__(SC_THREADS) sc_reduce_kernel(const T* __restrict__ in, size_t n, T* __restrict__ sums)
+{
+    __shared__ T s_w[SC_THREADS / 32];
+    const size_t b0 = (size_t)blockIdx.x * SC_TILE;
+    T acc = 0;
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; j++) {
+        const size_t i = b0 + (size_t)j * SC_THREADS + threadIdx.x;
+        if (i < n) acc += in[i];
+    }
+    T total;
+    sc_block_exclusive<T>(acc, s_w, total);
+    if (threadIdx.x == 0) sums[blockIdx.x] = total;
+}
+
+template <typename T> __global__ void __launch_bounds__(SC_THREADS) sc_spine_kernel(T* __restrict__ sums, size_t nb)
+{
+    __shared__ T s_w[SC_THREADS / 32];
+    T carry = 0;
+    for (size_t c0 = 0; c0 < nb; c0 += SC_THREADS) {
+        const size_t i = c0 + threadIdx.x;
+        const T v = i < nb ? sums[i] : (T)0;
+        T total;
+        const T ex = sc_block_exclusive<T>(v, s_w, total);
+        if (i < nb) sums[i] = carry + ex;
+        carry += total;
+    }
+}
+
+__device__ __forceinline__ int sc_pad(int p) { return p + (p >> 4); } // 16 consecutive items per thread: stride 17
+
+template <typename T>
+__global__ void __launch_bounds__(SC_THREADS) sc_apply_kernel(const T* __restrict__ in, T* __restrict__ out, size_t n,
+                                                              const T* __restrict__ offs)
+{
+    __shared__ T s_w[SC_THREADS / 32];
+    __shared__ T s_x[SC_TILE + SC_TILE / 16];
+    const size_t b0 = (size_t)blockIdx.x * SC_TILE;
+    // coalesced load into shared memory, then thread t scans its 16 consecutive items
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; j++) {
+        const size_t i = b0 + (size_t)j * SC_THREADS + threadIdx.x;
+        s_x[sc_pad(j * SC_THREADS + (int)threadIdx.x)] = i < n ? in[i] : (T)0;
+    }
+    __syncthreads();
+    T v[SC_ITEMS], acc = 0;
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; j++) {
+        v[j] = s_x[sc_pad((int)threadIdx.x * SC_ITEMS + j)];
+        acc += v[j];
+    }
+    T total;
+    T ex = sc_block_exclusive<T>(acc, s_w, total) + offs[blockIdx.x];
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; j++) {
+        s_x[sc_pad((int)threadIdx.x * SC_ITEMS + j)] = ex; // a thread rewrites only the slots it read
+        ex += v[j];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; j++) {
+        const size_t i = b0 + (size_t)j * SC_THREADS + threadIdx.x;
+        if (i < n) out[i] = s_x[sc_pad(j * SC_THREADS + (int)threadIdx.x)];
+    }
+}
+
+template <typename T> int excl_scan(pcp_ctx* ctx, const T* in, T* out, size_t n)
 {
     if (n == 0) return PCP_OK;
-    size_t tmp_bytes = 0;
-    PCP_CUDA_TRY(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, in, out, (int)n, ctx->stream));
-    DevBuf<char> tmp;
-    PCP_TRY(tmp.alloc(ctx, tmp_bytes));
-    PCP_CUDA_TRY(ctx, cub::DeviceScan::ExclusiveSum(tmp.p, tmp_bytes, in, out, (int)n, ctx->stream));
-    ctx->launches += 2;
+    const size_t nb = (n + SC_TILE - 1) / SC_TILE;
+    if (nb > 0x7fffffffull) return pcp_fail(ctx, PCP_ERR_RANGE, "scan: too many items");
+    DevBuf<T> sums;
+    PCP_TRY(sums.alloc(ctx, nb));
+    sc_reduce_kernel<T><<<(unsigned)nb, SC_THREADS, 0, ctx->stream>>>(in, n, sums.p);
+    PCP_LAUNCH_CHECK(ctx);
+    sc_spine_kernel<T><<<1, SC_THREADS, 0, ctx->stream>>>(sums.p, nb);
+    PCP_LAUNCH_CHECK(ctx);
+    sc_apply_kernel<T><<<(unsigned)nb, SC_THREADS, 0, ctx->stream>>>(in, out, n, sums.p);
+    PCP_LAUNCH_CHECK(ctx);
     return PCP_OK;
 }
+
+bool use_cub()
+{
+    static const bool v = getenv("PCP_SORT_CUB") != nullptr;
+    return v;
+}
+
+} // namespace
+
+int pcp_sort_pairs_u64(pcp_ctx* ctx, unsigned long long** keys, unsigned long long** keys_alt, uint32_t** vals,
+                       uint32_t** vals_alt, size_t n, int bits, bool iota_vals)
+{
+    if (use_cub()) {
+        if (iota_vals && n) {
+            rs_iota_kernel<<<pcp_blocks_for(n, 256), 256, 0, ctx->stream>>>(*vals, (uint32_t)n);
+            PCP_LAUNCH_CHECK(ctx);
+        }
+        return pcp_cub_sort_pairs_u64(ctx, keys, keys_alt, vals, vals_alt, n, bits);
+    }
+    return sort_pairs<unsigned long long>(ctx, keys, keys_alt, vals, vals_alt, n, bits, iota_vals);
+}
+int pcp_sort_pairs_u32(pcp_ctx* ctx, uint32_t** keys, uint32_t** keys_alt, uint32_t** vals, uint32_t** vals_alt, size_t n,
+                       int bits, bool iota_vals)
+{
+    if (use_cub()) {
+        if (iota_vals && n) {
+            rs_iota_kernel<<<pcp_blocks_for(n, 256), 256, 0, ctx->stream>>>(*vals, (uint32_t)n);
+            PCP_LAUNCH_CHECK(ctx);
+        }
+        return pcp_cub_sort_pairs_u32(ctx, keys, keys_alt, vals, vals_alt, n, bits);
+    }
+    return sort_pairs<uint32_t>(ctx, keys, keys_alt, vals, vals_alt, n, bits, iota_vals);
+}
+
 int pcp_exclusive_scan_u32(pcp_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n) { return excl_scan(ctx, in, out, n); }
-int pcp_exclusive_scan_u64(pcp_ctx* ctx, const unsigned long long* in, unsigned long long* out, size_t n) { return excl_scan(ctx, in, out, n); }
+int pcp_exclusive_scan_u64(pcp_ctx* ctx, const unsigned long long* in, unsigned long long* out, size_t n)
+{
+    return excl_scan(ctx, in, out, n);
+}
+// (tree order: used for predictions only, never for results -- see serial_sum.cu)
 int pcp_exclusive_scan_f64(pcp_ctx* ctx, const double* in, double* out, size_t n) { return excl_scan(ctx, in, out, n); }
+
+// In-place sort of n (key, value) pairs by the low `bits` bits of the key, stable; host or device arrays.
+// key_bytes: 4 or 8.  vals == NULL sorts (key, index) pairs and drops the indices.
+extern "C" int pcp_sort_pairs(pcp_ctx* ctx, void* keys, uint32_t* vals, size_t n, int key_bytes, int bits)
+{
+    if (!ctx || (n && !keys) || (key_bytes != 4 && key_bytes != 8))
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_sort_pairs: bad argument");
+    if (n == 0) return PCP_OK;
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    OutStage k, v;
+    PCP_TRY(k.open(ctx, keys, n * (size_t)key_bytes, true));
+    PCP_TRY(v.open(ctx, vals, n * 4, true));
+    DevBuf<char> kalt;
+    DevBuf<uint32_t> valt, vtmp;
+    PCP_TRY(kalt.alloc(ctx, n * (size_t)key_bytes));
+    PCP_TRY(valt.alloc(ctx, n));
+    uint32_t* v0 = static_cast<uint32_t*>(v.dptr);
+    if (!v0) {
+        PCP_TRY(vtmp.alloc(ctx, n));
+        v0 = vtmp.p;
+    }
+    uint32_t* v1 = valt.p;
+    StageTimer t(ctx, "sort.pairs", (double)n * (key_bytes + 4) * 2);
+    if (key_bytes == 8) {
+        unsigned long long *k0 = static_cast<unsigned long long*>(k.dptr), *k1 = reinterpret_cast<unsigned long long*>(kalt.p);
+        PCP_TRY(pcp_sort_pairs_u64(ctx, &k0, &k1, &v0, &v1, n, bits, vals == nullptr));
+        if (k0 != k.dptr) PCP_CUDA_TRY(ctx, cudaMemcpyAsync(k.dptr, k0, n * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    } else {
+        uint32_t *k0 = static_cast<uint32_t*>(k.dptr), *k1 = reinterpret_cast<uint32_t*>(kalt.p);
+        PCP_TRY(pcp_sort_pairs_u32(ctx, &k0, &k1, &v0, &v1, n, bits, vals == nullptr));
+        if (k0 != k.dptr) PCP_CUDA_TRY(ctx, cudaMemcpyAsync(k.dptr, k0, n * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    if (v.dptr && v0 != v.dptr) PCP_CUDA_TRY(ctx, cudaMemcpyAsync(v.dptr, v0, n * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    PCP_TRY(k.commit());
+    PCP_TRY(v.commit());
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}
+
+// Exclusive prefix sums of n uint32 (host or device arrays; out may equal in).
+extern "C" int pcp_exclusive_sum_u32(pcp_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n)
+{
+    if (!ctx || (n && (!in || !out))) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_exclusive_sum_u32: bad argument");
+    if (n == 0) return PCP_OK;
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    InStage i;
+    OutStage o;
+    PCP_TRY(i.open(ctx, in, n * 4));
+    PCP_TRY(o.open(ctx, out, n * 4));
+    PCP_TRY(pcp_exclusive_scan_u32(ctx, static_cast<const uint32_t*>(i.dptr), static_cast<uint32_t*>(o.dptr), n));
+    PCP_TRY(o.commit());
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    return PCP_OK;
+}

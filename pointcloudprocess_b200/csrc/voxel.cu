@@ -45,7 +45,7 @@ __global__ void __launch_bounds__(256) voxel_key_kernel(const char* __restrict__
         key = (KeyT)k;
     }
     keys[i] = key;
-    vals[i] = (uint32_t)i;
+    if (vals) vals[i] = (uint32_t)i;
     if (point_cell) {
         point_cell[3 * i + 0] = c0;
         point_cell[3 * i + 1] = c1;
@@ -226,12 +226,12 @@ int pcp_voxel_grid_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t strid
         {
             StageTimer t(ctx, "voxel.keys", 24.0 * n);
             voxel_key_kernel<uint32_t><<<nb, 256, 0, ctx->stream>>>(static_cast<const char*>(dpts), n, stride, P, keys,
-                                                                   vals, d_point_cell);
+                                                                   nullptr, d_point_cell); // values: the sort's iota
             PCP_LAUNCH_CHECK(ctx);
         }
         {
             StageTimer t(ctx, "voxel.sort");
-            PCP_TRY(pcp_sort_pairs_u32(ctx, &keys, &keys_alt, &vals, &vals_alt, n, nv < n ? 32 : sort_bits));
+            PCP_TRY(pcp_sort_pairs_u32(ctx, &keys, &keys_alt, &vals, &vals_alt, n, nv < n ? 32 : sort_bits, true));
         }
         StageTimer t(ctx, "voxel.segments");
         head_flag_kernel<uint32_t><<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(keys, nv, flag.p);
@@ -244,12 +244,12 @@ int pcp_voxel_grid_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t strid
         {
             StageTimer t(ctx, "voxel.keys", 24.0 * n);
             voxel_key_kernel<unsigned long long><<<nb, 256, 0, ctx->stream>>>(static_cast<const char*>(dpts), n, stride, P, keys,
-                                                                   vals, d_point_cell);
+                                                                   nullptr, d_point_cell);
             PCP_LAUNCH_CHECK(ctx);
         }
         {
             StageTimer t(ctx, "voxel.sort");
-            PCP_TRY(pcp_sort_pairs_u64(ctx, &keys, &keys_alt, &vals, &vals_alt, n, nv < n ? 64 : sort_bits));
+            PCP_TRY(pcp_sort_pairs_u64(ctx, &keys, &keys_alt, &vals, &vals_alt, n, nv < n ? 64 : sort_bits, true));
         }
         StageTimer t(ctx, "voxel.segments");
         head_flag_kernel<unsigned long long><<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(keys, nv, flag.p);
