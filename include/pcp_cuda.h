@@ -255,6 +255,17 @@ PCP_API int pcp_minmax(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, d
 PCP_API int pcp_sort_pairs(pcp_ctx* ctx, void* keys, uint32_t* vals, size_t n, int key_bytes, int bits);
 /* Exclusive prefix sums of n uint32 values (out may equal in). */
 PCP_API int pcp_exclusive_sum_u32(pcp_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n);
+/* The same prefix sums for callers that must not allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The scan's scratch (one word per tile of 4096 items) lives in a fixed 64 KiB array in device memory that every
+ * GPU loading the library holds until the process exits, so the call makes no cudaMalloc / cudaFree / pool
+ * allocation.  Limits: n <= PCP_NOALLOC_SCAN_MAX_N (PCP_ERR_RANGE beyond it); in and out must be DEVICE pointers
+ * on the context's GPU (PCP_ERR_INVALID otherwise; out may equal in).  The call is asynchronous on the context's
+ * stream (pcp_synchronize waits).  All calls on a device share the one array: calls that overlap on the GPU (other
+ * streams, other contexts on the same device) race; calls on one stream are ordered.  Results are bit-identical
+ * to pcp_exclusive_sum_u32's. */
+#define PCP_NOALLOC_SCAN_MAX_N (16384 * 4096) /* 67 108 864 items */
+PCP_API int pcp_exclusive_sum_u32_noalloc(pcp_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n);
 
 /* ---- synthetic clouds (bench / tests) ----------------------------------------------------
  * Fills n PointXYZRGBA records (stride 48) of the named kind; point i is a pure function of

@@ -17,7 +17,7 @@ SYMBOLS = [
     "pcp_remove_duplicate", "pcp_features_knn_ex", "pcp_remove_duplicate_centred", "pcp_serial_sum",
     "pcp_column_histogram", "pcp_select_range", "pcp_select_columns", "pcp_select_boundary", "pcp_features_merge", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
     "pcp_features_rpca", "pcp_rpca_iterations", "pcp_region_growing",
-    "pcp_sort_pairs", "pcp_exclusive_sum_u32",
+    "pcp_sort_pairs", "pcp_exclusive_sum_u32", "pcp_exclusive_sum_u32_noalloc",
     "pcp_pcd_read_header", "pcp_pcd_load", "pcp_pcd_load_many", "pcp_pcd_save", "pcp_lzf_compress", "pcp_lzf_decompress",
 ]
 
@@ -109,6 +109,7 @@ def load():
         "pcp_synth_cloud": (i32, [vp, i32, u64, u64, u64, u64, i32, vp]),
         "pcp_sort_pairs": (i32, [vp, vp, vp, sz, i32, i32]),
         "pcp_exclusive_sum_u32": (i32, [vp, vp, vp, sz]),
+        "pcp_exclusive_sum_u32_noalloc": (i32, [vp, vp, vp, sz]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)  # AttributeError here = the .so does not export what the header declares

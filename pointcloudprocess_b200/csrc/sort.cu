@@ -516,3 +516,61 @@ extern "C" int pcp_exclusive_sum_u32(pcp_ctx* ctx, const uint32_t* in, uint32_t*
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return PCP_OK;
 }
+
+// ---- the prefix sum for callers that must not allocate -------------------------------------------------------------
+// pcp_exclusive_sum_u32_noalloc: the same three kernels as pcp_exclusive_sum_u32, with the per-tile sums (the scan's
+// only scratch) in a fixed array in device memory instead of the context's arena.  No counterpart in the reference;
+// added for callers that cannot call cudaMalloc (CUDA graph capture, tight
+// serving loops).  Every GPU that loads the library holds the array (64 KiB) until the process exits.
+//   * PCP_NOALLOC_SCAN_MAX_N items at most (one scratch word per tile of 4096 items);
+//   * in / out must be DEVICE pointers on the context's GPU (a host array would need a staging buffer);
+//   * nothing in the array has to start at zero: sc_reduce_kernel writes every word [0, tiles) that the later kernels
+//     read, so the contents a previous call left behind are never seen;
+//   * every call on a device shares the one array: calls that overlap on the GPU (two streams, two contexts on the
+//     same device) race on it.  Calls on one stream are ordered and safe.
+static __device__ __align__(256) uint32_t g_noalloc_scan_sums[PCP_NOALLOC_SCAN_MAX_N / SC_TILE];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_ptr[NOALLOC_MAX_DEVICES]; // device address of the array, per device (NULL: not looked up yet)
+} // namespace
+
+extern "C" int pcp_exclusive_sum_u32_noalloc(pcp_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n)
+{
+    static_assert(PCP_NOALLOC_SCAN_MAX_N % SC_TILE == 0, "pcp_exclusive_sum_u32_noalloc: the maximum is a whole number of tiles");
+    if (!ctx || (n && (!in || !out))) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_exclusive_sum_u32_noalloc: bad argument");
+    if (n > (size_t)PCP_NOALLOC_SCAN_MAX_N)
+        return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_exclusive_sum_u32_noalloc: %zu items exceed the fixed scratch's maximum of %d "
+                                            "(PCP_NOALLOC_SCAN_MAX_N); use pcp_exclusive_sum_u32", n, PCP_NOALLOC_SCAN_MAX_N);
+    if (n == 0) return PCP_OK;
+    if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES)
+        return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_exclusive_sum_u32_noalloc: device %d beyond the %d supported", ctx->device,
+                        NOALLOC_MAX_DEVICES);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (pcp_classify(ctx, in) != PCP_PTR_DEVICE || pcp_classify(ctx, out) != PCP_PTR_DEVICE)
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_exclusive_sum_u32_noalloc: in and out must be device pointers on the "
+                                              "context's GPU (staging a host array would allocate)");
+    uint32_t* sums = nullptr;
+    {
+        // the array's name is a host-side stand-in here: its device address is looked up once per device, with that
+        // device current (set above)
+        std::lock_guard<std::mutex> g(g_noalloc_mu);
+        if (!g_noalloc_ptr[ctx->device]) {
+            void* p = nullptr;
+            PCP_CUDA_TRY(ctx, cudaGetSymbolAddress(&p, g_noalloc_scan_sums));
+            if (!p) return pcp_fail(ctx, PCP_ERR_CUDA, "pcp_exclusive_sum_u32_noalloc: cudaGetSymbolAddress returned NULL");
+            g_noalloc_ptr[ctx->device] = static_cast<uint32_t*>(p);
+        }
+        sums = g_noalloc_ptr[ctx->device];
+    }
+    const size_t nb = (n + SC_TILE - 1) / SC_TILE;
+    sc_reduce_kernel<uint32_t><<<(unsigned)nb, SC_THREADS, 0, ctx->stream>>>(in, n, sums);
+    PCP_LAUNCH_CHECK(ctx);
+    sc_spine_kernel<uint32_t><<<1, SC_THREADS, 0, ctx->stream>>>(sums, nb);
+    PCP_LAUNCH_CHECK(ctx);
+    sc_apply_kernel<uint32_t><<<(unsigned)nb, SC_THREADS, 0, ctx->stream>>>(in, out, n, sums);
+    PCP_LAUNCH_CHECK(ctx);
+    return PCP_OK; // asynchronous on the context's stream, like pcp_memcpy_async: pcp_synchronize to wait
+}
