@@ -29,9 +29,9 @@ int pcp_cub_sort_pairs_u32(pcp_ctx* ctx, uint32_t** keys, uint32_t** keys_alt, u
 
 namespace {
 
-constexpr int RS_THREADS = 256;
+constexpr int RS_THREADS = 512;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ITEMS = 16;
+constexpr int RS_ITEMS = 8;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS; // 4096 pairs
 constexpr int RS_MAXPASS = 8;
 constexpr uint32_t RS_AGG = 1u << 30, RS_PRE = 2u << 30, RS_VAL = (1u << 30) - 1u;
@@ -54,8 +54,11 @@ __device__ __forceinline__ void st_relaxed(uint32_t* p, uint32_t v)
 }
 
 // ---- digit histograms of every pass: one read of the keys ---------------------------------------------------
-// Equal digits of neighbouring keys are the rule here (sorted or nearly sorted input, constant high bits), so a
-// warp first groups its lanes by digit (__match_any_sync) and one lane adds the group's size.
+// Shared-memory atomics cost 2.7 cycles per warp instruction when the 32 lanes hit different words and 32 when they hit
+// one (measured, tools/ubench/match_atoms.cu).  Equal digits across a warp are the rule for the high digits of cell
+// keys and Morton codes (sorted or nearly sorted input, constant top bits), so the warp first ORs together the bits in
+// which its keys differ from lane 0's (two redux instructions per key, whatever the number of passes): a pass whose
+// digit bits do not differ at all is counted by one lane.
 template <typename K>
 __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const K* __restrict__ keys, uint32_t n, RsPlan plan,
                                                              uint32_t* __restrict__ ghist)
@@ -78,13 +81,23 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const K* __restrict
         }
 #pragma unroll
         for (int u = 0; u < U; u++) {
-            if (i0 + u * stride >= nround) break; // uniform per warp
+            if (i0 + u * stride - lane >= n) break; // uniform per warp: lane 0 is beyond the input
+            // (the valid lanes are a prefix of the warp; the others take lane 0's key and count nothing)
+            const K k0 = __shfl_sync(0xffffffffu, key[u], 0);
+            const K x = valid[u] ? (key[u] ^ k0) : (K)0;
+            K diff = (K)__reduce_or_sync(0xffffffffu, (uint32_t)x);
+            if constexpr (sizeof(K) == 8) diff |= (K)__reduce_or_sync(0xffffffffu, (uint32_t)(x >> 32)) << 32;
+            const uint32_t nvalid = (uint32_t)__popc(__ballot_sync(0xffffffffu, valid[u]));
 #pragma unroll
             for (int p = 0; p < RS_MAXPASS; p++) { // unrolled: the plan stays in the parameter bank
                 if (p >= plan.npass) break;
-                const uint32_t d = (uint32_t)(key[u] >> plan.shift[p]) & ((1u << plan.bits[p]) - 1u);
-                const unsigned peers = __match_any_sync(0xffffffffu, valid[u] ? d : 0xffffffffu);
-                if (valid[u] && lane == (uint32_t)(__ffs(peers) - 1)) atomicAdd(&sh[p * 256 + d], (uint32_t)__popc(peers));
+                const uint32_t m = (1u << plan.bits[p]) - 1u;
+                const uint32_t d = (uint32_t)(key[u] >> plan.shift[p]) & m;
+                if (((uint32_t)(diff >> plan.shift[p]) & m) == 0u) {
+                    if (lane == 0) atomicAdd(&sh[p * 256 + d], nvalid);
+                } else if (valid[u]) {
+                    atomicAdd(&sh[p * 256 + d], 1u);
+                }
             }
         }
     }
@@ -119,30 +132,61 @@ __global__ void __launch_bounds__(256) rs_scan_kernel(uint32_t* __restrict__ ghi
 }
 
 // ---- one pass --------------------------------------------------------------------------------------------------
+// 512 threads rank a tile of 4096 pairs, 8 per thread, warp-striped (item i of lane l = element warp*256 + 32*i + l of
+// the tile, so ranking in (warp, item, lane) order is ranking in input order: stable).
+//   counts   every warp counts its digits in its own row of s_cnt;
+//   offsets  thread d (256 of them) turns column d into the warps' starts inside bin d, publishes the tile's count of
+//            digit d and looks back over the earlier tiles for the bin's global start;
+//   ranks    item by item: the lanes with the same digit ("peers") take consecutive places after the warp's running
+//            offset.  How the peers are found is chosen per warp from the data (measured on B200, cycles per warp
+//            instruction and SM: match.any 2.4 for one distinct value, 15 for 8, 62 for 32 random ones; a shared-memory
+//            atomic 2.7 for 32 distinct addresses, 32 for one): __match_any_sync when the warp's digits are few
+//            (nearly sorted input, high digits), otherwise an atomicOr of the lane bits into a per-digit mask word;
+//   exchange keys and values go through shared memory in rank order, so the global writes are runs per digit.
 // IOTA: the values are 0..n-1 in order (not read).
+constexpr int RS_MATCH_MAX_DISTINCT = 8;
+constexpr int RS_LB = 8; // look-back words in flight per bin
+
+template <typename K> struct RsSmem {
+    static constexpr size_t CNT = 0;                                  // [RS_WARPS][256] u32
+    static constexpr size_t GOFF = CNT + (size_t)RS_WARPS * 256 * 4;  // [256] u32
+    static constexpr size_t WSUM = GOFF + 256 * 4;                    // [RS_WARPS] u32 + tile
+    static constexpr size_t EX = WSUM + 128;                          // keys [RS_TILE] K, then values [RS_TILE] u32
+    static constexpr size_t MASK_BYTES = (size_t)2 * RS_WARPS * 256 * 4; // peer masks, double-buffered: alias EX
+    static constexpr size_t EX_BYTES = (size_t)RS_TILE * (sizeof(K) + 4);
+    static constexpr size_t BYTES = EX + (EX_BYTES > MASK_BYTES ? EX_BYTES : MASK_BYTES);
+};
+
 template <typename K, bool IOTA>
 __global__ void __launch_bounds__(RS_THREADS, 2)
     rs_pass_kernel(const K* __restrict__ kin, const uint32_t* __restrict__ vin, K* __restrict__ kout,
                    uint32_t* __restrict__ vout, uint32_t n, int shift, int bits, const uint32_t* __restrict__ digit_base,
                    uint32_t* __restrict__ lookback, uint32_t* __restrict__ tile_counter)
 {
-    __shared__ uint32_t s_hist[RS_WARPS][256];
-    __shared__ uint32_t s_goff[256];
-    __shared__ uint32_t s_wsum[RS_WARPS];
-    __shared__ uint32_t s_tile;
-    __shared__ __align__(16) K s_ex[RS_TILE];
+    extern __shared__ __align__(16) unsigned char rs_smem[];
+    using L = RsSmem<K>;
+    uint32_t(*s_cnt)[256] = reinterpret_cast<uint32_t(*)[256]>(rs_smem + L::CNT);
+    uint32_t* s_goff = reinterpret_cast<uint32_t*>(rs_smem + L::GOFF);
+    uint32_t* s_wsum = reinterpret_cast<uint32_t*>(rs_smem + L::WSUM);
+    K* s_ex = reinterpret_cast<K*>(rs_smem + L::EX);
+    uint32_t* s_v = reinterpret_cast<uint32_t*>(rs_smem + L::EX + (size_t)RS_TILE * sizeof(K));
+    uint32_t* s_mask = reinterpret_cast<uint32_t*>(rs_smem + L::EX); // [2][RS_WARPS][256], dead before the exchange
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(tile_counter, 1u);
-#pragma unroll
-    for (int i = 0; i < 256 / 32; i++) s_hist[warp][lane + 32 * i] = 0;
+    if (tid == 0) s_wsum[RS_WARPS] = atomicAdd(tile_counter, 1u);
+    {
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        uint4* c4 = reinterpret_cast<uint4*>(rs_smem + L::CNT);
+        for (uint32_t i = tid; i < RS_WARPS * 256 / 4; i += RS_THREADS) c4[i] = z;
+        uint4* m4 = reinterpret_cast<uint4*>(s_mask);
+        for (uint32_t i = tid; i < 2 * RS_WARPS * 256 / 4; i += RS_THREADS) m4[i] = z;
+    }
     __syncthreads();
-    const uint32_t tile = s_tile;
+    const uint32_t tile = s_wsum[RS_WARPS];
     const uint32_t base = tile * (uint32_t)RS_TILE;
     const uint32_t cnt = min((uint32_t)RS_TILE, n - base);
     const uint32_t dmask = (1u << bits) - 1u;
-    // warp-striped: item i of lane l is element warp*512 + 32*i + l of the tile.  Elements beyond the input are
-    // all-ones keys: they fall into the last bin behind every real key (the ranking is stable), i.e. at tile
-    // positions >= cnt of the digit-sorted tile, and are never written.
+    // Elements beyond the input are all-ones keys: they fall into the last bin behind every real key (the ranking is
+    // stable), i.e. at tile positions >= cnt of the digit-sorted tile, and are never written.
     K key[RS_ITEMS];
     uint32_t val[RS_ITEMS];
     const uint32_t t0 = warp * (32u * RS_ITEMS) + lane;
@@ -157,19 +201,41 @@ __global__ void __launch_bounds__(RS_THREADS, 2)
         if constexpr (IOTA) val[i] = base + t;
         else val[i] = t < cnt ? vin[base + t] : 0u;
     }
-#pragma unroll
-    for (int i = 0; i < RS_ITEMS; i++) atomicAdd(&s_hist[warp][(uint32_t)(key[i] >> shift) & dmask], 1u);
-    __syncthreads();
+    // ---- counts; the first and the last item tell how many distinct digits the warp's instructions see ----
+    const uint32_t ltmask = (1u << lane) - 1u;
+    unsigned peers[RS_ITEMS];
+    bool use_match;
     {
-        // thread = bin: offsets of the warps inside the bin, the tile's count, the bins' starts, the look-back
-        uint32_t c[RS_WARPS], tot = 0;
+        const uint32_t d0 = (uint32_t)(key[0] >> shift) & dmask, d1 = (uint32_t)(key[RS_ITEMS - 1] >> shift) & dmask;
+        peers[0] = __match_any_sync(0xffffffffu, d0);
+        peers[RS_ITEMS - 1] = __match_any_sync(0xffffffffu, d1);
+        const int nd0 = __popc(__ballot_sync(0xffffffffu, (peers[0] & ltmask) == 0u));
+        const int nd1 = __popc(__ballot_sync(0xffffffffu, (peers[RS_ITEMS - 1] & ltmask) == 0u));
+        use_match = max(nd0, nd1) <= RS_MATCH_MAX_DISTINCT;
+    }
+    if (use_match) {
+#pragma unroll
+        for (int i = 0; i < RS_ITEMS; i++) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
+            if (i != 0 && i != RS_ITEMS - 1) peers[i] = __match_any_sync(0xffffffffu, d);
+            if ((peers[i] & ltmask) == 0u) atomicAdd(&s_cnt[warp][d], (uint32_t)__popc(peers[i])); // one lane per digit
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < RS_ITEMS; i++) atomicAdd(&s_cnt[warp][(uint32_t)(key[i] >> shift) & dmask], 1u);
+    }
+    __syncthreads();
+    uint32_t pub = 0, bin_start = 0;
+    if (tid < 256) {
+        // thread = bin: offsets of the warps inside the bin, the tile's count (published at once), the bins' starts
+        uint32_t tot = 0;
 #pragma unroll
         for (int w = 0; w < RS_WARPS; w++) {
-            const uint32_t v = s_hist[w][tid];
-            c[w] = tot;
+            const uint32_t v = s_cnt[w][tid];
+            s_cnt[w][tid] = tot;
             tot += v;
         }
-        const uint32_t pub = tot - (tid == dmask ? (uint32_t)RS_TILE - cnt : 0u); // the padding is not data
+        pub = tot - (tid == dmask ? (uint32_t)RS_TILE - cnt : 0u); // the padding is not data
         st_relaxed(lookback + (size_t)tile * 256 + tid, pub | (tile ? RS_AGG : RS_PRE));
         uint32_t incl = tot;
 #pragma unroll
@@ -178,61 +244,87 @@ __global__ void __launch_bounds__(RS_THREADS, 2)
             if (lane >= (uint32_t)o) incl += v;
         }
         if (lane == 31) s_wsum[warp] = incl;
-        __syncthreads();
+        asm volatile("bar.sync 1, 256;" ::: "memory"); // the 8 warps of the bins only
         uint32_t wpre = 0;
         for (uint32_t w = 0; w < warp; w++) wpre += s_wsum[w];
-        const uint32_t bin_start = wpre + incl - tot;
+        bin_start = wpre + incl - tot;
 #pragma unroll
-        for (int w = 0; w < RS_WARPS; w++) s_hist[w][tid] = bin_start + c[w];
+        for (int w = 0; w < RS_WARPS; w++) s_cnt[w][tid] += bin_start;
+    }
+    __syncthreads();
+    // ---- ranks in input order ----
+    uint32_t rank[RS_ITEMS];
+    if (use_match) {
+#pragma unroll
+        for (int i = 0; i < RS_ITEMS; i++) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
+            const uint32_t b = s_cnt[warp][d];
+            __syncwarp();
+            rank[i] = b + (uint32_t)__popc(peers[i] & ltmask);
+            if (lane == (uint32_t)(31 - __clz(peers[i]))) s_cnt[warp][d] = b + (uint32_t)__popc(peers[i]);
+            __syncwarp();
+        }
+    } else {
+        // peers by atomicOr into the digit's mask word; two buffers in turn, so the leader's clearing of item i's word
+        // is ordered before its next use (item i + 2) by item i + 1's barriers
+        uint32_t* mk = s_mask + warp * 256;
+#pragma unroll
+        for (int i = 0; i < RS_ITEMS; i++) {
+            const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
+            uint32_t* m = mk + (i & 1) * (RS_WARPS * 256) + d;
+            atomicOr(m, 1u << lane);
+            __syncwarp();
+            const uint32_t pm = *m;
+            const uint32_t b = s_cnt[warp][d];
+            __syncwarp();
+            rank[i] = b + (uint32_t)__popc(pm & ltmask);
+            if (lane == (uint32_t)(31 - __clz(pm))) {
+                s_cnt[warp][d] = b + (uint32_t)__popc(pm);
+                *m = 0u;
+            }
+        }
+    }
+    __syncthreads(); // the masks are dead: their memory takes the keys
+#pragma unroll
+    for (int i = 0; i < RS_ITEMS; i++) {
+        s_ex[rank[i]] = key[i];
+        s_v[rank[i]] = val[i];
+    }
+    if (tid < 256) {
+        // The look-back, as late as possible (the earlier tiles have had the whole ranking to publish) and RS_LB words
+        // at a time: a walk over the counts of the tiles before this one, back to the nearest tile that already knows
+        // its prefix, is a chain of dependent L2 round trips, and one tile per trip made the first wave of tiles
+        // (two per SM, all started together) the longest part of a pass.
         uint32_t ex = 0;
         if (tile) {
-            uint32_t t = tile - 1;
-            while (true) {
-                uint32_t v;
-                do {
-                    v = ld_relaxed(lookback + (size_t)t * 256 + tid);
-                } while ((v >> 30) == 0u);
-                ex += v & RS_VAL;
-                if (v & RS_PRE) break;
-                t--; // tile 0 always publishes a prefix
+            int t = (int)tile - 1;
+            bool done = false;
+            while (!done) {
+                uint32_t v[RS_LB];
+#pragma unroll
+                for (int j = 0; j < RS_LB; j++) v[j] = t - j >= 0 ? ld_relaxed(lookback + (size_t)(t - j) * 256 + tid) : RS_PRE;
+#pragma unroll
+                for (int j = 0; j < RS_LB; j++) {
+                    if (done || (v[j] >> 30) == 0u) break; // not published yet: load again from there
+                    ex += v[j] & RS_VAL;
+                    t--;
+                    done = (v[j] & RS_PRE) != 0u; // tile 0 always publishes a prefix; t < 0 reads as an empty prefix
+                }
             }
             st_relaxed(lookback + (size_t)tile * 256 + tid, (ex + pub) | RS_PRE);
         }
         s_goff[tid] = digit_base[tid] + ex - bin_start; // + tile position = global position (mod 2^32 arithmetic)
     }
     __syncthreads();
-    // ranks in load order: peers with the same digit take consecutive places after the warp's running offset
-    uint32_t rank[RS_ITEMS];
-#pragma unroll
-    for (int i = 0; i < RS_ITEMS; i++) {
-        const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
-        const unsigned peers = __match_any_sync(0xffffffffu, d);
-        const uint32_t b = s_hist[warp][d];
-        __syncwarp();
-        rank[i] = b + (uint32_t)__popc(peers & ((1u << lane) - 1u));
-        if (lane == (uint32_t)(31 - __clz(peers))) s_hist[warp][d] = b + (uint32_t)__popc(peers);
-        __syncwarp();
-    }
-#pragma unroll
-    for (int i = 0; i < RS_ITEMS; i++) s_ex[rank[i]] = key[i];
-    __syncthreads();
-    uint32_t gpos[RS_ITEMS];
 #pragma unroll
     for (int j = 0; j < RS_ITEMS; j++) {
         const uint32_t p = (uint32_t)j * RS_THREADS + tid;
         const K kk = s_ex[p];
-        gpos[j] = s_goff[(uint32_t)(kk >> shift) & dmask] + p;
-        if (p < cnt) kout[gpos[j]] = kk;
-    }
-    __syncthreads();
-    uint32_t* s_v = reinterpret_cast<uint32_t*>(s_ex);
-#pragma unroll
-    for (int i = 0; i < RS_ITEMS; i++) s_v[rank[i]] = val[i];
-    __syncthreads();
-#pragma unroll
-    for (int j = 0; j < RS_ITEMS; j++) {
-        const uint32_t p = (uint32_t)j * RS_THREADS + tid;
-        if (p < cnt) vout[gpos[j]] = s_v[p];
+        const uint32_t g = s_goff[(uint32_t)(kk >> shift) & dmask] + p;
+        if (p < cnt) {
+            kout[g] = kk;
+            vout[g] = s_v[p];
+        }
     }
 }
 
@@ -277,17 +369,19 @@ int sort_pairs(pcp_ctx* ctx, K** keys, K** keys_alt, uint32_t** vals, uint32_t**
     PCP_LAUNCH_CHECK(ctx);
     uint32_t skip = 0;
     PCP_TRY(pcp_readback(ctx, &skip, skip_dev, 4));
+    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(rs_pass_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RsSmem<K>::BYTES));
+    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(rs_pass_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RsSmem<K>::BYTES));
     K *kin = *keys, *kout = *keys_alt;
     uint32_t *vin = *vals, *vout = *vals_alt;
     bool first = true;
     for (int p = 0; p < plan.npass; p++) {
         if (skip & (1u << p)) continue;
         if (first && iota)
-            rs_pass_kernel<K, true><<<ntile, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, nn, plan.shift[p], plan.bits[p],
+            rs_pass_kernel<K, true><<<ntile, RS_THREADS, RsSmem<K>::BYTES, ctx->stream>>>(kin, vin, kout, vout, nn, plan.shift[p], plan.bits[p],
                                                                          ghist + p * 256, lookback + (size_t)p * ntile * 256,
                                                                          counters + p);
         else
-            rs_pass_kernel<K, false><<<ntile, RS_THREADS, 0, ctx->stream>>>(kin, vin, kout, vout, nn, plan.shift[p], plan.bits[p],
+            rs_pass_kernel<K, false><<<ntile, RS_THREADS, RsSmem<K>::BYTES, ctx->stream>>>(kin, vin, kout, vout, nn, plan.shift[p], plan.bits[p],
                                                                           ghist + p * 256, lookback + (size_t)p * ntile * 256,
                                                                           counters + p);
         PCP_LAUNCH_CHECK(ctx);
