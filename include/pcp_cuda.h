@@ -8,6 +8,10 @@
  *   - Points are (base pointer, count, byte stride); the first 24 bytes of a record are x,y,z doubles.
  *     PointXYZRGBA (point_type.h:9-82) has stride 48 with rgba at byte 32 and stamp_id at byte 36,
  *     PointC (point_type.h:300-323) stride 64, a packed double[3] array stride 24.
+ *     Stride 32 is the PACKED PointXYZRGBA: x, y, z doubles, rgba at byte 24, stamp_id at byte 28 -- exactly one
+ *     record of the binary PCD payload the reference writes for its clouds (FIELDS x y z rgba stamp_id, SIZE 8 8 8
+ *     4 4; pcd_helper.cpp:1074-1089), so a file's payload can be uploaded as stored (32 instead of 48 bytes per
+ *     point); the voxel grid / remove_duplicate entry points read and write that layout when stride == 32.
  *   - Every data pointer may be a HOST pointer (pageable or pinned) or a DEVICE pointer on the context's
  *     GPU; the library finds out with cudaPointerGetAttributes.  Host buffers are staged through the
  *     context's own device arena; device buffers are used in place.  All pointers of one call that
@@ -54,6 +58,16 @@ typedef struct pcp_point_property {
     int32_t SegmentID;
     float dis_from_point_plane;
 } pcp_point_property;
+
+/* The same record without its dead weight, for the trip over PCIe (24 bytes, lossless): Distance and curvature are
+ * PlanSegment's FLOAT members widened to double (calculate_feature.cpp:344-345), SegmentID and dis_from_point_plane
+ * are not set by calculate_plan_parameter*.  pcp_props_pack / pcp_props_unpack convert. */
+typedef struct pcp_point_property_packed {
+    float normal_x, normal_y, normal_z;
+    float Distance;
+    float curvature;
+    int32_t PointID;
+} pcp_point_property_packed;
 
 /* PlanSegment (data_struct.h:188-198) without its std::vector member, + the three eigenvalues. */
 typedef struct pcp_plan_segment {
@@ -209,6 +223,23 @@ PCP_API int pcp_voxel_grid(pcp_ctx* ctx, const void* pts, size_t n, size_t strid
  * In place: pts_inout holds *n_inout records on entry and the filtered cloud on return. */
 PCP_API int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf);
 
+/* Out of place: pts (n records) is left alone, the filtered cloud goes to pts_out (capacity n records of the same
+ * stride), *m receives its size -- no copy of the cloud is made at all (the in-place form needs two).  centre, min_b,
+ * div_b: NULL for the reference behaviour (own centroid, own box); centre alone, or all three, as
+ * pcp_remove_duplicate_centred below. */
+PCP_API int pcp_remove_duplicate_to(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, float leaf, const double* centre,
+                                    const int32_t* min_b, const int32_t* div_b, void* pts_out, size_t* m);
+
+/* LAS_POINT_PROPERTY records <-> packed records (pcp_point_property_packed).  pack: host or device arrays, on the
+ * context's stream (asynchronous when both are device arrays); unpack: plain host code on `threads` threads
+ * (<= 0: one per core), for callers that want the reference's struct back. */
+PCP_API int pcp_props_pack(pcp_ctx* ctx, const void* props, size_t n, pcp_point_property_packed* packed);
+PCP_API int pcp_props_unpack(const pcp_point_property_packed* packed, size_t n, void* props, int threads);
+/* PointXYZRGBA records (stride 48) <-> packed cloud records (stride 32, see the conventions above); host or device
+ * arrays.  unpack sets w = 1 (point_type.h:23) and zeroes the padding. */
+PCP_API int pcp_cloud_pack(pcp_ctx* ctx, const void* pts48, size_t n, void* pts32);
+PCP_API int pcp_cloud_unpack(pcp_ctx* ctx, const void* pts32, size_t n, void* pts48);
+
 /* ---- sharding (one shard per GPU; the cut follows cloud_grid.cpp's tiles) --------------------
  * remove_duplicate of a SHARD of a larger cloud: centred on the given centre (the whole cloud's serial-order
  * centroid) and voxelised in the whole cloud's grid box (min_b / div_b of the centred whole cloud,
@@ -218,6 +249,29 @@ PCP_API int pcp_remove_duplicate_centred(pcp_ctx* ctx, void* pts_inout, size_t* 
 /* compute3DCentroid's serial-order sums continued over a chunk: sum3 (in/out) holds the running x,y,z sums of
  * the points that precede the chunk, count (in/out, optional) the running number of finite points. */
 PCP_API int pcp_serial_sum(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double sum3[3], uint64_t* count);
+/* The same in two steps, for a cloud whose point order runs over several chunks or GPUs (DEVICE memory): `begin`
+ * does the parallel part for this chunk under a PREDICTED carry (an approximate sum of all points before the chunk,
+ * e.g. the tree-order sums of pcp_cloud_stats: only its binades matter; NULL = 0), `end` continues the exact
+ * running sums carry3_inout (host or device array: a device array is walked in place without synchronising, so the
+ * value can travel on to the next GPU) through the chunk -- tens of microseconds, the only sequential step of a
+ * chain of chunks -- and releases the handle (carry3_inout == NULL just releases). */
+PCP_API int pcp_serial_sum_begin(pcp_ctx* ctx, const void* dev_pts, size_t n, size_t stride, const double predicted3[3],
+                                 void** handle);
+PCP_API int pcp_serial_sum_end(void* handle, double* carry3_inout);
+/* One pass over a cloud: out10 (host or device array) = min x,y,z | max x,y,z (true extremes of the finite points;
+ * getMinMax3D's DBL_MIN seed is the caller's) | x,y,z sums in TREE order (a prediction for pcp_serial_sum_begin,
+ * never a result) | number of finite points. */
+PCP_API int pcp_cloud_stats(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double* out10);
+/* Stable partition of a cloud by destination shard: part p takes the finite points whose voxel column along `axis`
+ * lies in [bounds[p], bounds[p+1]) (columns below bounds[1] go to part 0, columns from bounds[nparts-1] up to the last
+ * part); out_pts receives the parts one after the other, input order kept inside each; counts[nparts] (host) their
+ * sizes.  At most 64 parts, stride a multiple of 16.  The sender's half of the all-to-all that moves every point
+ * to the GPU that owns its voxel. */
+PCP_API int pcp_partition_columns(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, int axis, float leaf, double centre,
+                                  int32_t min_b, const int32_t* bounds, int nparts, void* out_pts, uint64_t* counts);
+/* At most 1024 bytes of device memory read on the host, ordered behind the work submitted to the context so far and
+ * never queued behind a bulk download (a kernel writes them into mapped host memory). */
+PCP_API int pcp_peek(pcp_ctx* ctx, const void* dev_src, size_t bytes, void* host_dst);
 /* Histogram of voxel columns along `axis`: column = (int)((p + (-centre)) * (1/leaf) - min_b) as at
  * voxel_grid.h:936; bin = (column - col0) / cols_per_bin clamped to [0, nbins); counts are ADDED to hist_inout. */
 PCP_API int pcp_column_histogram(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, int axis, float leaf,

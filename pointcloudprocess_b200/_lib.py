@@ -17,7 +17,8 @@ SYMBOLS = [
     "pcp_remove_duplicate", "pcp_features_knn_ex", "pcp_remove_duplicate_centred", "pcp_serial_sum",
     "pcp_column_histogram", "pcp_select_range", "pcp_select_columns", "pcp_select_boundary", "pcp_features_merge", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
     "pcp_features_rpca", "pcp_rpca_iterations", "pcp_region_growing",
-    "pcp_sort_pairs", "pcp_exclusive_sum_u32", "pcp_exclusive_sum_u32_noalloc",
+    "pcp_remove_duplicate_to", "pcp_serial_sum_begin", "pcp_serial_sum_end", "pcp_cloud_stats", "pcp_partition_columns", "pcp_peek",
+    "pcp_props_pack", "pcp_props_unpack", "pcp_cloud_pack", "pcp_cloud_unpack", "pcp_sort_pairs", "pcp_exclusive_sum_u32", "pcp_exclusive_sum_u32_noalloc",
     "pcp_pcd_read_header", "pcp_pcd_load", "pcp_pcd_load_many", "pcp_pcd_save", "pcp_lzf_compress", "pcp_lzf_decompress",
 ]
 
@@ -108,6 +109,16 @@ def load():
         "pcp_minmax": (i32, [vp, vp, sz, sz, vp, vp]),
         "pcp_synth_cloud": (i32, [vp, i32, u64, u64, u64, u64, i32, vp]),
         "pcp_sort_pairs": (i32, [vp, vp, vp, sz, i32, i32]),
+        "pcp_remove_duplicate_to": (i32, [vp, vp, sz, sz, C.c_float, vp, vp, vp, vp, C.POINTER(sz)]),
+        "pcp_props_pack": (i32, [vp, vp, sz, vp]),
+        "pcp_serial_sum_begin": (i32, [vp, vp, sz, sz, vp, pp]),
+        "pcp_serial_sum_end": (i32, [vp, vp]),
+        "pcp_cloud_stats": (i32, [vp, vp, sz, sz, vp]),
+        "pcp_partition_columns": (i32, [vp, vp, sz, sz, i32, C.c_float, dbl, i32, vp, i32, vp, vp]),
+        "pcp_peek": (i32, [vp, vp, sz, vp]),
+        "pcp_cloud_pack": (i32, [vp, vp, sz, vp]),
+        "pcp_cloud_unpack": (i32, [vp, vp, sz, vp]),
+        "pcp_props_unpack": (i32, [vp, sz, vp, i32]),
         "pcp_exclusive_sum_u32": (i32, [vp, vp, vp, sz]),
         "pcp_exclusive_sum_u32_noalloc": (i32, [vp, vp, vp, sz]),
     }

@@ -23,6 +23,12 @@ PROP_DTYPE = np.dtype(
                "dis_from_point_plane"],
      "formats": ["<f4", "<f4", "<f4", "<f8", "<f8", "<i4", "<i4", "<f4"],
      "offsets": [0, 4, 8, 16, 24, 32, 36, 40], "itemsize": 48})
+PACKED_POINT_DTYPE = np.dtype(  # stride-32 cloud record = binary PCD payload record
+    {"names": ["x", "y", "z", "rgba", "stamp_id"], "formats": ["<f8", "<f8", "<f8", "<u4", "<u4"],
+     "offsets": [0, 8, 16, 24, 28], "itemsize": 32})
+PACKED_PROP_DTYPE = np.dtype(  # pcp_point_property_packed
+    {"names": ["normal_x", "normal_y", "normal_z", "Distance", "curvature", "PointID"],
+     "formats": ["<f4", "<f4", "<f4", "<f4", "<f4", "<i4"], "offsets": [0, 4, 8, 12, 16, 20], "itemsize": 24})
 PLAN_DTYPE = np.dtype(
     {"names": ["normal_x", "normal_y", "normal_z", "min_value", "curvature", "Distance", "eig"],
      "formats": ["<f4", "<f4", "<f4", "<f4", "<f4", "<f4", ("<f8", (3,))],
@@ -234,6 +240,34 @@ class Context:
         self._check(self.L.pcp_remove_duplicate(self.h, a.ctypes.data, C.byref(nn), a.dtype.itemsize, C.c_float(leaf)))
         return a[:nn.value].copy()
 
+    def remove_duplicate_to(self, cloud, leaf, out, centre=None, min_b=None, div_b=None):
+        """Out of place (pcp_remove_duplicate_to): cloud is a (ptr, n, stride) tuple or host array, `out` a device
+        pointer / host array with room for n records; returns m."""
+        p, n, s, keep = _pts(cloud)
+        m = C.c_size_t(0)
+        c = None if centre is None else np.ascontiguousarray(centre, dtype=np.float64)
+        mb = None if min_b is None else np.ascontiguousarray(min_b, dtype=np.int32)
+        db = None if div_b is None else np.ascontiguousarray(div_b, dtype=np.int32)
+        self._check(self.L.pcp_remove_duplicate_to(self.h, p, n, s, C.c_float(leaf), _ptr(c), _ptr(mb), _ptr(db), _ptr(out),
+                                                   C.byref(m)))
+        return m.value
+
+    def cloud_pack(self, pts48, n, pts32):
+        self._check(self.L.pcp_cloud_pack(self.h, _ptr(pts48), int(n), _ptr(pts32)))
+
+    def cloud_unpack(self, pts32, n, pts48):
+        self._check(self.L.pcp_cloud_unpack(self.h, _ptr(pts32), int(n), _ptr(pts48)))
+
+    def props_pack(self, props, n, packed):
+        self._check(self.L.pcp_props_pack(self.h, _ptr(props), int(n), _ptr(packed)))
+
+    def props_unpack(self, packed, n=None, threads=0):
+        packed = np.ascontiguousarray(packed)
+        n = len(packed) if n is None else n
+        out = np.zeros(n, dtype=PROP_DTYPE)
+        self._check(self.L.pcp_props_unpack(packed.ctypes.data, n, out.ctypes.data, int(threads)))
+        return out
+
     # ---- sharding primitives (SURVEY 8e) ----
     def remove_duplicate_centred(self, cloud, leaf, centre, min_b, div_b):
         """In place on a (ptr, n, stride) device tuple; returns m."""
@@ -254,16 +288,59 @@ class Context:
         self._check(self.L.pcp_serial_sum(self.h, p, n, s, acc.ctypes.data, C.byref(cnt)))
         return acc, cnt.value
 
-    def column_histogram(self, cloud, axis, leaf, centre, min_b, col0, cols_per_bin, hist):
+    def cloud_stats(self, cloud, out=None):
+        """-> 10 doubles: min xyz, max xyz, tree-order sums xyz, finite count (host array unless `out` is a device pointer)."""
         p, n, s, keep = _pts(cloud)
-        assert hist.dtype == np.uint64 and hist.flags.c_contiguous
-        self._check(self.L.pcp_column_histogram(self.h, p, n, s, axis, C.c_float(leaf), float(centre), int(min_b),
-                                                int(col0), int(cols_per_bin), hist.shape[0], hist.ctypes.data))
+        ret = None
+        if out is None:
+            ret = np.zeros(10)
+            out = ret
+        self._check(self.L.pcp_cloud_stats(self.h, p, n, s, _ptr(out)))
+        return ret
 
-    def select_range(self, cloud, axis, lo, hi, out):
+    def serial_sum_begin(self, cloud, predicted3=None):
+        p, n, s, keep = _pts(cloud)
+        h = C.c_void_p()
+        pred = None if predicted3 is None else np.ascontiguousarray(predicted3, dtype=np.float64)
+        self._check(self.L.pcp_serial_sum_begin(self.h, p, n, s, _ptr(pred), C.byref(h)))
+        return h
+
+    def serial_sum_end(self, handle, carry3):
+        """carry3: host numpy array of 3 doubles (updated in place) or a device pointer."""
+        self._check(self.L.pcp_serial_sum_end(handle, _ptr(carry3)))
+
+    def partition_columns(self, cloud, axis, leaf, centre, min_b, bounds, out):
+        p, n, s, keep = _pts(cloud)
+        b = np.ascontiguousarray(bounds, dtype=np.int32)
+        counts = np.zeros(len(b) - 1, dtype=np.uint64)
+        self._check(self.L.pcp_partition_columns(self.h, p, n, s, int(axis), C.c_float(leaf), float(centre), int(min_b),
+                                                 b.ctypes.data, len(b) - 1, _ptr(out), counts.ctypes.data))
+        return counts
+
+    def peek(self, dev_ptr, dtype, count=1):
+        out = np.zeros(count, dtype=dtype)
+        self._check(self.L.pcp_peek(self.h, _ptr(dev_ptr), out.nbytes, out.ctypes.data))
+        return out
+
+    def column_histogram(self, cloud, axis, leaf, centre, min_b, col0, cols_per_bin, hist):
+        """hist: uint64 numpy array, or a (device pointer, nbins) tuple; counts are ADDED."""
+        p, n, s, keep = _pts(cloud)
+        if isinstance(hist, tuple):
+            hp, nb = hist
+        else:
+            assert hist.dtype == np.uint64 and hist.flags.c_contiguous
+            hp, nb = hist.ctypes.data, hist.shape[0]
+        self._check(self.L.pcp_column_histogram(self.h, p, n, s, axis, C.c_float(leaf), float(centre), int(min_b),
+                                                int(col0), int(cols_per_bin), int(nb), _ptr(hp)))
+
+    def select_range(self, cloud, axis, lo, hi, out, cap=None):
+        """cap: records `out` has room for, when that is less than the input's size (checked after the fact: the
+        selections of this package are a small fraction of their input)."""
         p, n, s, keep = _pts(cloud)
         m = C.c_size_t(0)
         self._check(self.L.pcp_select_range(self.h, p, n, s, axis, float(lo), float(hi), _ptr(out), C.byref(m)))
+        if cap is not None and m.value > cap:
+            raise _lib.PcpError(-4, "select_range: %d records selected, room for %d" % (m.value, cap))
         return m.value
 
     def select_boundary(self, cloud, axis, kth_d2, lo, hi, cap, out_idx, out_xyz):

@@ -338,40 +338,123 @@ __global__ void __launch_bounds__(96) ss_small_kernel(const char* __restrict__ p
 
 } // namespace
 
-// carry != 0: d_sum3 holds the running sums of the points that precede this chunk (chunked / sharded clouds)
-int pcp_serial_sum_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, double* d_sum3, int carry)
+struct pcp_serial_plan {
+    const char* p = nullptr;
+    size_t n = 0, stride = 0, nleaf = 0, ngroup = 0, nsuper = 0;
+    DevBuf<Xfer> leafx, groupx, superx;
+};
+
+int pcp_serial_sum_prepare(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, const double* d_pred3, pcp_serial_plan** out)
 {
-    const char* p = static_cast<const char*>(dpts);
-    if (n < 16384) {
-        ss_small_kernel<<<1, 96, 0, ctx->stream>>>(p, n, stride, d_sum3, carry);
+    pcp_serial_plan* P = new pcp_serial_plan();
+    *out = P;
+    P->p = static_cast<const char*>(dpts);
+    P->n = n, P->stride = stride;
+    if (n < 16384) return PCP_OK; // small clouds are walked element by element in `finish`
+    const size_t nleaf = P->nleaf = (n + SS_LEAF - 1) / SS_LEAF;
+    const size_t ngroup = P->ngroup = (nleaf + SS_FAN - 1) / SS_FAN;
+    const size_t nsuper = P->nsuper = (ngroup + SS_FAN - 1) / SS_FAN;
+    DevBuf<double> lsum, lpre;
+    PCP_TRY(lsum.alloc(ctx, 3 * nleaf));
+    PCP_TRY(lpre.alloc(ctx, 3 * nleaf));
+    PCP_TRY(P->leafx.alloc(ctx, 3 * nleaf));
+    PCP_TRY(P->groupx.alloc(ctx, 3 * ngroup));
+    PCP_TRY(P->superx.alloc(ctx, 3 * nsuper));
+    const int wide = ctx->sm_count * 16; // 4 warps per block, grid-stride over leaves
+    const int blocks = (int)(((nleaf + 3) / 4 < (size_t)wide) ? (nleaf + 3) / 4 : (size_t)wide);
+    ss_leaf_sum_kernel<<<blocks, 128, 0, ctx->stream>>>(P->p, n, stride, nleaf, lsum.p);
+    PCP_LAUNCH_CHECK(ctx);
+    for (int a = 0; a < 3; a++) PCP_TRY(pcp_exclusive_scan_f64(ctx, lsum.p + a * nleaf, lpre.p + a * nleaf, nleaf));
+    ss_leaf_xfer_kernel<<<blocks, 128, 0, ctx->stream>>>(P->p, n, stride, nleaf, lpre.p, d_pred3, P->leafx.p);
+    PCP_LAUNCH_CHECK(ctx);
+    const int gb = (int)((3 * ngroup + 3) / 4 < (size_t)wide ? (3 * ngroup + 3) / 4 : (size_t)wide);
+    ss_group_kernel<<<gb, 128, 0, ctx->stream>>>(P->leafx.p, nleaf, ngroup, P->groupx.p);
+    PCP_LAUNCH_CHECK(ctx);
+    const int sb = (int)((3 * nsuper + 3) / 4 < (size_t)wide ? (3 * nsuper + 3) / 4 : (size_t)wide);
+    ss_group_kernel<<<sb, 128, 0, ctx->stream>>>(P->groupx.p, ngroup, nsuper, P->superx.p);
+    PCP_LAUNCH_CHECK(ctx);
+    return PCP_OK;
+}
+
+int pcp_serial_sum_finish(pcp_ctx* ctx, pcp_serial_plan* P, double* d_carry3)
+{
+    if (P->n < 16384) {
+        ss_small_kernel<<<1, 96, 0, ctx->stream>>>(P->p, P->n, P->stride, d_carry3, 1);
         PCP_LAUNCH_CHECK(ctx);
         return PCP_OK;
     }
-    const size_t nleaf = (n + SS_LEAF - 1) / SS_LEAF;
-    const size_t ngroup = (nleaf + SS_FAN - 1) / SS_FAN;
-    const size_t nsuper = (ngroup + SS_FAN - 1) / SS_FAN;
-    DevBuf<double> lsum, lpre;
-    DevBuf<Xfer> leafx, groupx, superx;
-    PCP_TRY(lsum.alloc(ctx, 3 * nleaf));
-    PCP_TRY(lpre.alloc(ctx, 3 * nleaf));
-    PCP_TRY(leafx.alloc(ctx, 3 * nleaf));
-    PCP_TRY(groupx.alloc(ctx, 3 * ngroup));
-    PCP_TRY(superx.alloc(ctx, 3 * nsuper));
-    const int wide = ctx->sm_count * 16; // 4 warps per block, grid-stride over leaves
-    const int blocks = (int)(((nleaf + 3) / 4 < (size_t)wide) ? (nleaf + 3) / 4 : (size_t)wide);
-    ss_leaf_sum_kernel<<<blocks, 128, 0, ctx->stream>>>(p, n, stride, nleaf, lsum.p);
-    PCP_LAUNCH_CHECK(ctx);
-    for (int a = 0; a < 3; a++) PCP_TRY(pcp_exclusive_scan_f64(ctx, lsum.p + a * nleaf, lpre.p + a * nleaf, nleaf));
-    ss_leaf_xfer_kernel<<<blocks, 128, 0, ctx->stream>>>(p, n, stride, nleaf, lpre.p, carry ? d_sum3 : nullptr, leafx.p);
-    PCP_LAUNCH_CHECK(ctx);
-    const int gb = (int)((3 * ngroup + 3) / 4 < (size_t)wide ? (3 * ngroup + 3) / 4 : (size_t)wide);
-    ss_group_kernel<<<gb, 128, 0, ctx->stream>>>(leafx.p, nleaf, ngroup, groupx.p);
-    PCP_LAUNCH_CHECK(ctx);
-    const int sb = (int)((3 * nsuper + 3) / 4 < (size_t)wide ? (3 * nsuper + 3) / 4 : (size_t)wide);
-    ss_group_kernel<<<sb, 128, 0, ctx->stream>>>(groupx.p, ngroup, nsuper, superx.p);
-    PCP_LAUNCH_CHECK(ctx);
-    ss_walk_kernel<<<1, 96, 0, ctx->stream>>>(p, n, stride, leafx.p, nleaf, groupx.p, ngroup, superx.p, nsuper, d_sum3,
-                                            carry, nullptr);
+    ss_walk_kernel<<<1, 96, 0, ctx->stream>>>(P->p, P->n, P->stride, P->leafx.p, P->nleaf, P->groupx.p, P->ngroup, P->superx.p,
+                                            P->nsuper, d_carry3, 1, nullptr);
     PCP_LAUNCH_CHECK(ctx);
     return PCP_OK;
+}
+
+void pcp_serial_sum_release(pcp_ctx*, pcp_serial_plan* P) { delete P; }
+
+// carry != 0: d_sum3 holds the running sums of the points that precede this chunk (chunked / sharded clouds)
+int pcp_serial_sum_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stride, double* d_sum3, int carry)
+{
+    if (!carry) PCP_CUDA_TRY(ctx, cudaMemsetAsync(d_sum3, 0, 24, ctx->stream));
+    pcp_serial_plan* P = nullptr;
+    int st = pcp_serial_sum_prepare(ctx, dpts, n, stride, carry ? d_sum3 : nullptr, &P);
+    if (st == PCP_OK) st = pcp_serial_sum_finish(ctx, P, d_sum3);
+    pcp_serial_sum_release(ctx, P);
+    return st;
+}
+
+// ---- C ABI of the two-step form (include/pcp_cuda.h) ----------------------------------------------------------------
+struct pcp_serial_handle {
+    pcp_ctx* ctx;
+    pcp_serial_plan* plan;
+};
+
+extern "C" int pcp_serial_sum_begin(pcp_ctx* ctx, const void* dev_pts, size_t n, size_t stride, const double predicted3[3],
+                                    void** handle)
+{
+    if (!ctx || !handle || stride < 24 || (n && !dev_pts)) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_serial_sum_begin: bad argument");
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    if (n && pcp_classify(ctx, dev_pts) != PCP_PTR_DEVICE)
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_serial_sum_begin: the cloud must be in device memory (it is read again by pcp_serial_sum_end)");
+    DevBuf<double> pred;
+    if (predicted3) {
+        PCP_TRY(pred.alloc(ctx, 3));
+        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(pred.p, predicted3, 24, cudaMemcpyDefault, ctx->stream));
+    }
+    pcp_serial_plan* P = nullptr;
+    const int st = pcp_serial_sum_prepare(ctx, dev_pts, n, stride, predicted3 ? pred.p : nullptr, &P);
+    if (st != PCP_OK) {
+        pcp_serial_sum_release(ctx, P);
+        return st;
+    }
+    *handle = new pcp_serial_handle{ctx, P};
+    return PCP_OK;
+}
+
+extern "C" int pcp_serial_sum_end(void* handle, double* carry3_inout)
+{
+    pcp_serial_handle* H = static_cast<pcp_serial_handle*>(handle);
+    if (!H) return PCP_ERR_INVALID;
+    pcp_ctx* ctx = H->ctx;
+    int st = PCP_OK;
+    {
+        std::lock_guard<std::recursive_mutex> lock(ctx->mu);
+        cudaSetDevice(ctx->device);
+        if (carry3_inout) {
+            // device array: walked in place, no synchronisation (the value can travel on to the next GPU);
+            // host array: staged through the context
+            if (pcp_classify(ctx, carry3_inout) == PCP_PTR_DEVICE) {
+                st = pcp_serial_sum_finish(ctx, H->plan, carry3_inout);
+            } else {
+                DevBuf<double> c;
+                st = c.alloc(ctx, 3);
+                if (st == PCP_OK && cudaMemcpyAsync(c.p, carry3_inout, 24, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) st = PCP_ERR_CUDA;
+                if (st == PCP_OK) st = pcp_serial_sum_finish(ctx, H->plan, c.p);
+                if (st == PCP_OK) st = pcp_readback(ctx, carry3_inout, c.p, 24);
+            }
+        }
+        pcp_serial_sum_release(ctx, H->plan);
+    }
+    delete H;
+    return st;
 }

@@ -359,3 +359,111 @@ extern "C" int pcp_features_merge(pcp_ctx* ctx, size_t nq, int k, int nlists, co
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return PCP_OK;
 }
+
+// ---- redistribution: stable partition of a cloud by destination shard ---------------------------------------------
+namespace {
+
+#define PCP_MAX_PARTS 64
+
+struct PartParams {
+    int axis, nparts;
+    double centre, inv_leaf;
+    int min_b;
+    int bounds[PCP_MAX_PARTS + 1];
+};
+
+__global__ void __launch_bounds__(256) part_key_kernel(const char* __restrict__ pts, size_t n, size_t stride, PartParams P,
+                                                       uint32_t* __restrict__ keys)
+{
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double* p = reinterpret_cast<const double*>(pts + i * stride);
+    const double x = p[0], y = p[1], z = p[2];
+    uint32_t key = (uint32_t)P.nparts; // non-finite points belong to no voxel: they go last and are not counted
+    if (isfinite(x) && isfinite(y) && isfinite(z)) {
+        const int c = column_of(P.axis == 0 ? x : (P.axis == 1 ? y : z), P.centre, P.inv_leaf, P.min_b);
+        int part = 0;
+        while (part + 1 < P.nparts && c >= P.bounds[part + 1]) part++;
+        key = (uint32_t)part;
+    }
+    keys[i] = key;
+}
+
+__global__ void __launch_bounds__(256) part_gather_kernel(const char* __restrict__ pts, size_t stride,
+                                                          const uint32_t* __restrict__ order, size_t n, char* __restrict__ out)
+{
+    // 16-byte granules, consecutive threads move consecutive granules of a record
+    const size_t g = stride >> 4;
+    const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (t >= n * g) return;
+    const size_t i = t / g, b = (t % g) << 4;
+    *reinterpret_cast<uint4*>(out + i * stride + b) = *reinterpret_cast<const uint4*>(pts + (size_t)order[i] * stride + b);
+}
+
+__global__ void __launch_bounds__(256) part_count_kernel(const uint32_t* __restrict__ sorted_keys, size_t n, int nparts,
+                                                         unsigned long long* __restrict__ first /*[nparts + 2]*/)
+{
+    // first[p] = first position holding a key >= p
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i > n) return;
+    const uint32_t cur = i < n ? sorted_keys[i] : (uint32_t)nparts + 1u;
+    const uint32_t prev = i > 0 ? sorted_keys[i - 1] : 0xffffffffu; // "-1"
+    for (uint32_t p = prev + 1u; p <= cur && p <= (uint32_t)nparts + 1u; p++) first[p] = i;
+}
+
+} // namespace
+
+extern "C" int pcp_partition_columns(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, int axis, float leaf, double centre,
+                                     int32_t min_b, const int32_t* bounds, int nparts, void* out_pts, uint64_t* counts)
+{
+    if (!ctx || !bounds || !counts || nparts < 1 || nparts > PCP_MAX_PARTS || stride < 32 || (stride & 15) || axis < 0 || axis > 2 ||
+        !(leaf > 0) || (n && (!pts || !out_pts)))
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_partition_columns: bad argument (stride must be a multiple of 16, at most %d parts)",
+                        PCP_MAX_PARTS);
+    for (int p = 0; p < nparts; p++) counts[p] = 0;
+    if (n == 0) return PCP_OK;
+    if (n >= ((size_t)1 << 30)) return pcp_fail(ctx, PCP_ERR_RANGE, "pcp_partition_columns: 2^30 or more points");
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    InStage in;
+    OutStage o;
+    PCP_TRY(in.open(ctx, pts, n * stride));
+    PCP_TRY(o.open(ctx, out_pts, n * stride));
+    PartParams P;
+    P.axis = axis, P.nparts = nparts, P.centre = centre, P.inv_leaf = 1.0 / (double)leaf, P.min_b = min_b;
+    for (int p = 0; p <= nparts; p++) P.bounds[p] = bounds[p];
+    DevBuf<uint32_t> k0, k1, v0, v1;
+    DevBuf<unsigned long long> first;
+    PCP_TRY(k0.alloc(ctx, n));
+    PCP_TRY(k1.alloc(ctx, n));
+    PCP_TRY(v0.alloc(ctx, n));
+    PCP_TRY(v1.alloc(ctx, n));
+    PCP_TRY(first.alloc(ctx, (size_t)nparts + 2));
+    StageTimer t(ctx, "shard.partition", 2.0 * stride * n);
+    part_key_kernel<<<pcp_blocks_for(n, 256), 256, 0, ctx->stream>>>(static_cast<const char*>(in.dptr), n, stride, P, k0.p);
+    PCP_LAUNCH_CHECK(ctx);
+    uint32_t *keys = k0.p, *keys_alt = k1.p, *vals = v0.p, *vals_alt = v1.p;
+    int bits = 1;
+    while ((1 << bits) < nparts + 1) bits++;
+    PCP_TRY(pcp_sort_pairs_u32(ctx, &keys, &keys_alt, &vals, &vals_alt, n, bits, true)); // stable: input order kept inside a part
+    part_count_kernel<<<pcp_blocks_for(n + 1, 256), 256, 0, ctx->stream>>>(keys, n, nparts, first.p);
+    PCP_LAUNCH_CHECK(ctx);
+    part_gather_kernel<<<pcp_blocks_for(n * (stride >> 4), 256), 256, 0, ctx->stream>>>(static_cast<const char*>(in.dptr), stride, vals,
+                                                                                       n, static_cast<char*>(o.dptr));
+    PCP_LAUNCH_CHECK(ctx);
+    unsigned long long hf[PCP_MAX_PARTS + 2];
+    PCP_TRY(pcp_readback(ctx, hf, first.p, ((size_t)nparts + 2) * 8));
+    for (int p = 0; p < nparts; p++) counts[p] = hf[p + 1] - hf[p];
+    PCP_TRY(o.commit((size_t)hf[nparts] * stride));
+    return PCP_OK;
+}
+
+// A few bytes of device memory read on the host, ordered behind the work submitted to the context so far, without
+// queueing behind a bulk download on a copy lane (a kernel writes them into mapped host memory).
+extern "C" int pcp_peek(pcp_ctx* ctx, const void* dev_src, size_t bytes, void* host_dst)
+{
+    if (!ctx || !dev_src || !host_dst || bytes > PCP_READBACK_MAX) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_peek: bad argument (at most %d bytes)", PCP_READBACK_MAX);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    return pcp_readback(ctx, host_dst, dev_src, bytes);
+}

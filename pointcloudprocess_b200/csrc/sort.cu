@@ -6,12 +6,14 @@
 //
 // What it knows about its keys (cell keys and Morton codes):
 //   * the caller passes the number of significant key bits; the passes split them EVENLY (42 bits -> 6 x 7, not
-//     5 x 8 + 2), so every pass ranks against as few bins as possible;
+//     5 x 8 + 2), so every pass ranks against as few bins as possible.  PCP_SORT_DIGIT9=1 allows 9-bit digits where
+//     that saves a whole pass (42 bits -> 5 passes): measured at 25 M pairs it gains 10 % on clustered keys (Morton
+//     codes of points in voxel order) and loses 8 % on keys in random order (shorter runs per bin), so it is off;
 //   * a pass whose histogram is a single bin (the high cell / Morton bits of a slab of a larger cloud, a flat cloud's
 //     z bits) permutes nothing and is skipped outright -- the histograms of all passes are known before the first one;
 //   * values are the point indices 0..n-1 on entry of every caller, so the first executed pass generates them instead
 //     of reading them (4 of 24 bytes per pair and pass).
-// A pass: 256 threads rank a tile of 4096 pairs.  Keys are loaded warp-striped, every warp counts its digits in its
+// A pass: 512 threads rank a tile of 4096 pairs.  Keys are loaded warp-striped, every warp counts its digits in its
 // own shared histogram, thread d turns column d into warp offsets, publishes the tile's count of digit d and looks
 // back over the earlier tiles' counts (32-bit words: 2 flag bits + 30 value bits, hence n < 2^30); ranks come from
 // __match_any_sync in load order (stable); pairs are exchanged through shared memory so that the global writes are
@@ -34,6 +36,7 @@ constexpr int RS_WARPS = RS_THREADS / 32;
 constexpr int RS_ITEMS = 8;
 constexpr int RS_TILE = RS_THREADS * RS_ITEMS; // 4096 pairs
 constexpr int RS_MAXPASS = 8;
+constexpr int RS_NBMAX = 512; // bins of the widest digit (9 bits); histograms are laid out with this stride
 constexpr uint32_t RS_AGG = 1u << 30, RS_PRE = 2u << 30, RS_VAL = (1u << 30) - 1u;
 
 struct RsPlan {
@@ -63,8 +66,8 @@ template <typename K>
 __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const K* __restrict__ keys, uint32_t n, RsPlan plan,
                                                              uint32_t* __restrict__ ghist)
 {
-    __shared__ uint32_t sh[RS_MAXPASS * 256];
-    for (int i = threadIdx.x; i < plan.npass * 256; i += RS_THREADS) sh[i] = 0;
+    __shared__ uint32_t sh[RS_MAXPASS * RS_NBMAX];
+    for (int i = threadIdx.x; i < plan.npass * RS_NBMAX; i += RS_THREADS) sh[i] = 0;
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31;
     constexpr int U = 4;
@@ -94,38 +97,39 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const K* __restrict
                 const uint32_t m = (1u << plan.bits[p]) - 1u;
                 const uint32_t d = (uint32_t)(key[u] >> plan.shift[p]) & m;
                 if (((uint32_t)(diff >> plan.shift[p]) & m) == 0u) {
-                    if (lane == 0) atomicAdd(&sh[p * 256 + d], nvalid);
+                    if (lane == 0) atomicAdd(&sh[p * RS_NBMAX + d], nvalid);
                 } else if (valid[u]) {
-                    atomicAdd(&sh[p * 256 + d], 1u);
+                    atomicAdd(&sh[p * RS_NBMAX + d], 1u);
                 }
             }
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < plan.npass * 256; i += RS_THREADS)
+    for (int i = threadIdx.x; i < plan.npass * RS_NBMAX; i += RS_THREADS)
         if (sh[i]) atomicAdd(&ghist[i], sh[i]);
 }
 
-// exclusive scan of each pass's 256 bins (in place) and the mask of the passes that a single bin makes trivial
-__global__ void __launch_bounds__(256) rs_scan_kernel(uint32_t* __restrict__ ghist, int npass, uint32_t n,
-                                                      uint32_t* __restrict__ skipmask)
+// exclusive scan of each pass's bins (in place) and the mask of the passes that a single bin makes trivial
+__global__ void __launch_bounds__(RS_NBMAX) rs_scan_kernel(uint32_t* __restrict__ ghist, int npass, uint32_t n,
+                                                           uint32_t* __restrict__ skipmask)
 {
-    __shared__ uint32_t ws[8];
+    __shared__ uint32_t ws[RS_NBMAX / 32];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t mask = 0;
     for (int p = 0; p < npass; p++) {
-        const uint32_t c = ghist[p * 256 + threadIdx.x];
+        const uint32_t c = ghist[p * RS_NBMAX + threadIdx.x];
         uint32_t incl = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= (uint32_t)o) incl += v;
         }
+        __syncthreads(); // ws of the pass before is read no more
         if (lane == 31) ws[warp] = incl;
         __syncthreads();
         uint32_t wpre = 0;
         for (uint32_t w = 0; w < warp; w++) wpre += ws[w];
-        ghist[p * 256 + threadIdx.x] = wpre + incl - c;
+        ghist[p * RS_NBMAX + threadIdx.x] = wpre + incl - c;
         if (__syncthreads_or(c == n)) mask |= 1u << p;
     }
     if (threadIdx.x == 0) *skipmask = mask;
@@ -147,38 +151,38 @@ __global__ void __launch_bounds__(256) rs_scan_kernel(uint32_t* __restrict__ ghi
 constexpr int RS_MATCH_MAX_DISTINCT = 8;
 constexpr int RS_LB = 8; // look-back words in flight per bin
 
-template <typename K> struct RsSmem {
-    static constexpr size_t CNT = 0;                                  // [RS_WARPS][256] u32
-    static constexpr size_t GOFF = CNT + (size_t)RS_WARPS * 256 * 4;  // [256] u32
-    static constexpr size_t WSUM = GOFF + 256 * 4;                    // [RS_WARPS] u32 + tile
+template <typename K, int NB> struct RsSmem {
+    static constexpr size_t CNT = 0;                                  // [RS_WARPS][NB] u32
+    static constexpr size_t GOFF = CNT + (size_t)RS_WARPS * NB * 4;  // [NB] u32
+    static constexpr size_t WSUM = GOFF + NB * 4;                    // [RS_WARPS] u32 + tile
     static constexpr size_t EX = WSUM + 128;                          // keys [RS_TILE] K, then values [RS_TILE] u32
-    static constexpr size_t MASK_BYTES = (size_t)2 * RS_WARPS * 256 * 4; // peer masks, double-buffered: alias EX
+    static constexpr size_t MASK_BYTES = (size_t)2 * RS_WARPS * NB * 4; // peer masks, double-buffered: alias EX
     static constexpr size_t EX_BYTES = (size_t)RS_TILE * (sizeof(K) + 4);
     static constexpr size_t BYTES = EX + (EX_BYTES > MASK_BYTES ? EX_BYTES : MASK_BYTES);
 };
 
-template <typename K, bool IOTA>
+template <typename K, bool IOTA, int NB>
 __global__ void __launch_bounds__(RS_THREADS, 2)
     rs_pass_kernel(const K* __restrict__ kin, const uint32_t* __restrict__ vin, K* __restrict__ kout,
                    uint32_t* __restrict__ vout, uint32_t n, int shift, int bits, const uint32_t* __restrict__ digit_base,
                    uint32_t* __restrict__ lookback, uint32_t* __restrict__ tile_counter)
 {
     extern __shared__ __align__(16) unsigned char rs_smem[];
-    using L = RsSmem<K>;
-    uint32_t(*s_cnt)[256] = reinterpret_cast<uint32_t(*)[256]>(rs_smem + L::CNT);
+    using L = RsSmem<K, NB>;
+    uint32_t(*s_cnt)[NB] = reinterpret_cast<uint32_t(*)[NB]>(rs_smem + L::CNT);
     uint32_t* s_goff = reinterpret_cast<uint32_t*>(rs_smem + L::GOFF);
     uint32_t* s_wsum = reinterpret_cast<uint32_t*>(rs_smem + L::WSUM);
     K* s_ex = reinterpret_cast<K*>(rs_smem + L::EX);
     uint32_t* s_v = reinterpret_cast<uint32_t*>(rs_smem + L::EX + (size_t)RS_TILE * sizeof(K));
-    uint32_t* s_mask = reinterpret_cast<uint32_t*>(rs_smem + L::EX); // [2][RS_WARPS][256], dead before the exchange
+    uint32_t* s_mask = reinterpret_cast<uint32_t*>(rs_smem + L::EX); // [2][RS_WARPS][NB], dead before the exchange
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s_wsum[RS_WARPS] = atomicAdd(tile_counter, 1u);
     {
         const uint4 z = make_uint4(0, 0, 0, 0);
         uint4* c4 = reinterpret_cast<uint4*>(rs_smem + L::CNT);
-        for (uint32_t i = tid; i < RS_WARPS * 256 / 4; i += RS_THREADS) c4[i] = z;
+        for (uint32_t i = tid; i < RS_WARPS * NB / 4; i += RS_THREADS) c4[i] = z;
         uint4* m4 = reinterpret_cast<uint4*>(s_mask);
-        for (uint32_t i = tid; i < 2 * RS_WARPS * 256 / 4; i += RS_THREADS) m4[i] = z;
+        for (uint32_t i = tid; i < 2 * RS_WARPS * NB / 4; i += RS_THREADS) m4[i] = z;
     }
     __syncthreads();
     const uint32_t tile = s_wsum[RS_WARPS];
@@ -226,7 +230,7 @@ __global__ void __launch_bounds__(RS_THREADS, 2)
     }
     __syncthreads();
     uint32_t pub = 0, bin_start = 0;
-    if (tid < 256) {
+    if (tid < NB) {
         // thread = bin: offsets of the warps inside the bin, the tile's count (published at once), the bins' starts
         uint32_t tot = 0;
 #pragma unroll
@@ -236,7 +240,7 @@ __global__ void __launch_bounds__(RS_THREADS, 2)
             tot += v;
         }
         pub = tot - (tid == dmask ? (uint32_t)RS_TILE - cnt : 0u); // the padding is not data
-        st_relaxed(lookback + (size_t)tile * 256 + tid, pub | (tile ? RS_AGG : RS_PRE));
+        st_relaxed(lookback + (size_t)tile * NB + tid, pub | (tile ? RS_AGG : RS_PRE));
         uint32_t incl = tot;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -244,7 +248,8 @@ __global__ void __launch_bounds__(RS_THREADS, 2)
             if (lane >= (uint32_t)o) incl += v;
         }
         if (lane == 31) s_wsum[warp] = incl;
-        asm volatile("bar.sync 1, 256;" ::: "memory"); // the 8 warps of the bins only
+        if constexpr (NB == RS_THREADS) __syncthreads();
+        else asm volatile("bar.sync 1, %0;" ::"n"(NB) : "memory"); // the warps of the bins only
         uint32_t wpre = 0;
         for (uint32_t w = 0; w < warp; w++) wpre += s_wsum[w];
         bin_start = wpre + incl - tot;
@@ -267,11 +272,11 @@ __global__ void __launch_bounds__(RS_THREADS, 2)
     } else {
         // peers by atomicOr into the digit's mask word; two buffers in turn, so the leader's clearing of item i's word
         // is ordered before its next use (item i + 2) by item i + 1's barriers
-        uint32_t* mk = s_mask + warp * 256;
+        uint32_t* mk = s_mask + warp * NB;
 #pragma unroll
         for (int i = 0; i < RS_ITEMS; i++) {
             const uint32_t d = (uint32_t)(key[i] >> shift) & dmask;
-            uint32_t* m = mk + (i & 1) * (RS_WARPS * 256) + d;
+            uint32_t* m = mk + (i & 1) * (RS_WARPS * NB) + d;
             atomicOr(m, 1u << lane);
             __syncwarp();
             const uint32_t pm = *m;
@@ -290,7 +295,7 @@ __global__ void __launch_bounds__(RS_THREADS, 2)
         s_ex[rank[i]] = key[i];
         s_v[rank[i]] = val[i];
     }
-    if (tid < 256) {
+    if (tid < NB) {
         // The look-back, as late as possible (the earlier tiles have had the whole ranking to publish) and RS_LB words
         // at a time: a walk over the counts of the tiles before this one, back to the nearest tile that already knows
         // its prefix, is a chain of dependent L2 round trips, and one tile per trip made the first wave of tiles
@@ -302,7 +307,7 @@ __global__ void __launch_bounds__(RS_THREADS, 2)
             while (!done) {
                 uint32_t v[RS_LB];
 #pragma unroll
-                for (int j = 0; j < RS_LB; j++) v[j] = t - j >= 0 ? ld_relaxed(lookback + (size_t)(t - j) * 256 + tid) : RS_PRE;
+                for (int j = 0; j < RS_LB; j++) v[j] = t - j >= 0 ? ld_relaxed(lookback + (size_t)(t - j) * NB + tid) : RS_PRE;
 #pragma unroll
                 for (int j = 0; j < RS_LB; j++) {
                     if (done || (v[j] >> 30) == 0u) break; // not published yet: load again from there
@@ -311,7 +316,7 @@ __global__ void __launch_bounds__(RS_THREADS, 2)
                     done = (v[j] & RS_PRE) != 0u; // tile 0 always publishes a prefix; t < 0 reads as an empty prefix
                 }
             }
-            st_relaxed(lookback + (size_t)tile * 256 + tid, (ex + pub) | RS_PRE);
+            st_relaxed(lookback + (size_t)tile * NB + tid, (ex + pub) | RS_PRE);
         }
         s_goff[tid] = digit_base[tid] + ex - bin_start; // + tile position = global position (mod 2^32 arithmetic)
     }
@@ -334,6 +339,24 @@ __global__ void __launch_bounds__(256) rs_iota_kernel(uint32_t* __restrict__ v, 
     if (i < n) v[i] = i;
 }
 
+template <typename K, int NB>
+int launch_pass(pcp_ctx* ctx, bool iota, const K* kin, const uint32_t* vin, K* kout, uint32_t* vout, uint32_t nn, uint32_t ntile,
+                int shift, int bits, const uint32_t* digit_base, uint32_t* lookback, uint32_t* counter)
+{
+    constexpr size_t smem = RsSmem<K, NB>::BYTES;
+    if (iota) {
+        PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(rs_pass_kernel<K, true, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        rs_pass_kernel<K, true, NB><<<ntile, RS_THREADS, smem, ctx->stream>>>(kin, vin, kout, vout, nn, shift, bits, digit_base,
+                                                                            lookback, counter);
+    } else {
+        PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(rs_pass_kernel<K, false, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        rs_pass_kernel<K, false, NB><<<ntile, RS_THREADS, smem, ctx->stream>>>(kin, vin, kout, vout, nn, shift, bits, digit_base,
+                                                                             lookback, counter);
+    }
+    PCP_LAUNCH_CHECK(ctx);
+    return PCP_OK;
+}
+
 template <typename K>
 int sort_pairs(pcp_ctx* ctx, K** keys, K** keys_alt, uint32_t** vals, uint32_t** vals_alt, size_t n, int bits, bool iota)
 {
@@ -341,50 +364,50 @@ int sort_pairs(pcp_ctx* ctx, K** keys, K** keys_alt, uint32_t** vals, uint32_t**
     if (n >= ((size_t)1 << 30)) return pcp_fail(ctx, PCP_ERR_RANGE, "sort: 2^30 or more items in one call");
     if (bits < 1) bits = 1;
     if (bits > (int)(8 * sizeof(K))) bits = (int)(8 * sizeof(K));
+    // digits of at most 8 bits (9 with PCP_SORT_DIGIT9, see the header); the bits are split evenly, the first
+    // (bits % npass) passes take one bit more
+    static const int max_digit = getenv("PCP_SORT_DIGIT9") ? 9 : 8;
     RsPlan plan;
     plan.npass = (bits + 7) / 8;
-    for (int p = 0, at = 0; p < plan.npass; p++) { // even split: the first (bits % npass) passes take one bit more
+    if ((bits + max_digit - 1) / max_digit < plan.npass) plan.npass = (bits + max_digit - 1) / max_digit;
+    for (int p = 0, at = 0; p < plan.npass; p++) {
         plan.bits[p] = bits / plan.npass + (p < bits % plan.npass ? 1 : 0);
         plan.shift[p] = at;
         at += plan.bits[p];
     }
     const uint32_t nn = (uint32_t)n;
     const uint32_t ntile = (nn + RS_TILE - 1) / RS_TILE;
-    // [npass][256] histograms, [8] tile counters, [8] skip mask and spare, [npass][ntile][256] look-back words
-    const size_t head = (size_t)plan.npass * 256 + 16;
-    const size_t words = head + (size_t)plan.npass * ntile * 256;
+    // [npass][512] histograms, [8] tile counters, [8] skip mask and spare, [npass][ntile][512] look-back words
+    const size_t head = (size_t)plan.npass * RS_NBMAX + 16;
+    const size_t words = head + (size_t)plan.npass * ntile * RS_NBMAX;
     DevBuf<uint32_t> work;
     PCP_TRY(work.alloc(ctx, words));
     PCP_CUDA_TRY(ctx, cudaMemsetAsync(work.p, 0, words * 4, ctx->stream));
     uint32_t* ghist = work.p;
-    uint32_t* counters = work.p + (size_t)plan.npass * 256;
+    uint32_t* counters = work.p + (size_t)plan.npass * RS_NBMAX;
     uint32_t* skip_dev = counters + 8;
     uint32_t* lookback = work.p + head;
-    int hb = ctx->sm_count * 8;
+    int hb = ctx->sm_count * 4;
     const int need = (int)((nn + RS_THREADS * 4 - 1) / (RS_THREADS * 4));
     if (hb > need) hb = need;
     rs_hist_kernel<K><<<hb, RS_THREADS, 0, ctx->stream>>>(*keys, nn, plan, ghist);
     PCP_LAUNCH_CHECK(ctx);
-    rs_scan_kernel<<<1, 256, 0, ctx->stream>>>(ghist, plan.npass, nn, skip_dev);
+    rs_scan_kernel<<<1, RS_NBMAX, 0, ctx->stream>>>(ghist, plan.npass, nn, skip_dev);
     PCP_LAUNCH_CHECK(ctx);
     uint32_t skip = 0;
     PCP_TRY(pcp_readback(ctx, &skip, skip_dev, 4));
-    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(rs_pass_kernel<K, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RsSmem<K>::BYTES));
-    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(rs_pass_kernel<K, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RsSmem<K>::BYTES));
     K *kin = *keys, *kout = *keys_alt;
     uint32_t *vin = *vals, *vout = *vals_alt;
     bool first = true;
     for (int p = 0; p < plan.npass; p++) {
         if (skip & (1u << p)) continue;
-        if (first && iota)
-            rs_pass_kernel<K, true><<<ntile, RS_THREADS, RsSmem<K>::BYTES, ctx->stream>>>(kin, vin, kout, vout, nn, plan.shift[p], plan.bits[p],
-                                                                         ghist + p * 256, lookback + (size_t)p * ntile * 256,
-                                                                         counters + p);
+        uint32_t* lb = lookback + (size_t)p * ntile * RS_NBMAX;
+        if (plan.bits[p] > 8)
+            PCP_TRY((launch_pass<K, 512>(ctx, first && iota, kin, vin, kout, vout, nn, ntile, plan.shift[p], plan.bits[p],
+                                         ghist + p * RS_NBMAX, lb, counters + p)));
         else
-            rs_pass_kernel<K, false><<<ntile, RS_THREADS, RsSmem<K>::BYTES, ctx->stream>>>(kin, vin, kout, vout, nn, plan.shift[p], plan.bits[p],
-                                                                          ghist + p * 256, lookback + (size_t)p * ntile * 256,
-                                                                          counters + p);
-        PCP_LAUNCH_CHECK(ctx);
+            PCP_TRY((launch_pass<K, 256>(ctx, first && iota, kin, vin, kout, vout, nn, ntile, plan.shift[p], plan.bits[p],
+                                         ghist + p * RS_NBMAX, lb, counters + p)));
         first = false;
         K* tk = kin;
         kin = kout, kout = tk;

@@ -96,8 +96,11 @@ __global__ void __launch_bounds__(128) voxel_centroid_kernel(const char* __restr
         if (P.use_shift) p[0] = __dadd_rn(p[0], P.shift[0]), p[1] = __dadd_rn(p[1], P.shift[1]), p[2] = __dadd_rn(p[2], P.shift[2]);
         double v[8];
         if (downsample_all) {
-            uint32_t rgba = *reinterpret_cast<const uint32_t*>(rec + 32);
-            uint32_t stamp = *reinterpret_cast<const uint32_t*>(rec + 36);
+            // PointXYZRGBA keeps rgba / stamp_id at bytes 32 / 36; the packed 32-byte record (a PCD binary payload
+            // record: x, y, z, rgba, stamp_id) at 24 / 28
+            const size_t ao = stride == 32 ? 24 : 32;
+            uint32_t rgba = *reinterpret_cast<const uint32_t*>(rec + ao);
+            uint32_t stamp = *reinterpret_cast<const uint32_t*>(rec + ao + 4);
             v[0] = (double)(float)p[0];
             v[1] = (double)(float)p[1];
             v[2] = (double)(float)p[2];
@@ -128,18 +131,23 @@ __global__ void __launch_bounds__(128) voxel_centroid_kernel(const char* __restr
     od[0] = s[0];
     od[1] = s[1];
     od[2] = s[2];
-    if (out_stride >= 32) od[3] = 1.0;
-    if (out_stride >= 40) {
-        uint32_t rgb = 0, stamp = 0;
-        if (downsample_all) {
-            float r = (float)s[5], g = (float)s[6], bl = (float)s[7];
-            rgb = (uint32_t)(((int)r << 16) | ((int)g << 8) | (int)bl);
-            stamp = (uint32_t)s[4]; // cvt.rzi.u32.f64 == static_cast<uint32_t> for in-range values
-        }
-        *reinterpret_cast<uint32_t*>(o + 32) = rgb;
-        *reinterpret_cast<uint32_t*>(o + 36) = stamp;
+    uint32_t rgb = 0, stamp = 0;
+    if (downsample_all) {
+        float r = (float)s[5], g = (float)s[6], bl = (float)s[7];
+        rgb = (uint32_t)(((int)r << 16) | ((int)g << 8) | (int)bl);
+        stamp = (uint32_t)s[4]; // cvt.rzi.u32.f64 == static_cast<uint32_t> for in-range values
     }
-    if (out_stride >= 48) *reinterpret_cast<uint64_t*>(o + 40) = 0ull;
+    if (out_stride == 32 && downsample_all) { // packed record: no w, no padding
+        *reinterpret_cast<uint32_t*>(o + 24) = rgb;
+        *reinterpret_cast<uint32_t*>(o + 28) = stamp;
+    } else {
+        if (out_stride >= 32) od[3] = 1.0;
+        if (out_stride >= 40) {
+            *reinterpret_cast<uint32_t*>(o + 32) = rgb;
+            *reinterpret_cast<uint32_t*>(o + 36) = stamp;
+        }
+        if (out_stride >= 48) *reinterpret_cast<uint64_t*>(o + 40) = 0ull;
+    }
     if (cell_count) cell_count[c] = (int32_t)(e - b);
 }
 
@@ -284,8 +292,8 @@ extern "C" int pcp_voxel_grid(pcp_ctx* ctx, const void* pts, size_t n, size_t st
 {
     if (!ctx || !m || !leaf || stride < 24 || (n && (!pts || !out_pts)))
         return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_voxel_grid: bad argument");
-    if (downsample_all && stride < 40)
-        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_voxel_grid: downsample_all needs rgba/stamp_id (stride >= 40)");
+    if (downsample_all && stride < 32)
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_voxel_grid: downsample_all needs rgba/stamp_id (stride 32 packed, or >= 40)");
     std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     InStage in;
@@ -326,21 +334,35 @@ extern "C" int pcp_centroid(pcp_ctx* ctx, const void* pts, size_t n, size_t stri
 }
 
 // centre == NULL: the cloud's own serial-order centroid (the reference behaviour); otherwise the given centre
-// (a shard of a larger cloud is centred on the centroid of the WHOLE cloud so that voxels line up across shards)
-static int remove_duplicate_impl(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf,
-                                 const double* centre, const int32_t* min_b = nullptr, const int32_t* div_b = nullptr)
+// (a shard of a larger cloud is centred on the centroid of the WHOLE cloud so that voxels line up across shards).
+// pts_out == NULL: in place (pts holds *n_inout records on entry and the filtered cloud on return); otherwise the
+// input is left alone and the filtered cloud goes to pts_out (capacity *n_inout records): no copy of the cloud at all.
+static int remove_duplicate_impl(pcp_ctx* ctx, void* pts, size_t* n_inout, size_t stride, float leaf, const double* centre,
+                                 const int32_t* min_b = nullptr, const int32_t* div_b = nullptr, void* pts_out = nullptr)
 {
     size_t n = *n_inout;
     if (n == 0) return PCP_OK;
     std::lock_guard<std::recursive_mutex> lock(ctx->mu);
     PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
     OutStage io; // in-place: host clouds are staged in, filtered on the device, staged back
-    PCP_TRY(io.open(ctx, pts_inout, n * stride, true));
-    char* d = static_cast<char*>(io.dptr);
-    DevBuf<char> tmp; // the filtered cloud, copied over the input at the end (the gather must not overwrite its source)
+    InStage in;
+    OutStage out;
+    DevBuf<char> tmp; // in place: the filtered cloud, copied over the input at the end (the gather must not overwrite its source)
+    const char* d = nullptr;
+    char* dst = nullptr;
+    if (pts_out) {
+        PCP_TRY(in.open(ctx, pts, n * stride));
+        PCP_TRY(out.open(ctx, pts_out, n * stride));
+        d = static_cast<const char*>(in.dptr);
+        dst = static_cast<char*>(out.dptr);
+    } else {
+        PCP_TRY(io.open(ctx, pts, n * stride, true));
+        PCP_TRY(tmp.alloc(ctx, n * stride));
+        d = static_cast<const char*>(io.dptr);
+        dst = tmp.p;
+    }
     DevBuf<double> s3;
     DevBuf<pcp_bbox> bb;
-    PCP_TRY(tmp.alloc(ctx, n * stride));
     PCP_TRY(s3.alloc(ctx, 3));
     PCP_TRY(bb.alloc(ctx, 1));
     // the two transformPointCloud passes (point_cloud_helper.cpp:52-53, 60-61) are folded into the voxel kernels:
@@ -360,21 +382,27 @@ static int remove_duplicate_impl(pcp_ctx* ctx, void* pts_inout, size_t* n_inout,
     double l = (double)leaf; // const float -> setLeafSize(double,double,double), point_cloud_helper.cpp:57
     double leaf3[3] = {l, l, l};
     size_t m = 0;
-    PCP_TRY(pcp_voxel_grid_device(ctx, d, n, stride, leaf3, 1, tmp.p, stride, &m, nullptr, nullptr, nullptr, nullptr,
+    PCP_TRY(pcp_voxel_grid_device(ctx, d, n, stride, leaf3, 1, dst, stride, &m, nullptr, nullptr, nullptr, nullptr,
                                   min_b, div_b, c3, &hb));
-    if (m) {
-        StageTimer t(ctx, "dedup.copy_back", 96.0 * m);
-        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(d, tmp.p, m * stride, cudaMemcpyDeviceToDevice, ctx->stream));
-    }
     *n_inout = m;
-    PCP_TRY(io.commit(m * stride));
+    if (pts_out) {
+        PCP_TRY(out.commit(m * stride));
+    } else {
+        if (m) {
+            StageTimer t(ctx, "dedup.copy_back", 96.0 * m);
+            PCP_CUDA_TRY(ctx, cudaMemcpyAsync(io.dptr, tmp.p, m * stride, cudaMemcpyDeviceToDevice, ctx->stream));
+        }
+        PCP_TRY(io.commit(m * stride));
+    }
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return PCP_OK;
 }
 
+static bool rd_stride_ok(size_t stride) { return stride == 32 || stride >= 40; }
+
 extern "C" int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf)
 {
-    if (!ctx || !n_inout || stride < 40 || (*n_inout && !pts_inout))
+    if (!ctx || !n_inout || !rd_stride_ok(stride) || (*n_inout && !pts_inout))
         return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_remove_duplicate: bad argument");
     return remove_duplicate_impl(ctx, pts_inout, n_inout, stride, leaf, nullptr);
 }
@@ -382,7 +410,17 @@ extern "C" int pcp_remove_duplicate(pcp_ctx* ctx, void* pts_inout, size_t* n_ino
 extern "C" int pcp_remove_duplicate_centred(pcp_ctx* ctx, void* pts_inout, size_t* n_inout, size_t stride, float leaf,
                                             const double centre[3], const int32_t min_b[3], const int32_t div_b[3])
 {
-    if (!ctx || !n_inout || !centre || !min_b || !div_b || stride < 40 || (*n_inout && !pts_inout))
+    if (!ctx || !n_inout || !centre || !min_b || !div_b || !rd_stride_ok(stride) || (*n_inout && !pts_inout))
         return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_remove_duplicate_centred: bad argument");
     return remove_duplicate_impl(ctx, pts_inout, n_inout, stride, leaf, centre, min_b, div_b);
+}
+
+extern "C" int pcp_remove_duplicate_to(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, float leaf,
+                                       const double* centre, const int32_t* min_b, const int32_t* div_b, void* pts_out,
+                                       size_t* m)
+{
+    if (!ctx || !m || !rd_stride_ok(stride) || (n && (!pts || !pts_out)) || ((min_b || div_b) && !(centre && min_b && div_b)))
+        return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_remove_duplicate_to: bad argument");
+    *m = n;
+    return remove_duplicate_impl(ctx, const_cast<void*>(pts), m, stride, leaf, centre, min_b, div_b, pts_out);
 }
