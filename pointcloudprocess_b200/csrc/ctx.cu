@@ -397,7 +397,7 @@ int pcp_copy_async(pcp_ctx* ctx, int lane, void* dst, const void* src, size_t by
     PCP_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->lane[lane], ctx->lane_in[lane], 0));
     // In pieces: a copy engine serves one copy at a time, and the few-byte read-backs of the compute stream
     // (counts, cell totals) must not queue behind a gigabyte transfer.
-    const size_t piece = (size_t)4 << 20;
+    const size_t piece = (size_t)32 << 20;
     for (size_t off = 0; off < bytes; off += piece)
         PCP_CUDA_TRY(ctx, cudaMemcpyAsync(static_cast<char*>(dst) + off, static_cast<const char*>(src) + off,
                                           std::min(piece, bytes - off), cudaMemcpyDefault, ctx->lane[lane]));

@@ -6,6 +6,8 @@
 #include "sort.cuh"
 #include <cfloat>
 #include <cmath>
+#include <algorithm>
+#include <cstdlib>
 
 namespace {
 
@@ -175,10 +177,15 @@ __global__ void __launch_bounds__(256) cinfo_kernel(const unsigned long long* __
 // upwards: the leaf of base cell c is its largest ancestor (level <= PCP_ITEM_LMAX) that still holds at most
 // cmax points; the first base cell of the leaf emits the one item that carries all of the leaf's points, so
 // that the 3x3x3 block staged for them grows with the local point spacing (knn_fast.cuh).
+// PCP_ITEM_CMAX / PCP_ITEM_CMIN (experiments, tools/sweep_items.sh): cmin > 0 also makes a node of at most 32 points an
+// item when one of its children holds fewer than cmin -- measured: no better than a larger cmax (38.9-39.1 ms).
 __device__ __forceinline__ int leaf_of_cell(const unsigned long long* __restrict__ ckey,
                                             const uint32_t* __restrict__ cstart, const pcp_hslot* __restrict__ ltab,
-                                            uint32_t lmask, uint32_t c, uint32_t cmax, uint32_t& ca, uint32_t& npts)
+                                            uint32_t lmask, uint32_t c, uint32_t cmax_cmin, uint32_t& ca, uint32_t& npts)
 {
+    // A node is an item when it holds at most cmax points, or at most 32 with a child of fewer than cmin; a base cell's
+    // leaf is its LARGEST such ancestor (every base cell below a node sees the same ancestors: consistent).
+    const uint32_t cmax = cmax_cmin & 0xffffu, cmin = cmax_cmin >> 16;
     int level = 0;
     ca = c;
     npts = cstart[c + 1] - cstart[c];
@@ -188,8 +195,22 @@ __device__ __forceinline__ int leaf_of_cell(const unsigned long long* __restrict
         uint32_t a = 0, cn = 0;
         if (!pcp_hash_find(ltab, lmask, PCP_LKEY(l, key >> (3 * l)), a, cn)) break;
         const uint32_t np = cstart[a + cn] - cstart[a];
-        if (np > cmax) break;
-        level = l, ca = a, npts = np;
+        if (np > 32u || (np > cmax && cmin == 0u)) break;
+        bool ok = np <= cmax;
+        if (!ok) { // does a child (level l - 1) hold fewer than cmin points?
+            uint32_t run = 0;
+            unsigned long long ck = ckey[a] >> (3 * (l - 1));
+            for (uint32_t b = a; b < a + cn && !ok; b++) {
+                const unsigned long long k2 = ckey[b] >> (3 * (l - 1));
+                if (k2 != ck) {
+                    ok = run < cmin;
+                    ck = k2, run = 0;
+                }
+                run += cstart[b + 1] - cstart[b];
+            }
+            if (!ok) ok = run < cmin;
+        }
+        if (ok) level = l, ca = a, npts = np;
     }
     return level;
 }
@@ -285,6 +306,12 @@ int pcp_index_build_items(pcp_ctx* ctx, pcp_index* ix, uint32_t cmax)
 {
     if (cmax < 1) cmax = 1;
     if (cmax > 32) cmax = 32;
+    {
+        static const char* e1 = getenv("PCP_ITEM_CMAX");
+        static const char* e2 = getenv("PCP_ITEM_CMIN");
+        if (e1 && atoi(e1) > 0) cmax = (uint32_t)std::min(atoi(e1), 32);
+        if (e2 && atoi(e2) > 0) cmax |= (uint32_t)std::min(atoi(e2), 32) << 16;
+    }
     if (ix->item_cell && ix->item_cmax == cmax) return PCP_OK;
     StageTimer t(ctx, "index.items");
     const uint32_t ncell = ix->ncell;

@@ -59,11 +59,12 @@ struct pcp_index {
 #define PCP_HLEVELS 5
 #define PCP_ITEM_LMAX 3           // coarsest level of a dense-kernel work item
 // leaf capacity for k neighbours: a planar patch of cmax/4..cmax points per leaf keeps the k-th neighbour inside
-// the 3x3x3 block of leaves for most queries while the block stays within the staging capacity (tuned on the
-// city cloud: 1.15 k; 23 for the reference's k = 20)
+// the 3x3x3 block of leaves for most queries while the block stays within the staging capacity.  Swept on the 25 M-point
+// city shard (tools/sweep_items.sh; whole step): 1.15 k = 23 -> 39.2 ms, 26 -> 39.1, 29 -> 38.8, 32 -> 39.1: larger leaves
+// leave fewer queries to the far kernel (1.36 M -> 1.18 M) and more blocks to the second dense pass; 1.45 k it is.
 static inline uint32_t pcp_item_cmax(int k)
 {
-    const int c = (int)(1.15 * k + 0.5);
+    const int c = (int)(1.45 * k + 0.5);
     return (uint32_t)(c < 8 ? 8 : (c > 32 ? 32 : c));
 }
 #define PCP_LKEY(level, prefix) (((unsigned long long)(level) << 58) | (prefix))

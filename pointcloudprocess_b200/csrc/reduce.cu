@@ -150,7 +150,10 @@ extern "C" int pcp_cloud_stats(pcp_ctx* ctx, const void* pts, size_t n, size_t s
     InStage in;
     PCP_TRY(in.open(ctx, pts, n * stride));
     pcp_bbox bb;
-    PCP_TRY(pcp_bbox_host(ctx, in.dptr, n, stride, &bb));
+    {
+        StageTimer t(ctx, "shard.stats", 24.0 * n);
+        PCP_TRY(pcp_bbox_host(ctx, in.dptr, n, stride, &bb));
+    }
     double h[10];
     for (int d = 0; d < 3; d++) h[d] = bb.mn[d], h[3 + d] = bb.mx[d], h[6 + d] = bb.sum[d];
     h[9] = (double)bb.count;

@@ -422,6 +422,7 @@ extern "C" int pcp_serial_sum_begin(pcp_ctx* ctx, const void* dev_pts, size_t n,
         PCP_CUDA_TRY(ctx, cudaMemcpyAsync(pred.p, predicted3, 24, cudaMemcpyDefault, ctx->stream));
     }
     pcp_serial_plan* P = nullptr;
+    StageTimer t(ctx, "shard.serial_sum_begin", 24.0 * n);
     const int st = pcp_serial_sum_prepare(ctx, dev_pts, n, stride, predicted3 ? pred.p : nullptr, &P);
     if (st != PCP_OK) {
         pcp_serial_sum_release(ctx, P);
@@ -441,6 +442,7 @@ extern "C" int pcp_serial_sum_end(void* handle, double* carry3_inout)
         std::lock_guard<std::recursive_mutex> lock(ctx->mu);
         cudaSetDevice(ctx->device);
         if (carry3_inout) {
+            StageTimer t(ctx, "shard.serial_sum_end");
             // device array: walked in place, no synchronisation (the value can travel on to the next GPU);
             // host array: staged through the context
             if (pcp_classify(ctx, carry3_inout) == PCP_PTR_DEVICE) {

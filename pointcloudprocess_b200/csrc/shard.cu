@@ -63,20 +63,35 @@ __global__ void __launch_bounds__(256) sel_scatter_kernel(const char* __restrict
     if (i == n - 1) *m_out = scan[i] + flag[i];
 }
 
+// bins in shared memory (block-private, flushed once) when they fit: one global atomic per point on a few hundred bins
+// serialises on the L2 atomic units (2.5 ms for 25 M points)
+#define PCP_HIST_SMEM_BINS 4096
 __global__ void __launch_bounds__(256) column_hist_kernel(const char* __restrict__ pts, size_t n, size_t stride, int axis,
                                                           double centre, double inv_leaf, int min_b, int col0, int ncols,
                                                           int cols_per_bin, unsigned long long* __restrict__ hist)
 {
-    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const double* p = reinterpret_cast<const double*>(pts + i * stride);
-    const double x = p[0], y = p[1], z = p[2];
-    if (!(isfinite(x) && isfinite(y) && isfinite(z))) return;
-    const int c = column_of(axis == 0 ? x : (axis == 1 ? y : z), centre, inv_leaf, min_b);
-    long long b = ((long long)c - col0) / cols_per_bin;
-    if (c < col0) b = 0;
-    if (b >= ncols) b = ncols - 1;
-    atomicAdd(&hist[b], 1ull);
+    __shared__ unsigned int sh[PCP_HIST_SMEM_BINS];
+    const bool local = ncols <= PCP_HIST_SMEM_BINS;
+    if (local) {
+        for (int b = threadIdx.x; b < ncols; b += blockDim.x) sh[b] = 0u;
+        __syncthreads();
+    }
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const double* p = reinterpret_cast<const double*>(pts + i * stride);
+        const double x = p[0], y = p[1], z = p[2];
+        if (!(isfinite(x) && isfinite(y) && isfinite(z))) continue;
+        const int c = column_of(axis == 0 ? x : (axis == 1 ? y : z), centre, inv_leaf, min_b);
+        long long b = ((long long)c - col0) / cols_per_bin;
+        if (c < col0) b = 0;
+        if (b >= ncols) b = ncols - 1;
+        if (local) atomicAdd(&sh[b], 1u);
+        else atomicAdd(&hist[b], 1ull);
+    }
+    if (local) {
+        __syncthreads();
+        for (int b = threadIdx.x; b < ncols; b += blockDim.x)
+            if (sh[b]) atomicAdd(&hist[b], (unsigned long long)sh[b]);
+    }
 }
 
 } // namespace
@@ -115,7 +130,10 @@ extern "C" int pcp_column_histogram(pcp_ctx* ctx, const void* pts, size_t n, siz
     OutStage h;
     PCP_TRY(in.open(ctx, pts, n * stride));
     PCP_TRY(h.open(ctx, hist_inout, (size_t)nbins * 8, true));
-    column_hist_kernel<<<pcp_blocks_for(n, 256), 256, 0, ctx->stream>>>(static_cast<const char*>(in.dptr), n, stride, axis,
+    StageTimer t(ctx, "shard.histogram", 8.0 * n);
+    unsigned hb = pcp_blocks_for(n, 256 * 16); // 16 points per thread: a block's private bins are flushed once
+    if (hb > (unsigned)ctx->sm_count * 8u) hb = (unsigned)ctx->sm_count * 8u;
+    column_hist_kernel<<<hb, 256, 0, ctx->stream>>>(static_cast<const char*>(in.dptr), n, stride, axis,
                                                                         centre, 1.0 / (double)leaf, min_b, col0, nbins,
                                                                         cols_per_bin, (unsigned long long*)h.dptr);
     PCP_LAUNCH_CHECK(ctx);
