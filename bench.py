@@ -448,7 +448,7 @@ def run_gpu(args):
         if world > 1:
             comm = sharded.DistComm(dist, torch, rank, world, torch.device("cuda", local))
         job = sharded.ShardedPipeline(ctx, rank, world, n_total, seed=cfg["seed"], leaf=cfg["leaf"], k=cfg["k"],
-                                      kind=cfg["kind"], comm=comm, torch=torch)
+                                      kind=cfg["kind"], comm=comm, torch=torch, halo=args.halo)
         if comm is not None:
             comm.peek = job._peek
         job.generate()  # this rank's range of the cloud in point order, packed records resident in HBM (untimed)
@@ -631,6 +631,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg")
     ap.add_argument("--gather", action="store_true", help="also time the final result gather to rank 0")
+    ap.add_argument("--halo", type=float, default=1.0, help="halo width in metres (N > 1)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

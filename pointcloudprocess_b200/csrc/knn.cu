@@ -21,14 +21,26 @@ __global__ void __launch_bounds__(256) props_fallback_kernel(void* props, double
         for (int e = 0; e < k; e++) knn_idx[j * k + e] = -1;
 }
 
+// qpts != NULL: also the squared distances (the expression of the search kernels, bit for bit: L2_Simple order, no FMA)
 __global__ void __launch_bounds__(256) knn_export_kernel(const pcp_rec* __restrict__ rec,
                                                          const uint32_t* __restrict__ pos, size_t total, int k,
-                                                         int32_t* __restrict__ idx, int32_t* __restrict__ found)
+                                                         int32_t* __restrict__ idx, int32_t* __restrict__ found,
+                                                         const char* __restrict__ qpts = nullptr, size_t qstride = 0,
+                                                         double* __restrict__ d2 = nullptr)
 {
     size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (t >= total) return;
     uint32_t p = pos[t];
     idx[t] = p == 0xffffffffu ? -1 : (int32_t)rec[p].idx;
+    if (d2) {
+        double v = __longlong_as_double(0x7ff0000000000000ll);
+        if (p != 0xffffffffu) {
+            const double* qp = reinterpret_cast<const double*>(qpts + (t / k) * qstride);
+            const pcp_rec r = pcp_load_rec(rec, p);
+            v = pcp_dist2(qp[0], qp[1], qp[2], r.x, r.y, r.z);
+        }
+        d2[t] = v;
+    }
     if (found && (t % k) == 0) {
         int c = 0;
         for (int e = 0; e < k; e++) c += pos[t + e] != 0xffffffffu;
@@ -364,10 +376,11 @@ extern "C" int pcp_knn(const pcp_index* ix, const void* q, size_t nq, size_t qst
     PCP_TRY(o_idx.open(ctx, idx, nq * (size_t)k * 4));
     PCP_TRY(o_d2.open(ctx, d2, nq * (size_t)k * 8));
     PCP_TRY(o_found.open(ctx, found, nq * 4));
-    DevBuf<uint32_t> pos, counter;
+    DevBuf<uint32_t> pos, counter, fail;
     PCP_TRY(pos.alloc(ctx, nq * (size_t)k));
-    PCP_TRY(counter.alloc(ctx, 1));
-    PCP_CUDA_TRY(ctx, cudaMemsetAsync(counter.p, 0, 4, ctx->stream));
+    PCP_TRY(counter.alloc(ctx, 8));
+    PCP_CUDA_TRY(ctx, cudaMemsetAsync(counter.p, 0, 32, ctx->stream));
+    const int kk = (int)(ix->n < (size_t)k ? ix->n : (size_t)k);
     pcp_wknn_params W;
     memset(&W, 0, sizeof(W));
     W.rec = ix->rec;
@@ -377,33 +390,71 @@ extern "C" int pcp_knn(const pcp_index* ix, const void* q, size_t nq, size_t qst
     W.g = ix->grid;
     W.htab = ix->htab, W.hmask = ix->hmask, W.ltab = ix->ltab, W.lmask = ix->lmask;
     W.k = k;
-    W.kk = (int)(ix->n < (size_t)k ? ix->n : (size_t)k);
+    W.kk = kk;
     W.qcount = (uint32_t)nq;
     W.qpts = static_cast<const char*>(in.dptr);
     W.qstride = qstride;
     W.out_pos = pos.p;
     W.out_d2 = (double*)o_d2.dptr;
-    W.work_counter = counter.p;
+    W.work_counter = counter.p + 3;
     DevBuf<unsigned long long> dbg;
     if (getenv("PCP_KNN_DEBUG")) {
         PCP_TRY(dbg.alloc(ctx, 17));
         PCP_CUDA_TRY(ctx, cudaMemsetAsync(dbg.p, 0, 17 * 8, ctx->stream));
         W.dbg = dbg.p;
     }
+    // Many queries at once (the boundary queries of a neighbouring shard, closest-point batches): the far kernel's
+    // pruned search, as for the cloud's own left-over queries -- the streaming kernel scans whole 3x3x3 blocks of level
+    // cells and is kept for what the far kernel cannot settle (list overflows on mass ties, non-finite queries).
+    static const bool ext_stream_only = getenv("PCP_KNN_STREAM") != nullptr;
+    const bool use_far = !ext_stream_only && nq >= 64 && kk > 0 && ix->cinfo && nq * (unsigned long long)k < (1ull << 32);
+    bool export_d2 = false;
     {
         StageTimer t(ctx, "knn.query_kernel");
-        PCP_TRY(run_wknn(ctx, W, (uint32_t)nq));
+        uint32_t nstream = (uint32_t)nq;
+        if (use_far) {
+            PCP_TRY(fail.alloc(ctx, nq));
+            const uint32_t nq32 = (uint32_t)nq;
+            PCP_CUDA_TRY(ctx, cudaMemcpyAsync(counter.p, &nq32, 4, cudaMemcpyHostToDevice, ctx->stream));
+            pcp_fknn_params P;
+            P.rec = ix->rec, P.fpt = ix->fpt, P.htab = ix->htab, P.hmask = ix->hmask, P.ltab = ix->ltab, P.lmask = ix->lmask;
+            P.cinfo = ix->cinfo, P.ckey = ix->ckey, P.cstart = ix->cstart, P.ncell = ix->ncell;
+            P.item_cell = P.item_first = P.item_meta = nullptr, P.nitem = 0;
+            P.g = ix->grid, P.k = k, P.kk = kk, P.eps0 = ix->eps0, P.epsd = ix->epsd, P.query_limit = LLONG_MAX;
+            P.kth_d2 = nullptr, P.props = nullptr, P.eig3 = nullptr, P.lps3 = nullptr, P.knn_idx = nullptr;
+            P.fail_list = nullptr, P.fail_u = nullptr, P.fail_count = nullptr, P.work_counter = nullptr, P.dbg = nullptr;
+            P.nbr_out = pos.p; // rows of sorted positions, one per query
+            pcp_far_args A;
+            A.list = nullptr, A.listU = nullptr;
+            A.count = counter.p;
+            A.work_counter = counter.p + 1;
+            A.fail_list = fail.p;
+            A.fail_count = counter.p + 2;
+            A.ext_q = static_cast<const char*>(in.dptr);
+            A.ext_stride = qstride;
+            PCP_TRY(launch_far(ctx, P, A));
+            uint32_t hc[3];
+            PCP_TRY(pcp_readback(ctx, hc, counter.p, 12));
+            nstream = hc[2];
+            W.qsel = fail.p;
+            W.qcount = nstream;
+            W.out_d2 = nullptr; // the export computes every distance
+            export_d2 = o_d2.dptr != nullptr;
+        }
+        if (nstream) PCP_TRY(run_wknn(ctx, W, nstream));
         knn_export_kernel<<<pcp_blocks_for(nq * (size_t)k, 256), 256, 0, ctx->stream>>>(
-            ix->rec, pos.p, nq * (size_t)k, k, (int32_t*)o_idx.dptr, (int32_t*)o_found.dptr);
+            ix->rec, pos.p, nq * (size_t)k, k, (int32_t*)o_idx.dptr, (int32_t*)o_found.dptr,
+            export_d2 ? static_cast<const char*>(in.dptr) : nullptr, qstride, export_d2 ? (double*)o_d2.dptr : nullptr);
         PCP_LAUNCH_CHECK(ctx);
     }
     if (W.dbg) {
         unsigned long long h[17];
         PCP_TRY(pcp_readback(ctx, h, dbg.p, 17 * 8));
-        fprintf(stderr, "[pcp knn] %zu external queries, settled at level:", nq);
+        fprintf(stderr, "[pcp knn] %zu external queries (%u by the streaming kernel), settled at level:", nq, W.qcount);
         for (int l = 0; l < 16; l++)
             if (h[l]) fprintf(stderr, " %d:%llu", l, h[l]);
-        fprintf(stderr, "; %.0f points scanned per query (top level %d)\n", (double)h[16] / (double)nq, ix->grid.top_level);
+        fprintf(stderr, "; %.0f points scanned per streamed query (top level %d)\n", W.qcount ? (double)h[16] / (double)W.qcount : 0.0,
+                ix->grid.top_level);
     }
     PCP_TRY(o_idx.commit());
     PCP_TRY(o_d2.commit());

@@ -164,6 +164,10 @@ struct pcp_far_args {
     uint32_t* work_counter;
     uint32_t* fail_list;     // queries for the streaming FP64 kernel (list overflow)
     uint32_t* fail_count;
+    // external queries (pcp_knn): query qi is the point at ext_q + qi * ext_stride (x, y, z doubles), no list, no bound;
+    // its neighbour row is row qi of nbr_out
+    const char* ext_q = nullptr;
+    size_t ext_stride = 0;
 };
 
 template <int CAP, bool DEFER = false>
@@ -184,9 +188,19 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
         if (lane == 0) qi = atomicAdd(A.work_counter, 1u);
         qi = __shfl_sync(0xffffffffu, qi, 0);
         if (qi >= nq) break;
-        const uint32_t qpos = __ldg(A.list + qi);
-        float U = __ldg(A.listU + qi);
-        const pcp_rec q = pcp_load_rec(P.rec, qpos);
+        const uint32_t qpos = A.ext_q ? qi : __ldg(A.list + qi);
+        float U = A.ext_q ? INF : __ldg(A.listU + qi);
+        pcp_rec q;
+        if (A.ext_q) {
+            const double* qp = reinterpret_cast<const double*>(A.ext_q + (size_t)qi * A.ext_stride);
+            q.x = qp[0], q.y = qp[1], q.z = qp[2], q.idx = 0;
+            if (!(isfinite(q.x) && isfinite(q.y) && isfinite(q.z))) { // the streaming kernel writes the empty row
+                if (lane == 0) A.fail_list[atomicAdd(A.fail_count, 1u)] = qpos;
+                continue;
+            }
+        } else {
+            q = pcp_load_rec(P.rec, qpos);
+        }
         const int bx = min(max(pcp_cell_coord(q.x, P.g.org[0], P.g.inv_h, 0), 0), P.g.dims[0] - 1);
         const int by = min(max(pcp_cell_coord(q.y, P.g.org[1], P.g.inv_h, 0), 0), P.g.dims[1] - 1);
         const int bz = min(max(pcp_cell_coord(q.z, P.g.org[2], P.g.inv_h, 0), 0), P.g.dims[2] - 1);

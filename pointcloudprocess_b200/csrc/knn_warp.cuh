@@ -26,6 +26,7 @@ struct pcp_wknn_params {
     uint32_t qcount;
     const char* qpts;
     size_t qstride;
+    const uint32_t* qsel; // optional, with qpts: query qi is external point qsel[qi], and that is its output row
     // outputs, row r = query ordinal in the list: kk sorted positions (and squared distances)
     uint32_t* out_pos; // [nq][k]
     double* out_d2;    // [nq][k] or NULL
@@ -94,13 +95,14 @@ template <int KPL> static __global__ void __launch_bounds__(128) knn_warp_kernel
         if (qi >= nq) return;
         double qx, qy, qz;
         int level = 0;
+        const uint32_t row = (!P.qlist && P.qsel) ? __ldg(P.qsel + qi) : qi;
         if (P.qlist) {
             uint32_t code = __ldg(P.qlist + qi);
             level = (code & 0x80000000u) ? 1 : 0;
             const pcp_rec q = pcp_load_rec(P.rec, code & 0x7fffffffu);
             qx = q.x, qy = q.y, qz = q.z;
         } else {
-            const double* qp = reinterpret_cast<const double*>(P.qpts + (size_t)qi * P.qstride);
+            const double* qp = reinterpret_cast<const double*>(P.qpts + (size_t)row * P.qstride);
             qx = qp[0], qy = qp[1], qz = qp[2];
         }
         pcp_wlist<KPL> L;
@@ -191,8 +193,8 @@ template <int KPL> static __global__ void __launch_bounds__(128) knn_warp_kernel
             const int e = s * 32 + lane;
             if (e < P.k) {
                 const bool have = e < found && L.d[s] < DBL_MAX;
-                P.out_pos[(size_t)qi * P.k + e] = have ? L.pos[s] : 0xffffffffu;
-                if (P.out_d2) P.out_d2[(size_t)qi * P.k + e] = have ? L.d[s] : __longlong_as_double(0x7ff0000000000000ll);
+                P.out_pos[(size_t)row * P.k + e] = have ? L.pos[s] : 0xffffffffu;
+                if (P.out_d2) P.out_d2[(size_t)row * P.k + e] = have ? L.d[s] : __longlong_as_double(0x7ff0000000000000ll);
             }
         }
     }

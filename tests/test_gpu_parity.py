@@ -473,3 +473,58 @@ def test_fused_and_single_pass_variants_equal_the_default_path(ctx):
         for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS", "PCP_FK_NOFLAT", "PCP_RADIUS_WARP"):
             os.environ.pop(env, None)
         ix.free()
+
+
+def test_knn_batched_external_queries_edge_cases(ctx, orc):
+    """pcp_knn with >= 64 queries runs the far kernel's pruned search with the streaming kernel behind it: queries far
+    outside the cloud, non-finite queries, fewer points than k, mass ties (duplicates), and both paths agree."""
+    import os
+    import subprocess
+    import sys
+    import pointcloudprocess_b200 as pcp
+    rng = np.random.default_rng(5)
+    # (a) far outside + NaN queries
+    cloud = cloud_uniform(20000, 3, True)
+    q = np.concatenate([rng.uniform(-200, 200, size=(300, 3)) + UTM, rng.uniform(0, 10, size=(300, 3)) + UTM])
+    q[7] = np.nan
+    q[500, 1] = np.inf
+    ix = pcp.Index(ctx, cloud)
+    idx, d2, found = ix.knn(q, 20)
+    ok = np.isfinite(q).all(axis=1)
+    ridx, rd2, rfound = orc.knn_brute(cloud, q[ok], 20)
+    assert np.array_equal(idx[ok], ridx) and np.array_equal(d2[ok], rd2) and np.array_equal(found[ok], rfound)
+    assert (idx[~ok] == -1).all() and (found[~ok] == 0).all() and np.isinf(d2[~ok]).all()
+    ix.free()
+    # (b) fewer points than k
+    small = cloud_uniform(11, 4, True)
+    ix = pcp.Index(ctx, small)
+    q = rng.uniform(-5, 15, size=(128, 3)) + UTM
+    idx, d2, found = ix.knn(q, 20)
+    ridx, rd2, rfound = orc.knn_brute(small, q, 20)
+    assert np.array_equal(idx, ridx) and np.array_equal(d2, rd2) and np.array_equal(found, rfound)
+    ix.free()
+    # (c) mass ties: every point 40 times
+    base = rng.uniform(0, 3, size=(200, 3)) + UTM
+    dup = pcp.make_cloud(np.repeat(base, 40, axis=0))
+    ix = pcp.Index(ctx, dup)
+    q = np.concatenate([base[:100], rng.uniform(0, 3, size=(100, 3)) + UTM])
+    idx, d2, found = ix.knn(q, 30)
+    ridx, rd2, rfound = orc.knn_brute(dup, q, 30)
+    assert np.array_equal(idx, ridx) and np.array_equal(d2, rd2)
+    ix.free()
+    # (d) the streaming kernel alone (PCP_KNN_STREAM=1, read once per process) gives the same bytes
+    code = ("import numpy as np, pointcloudprocess_b200 as pcp, hashlib\n"
+            "ctx = pcp.Context(0)\n"
+            "c = ctx.synth_cloud('city', 300000, seed=2)\n"
+            "rng = np.random.default_rng(1)\n"
+            "q = np.stack([c['x'], c['y'], c['z']], 1)[rng.integers(0, len(c), 5000)] + rng.normal(0, 0.5, (5000, 3))\n"
+            "ix = pcp.Index(ctx, c)\n"
+            "i, d, f = ix.knn(q, 20)\n"
+            "print(hashlib.sha1(i.tobytes() + d.tobytes() + f.tobytes()).hexdigest())\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for env in ({}, {"PCP_KNN_STREAM": "1"}):
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=root, env=dict(os.environ, **env), timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(r.stdout.strip().splitlines()[-1])
+    assert outs[0] == outs[1]
