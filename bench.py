@@ -631,7 +631,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg")
     ap.add_argument("--gather", action="store_true", help="also time the final result gather to rank 0")
-    ap.add_argument("--halo", type=float, default=1.0, help="halo width in metres (N > 1)")
+    ap.add_argument("--halo", type=float, default=2.0, help="halo width in metres (N > 1)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -306,7 +306,7 @@ class ShardedPipeline:
 
     CHUNK = 8_000_000  # points generated at a time (setup)
 
-    def __init__(self, ctx, rank, world, n_total, seed=5, leaf=0.02, k=20, kind="city", comm=None, torch=None, halo=1.0):
+    def __init__(self, ctx, rank, world, n_total, seed=5, leaf=0.02, k=20, kind="city", comm=None, torch=None, halo=2.0):
         if torch is None:
             raise ValueError("ShardedPipeline needs torch for its device buffers")
         self.ctx, self.rank, self.world = ctx, rank, world
