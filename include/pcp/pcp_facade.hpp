@@ -59,13 +59,23 @@ struct PlanSegment {
     std::vector<int> PointID;
 };
 
+// point_cloud.h:295-312 without Eigen: the acquisition header and sensor pose travel with the cloud as plain members
+// (Header: sensor_point_cloud2.h's seq / stamp / frame_id; sensor_origin_ x y z w; sensor_orientation_ w x y z)
+struct Header {
+    uint32_t seq = 0;
+    uint64_t stamp = 0;
+    std::string frame_id;
+};
 template <typename PointT> class PointCloud {
   public:
     typedef std::shared_ptr<PointCloud<PointT>> Ptr;
     typedef std::shared_ptr<const PointCloud<PointT>> ConstPtr;
+    Header header;
     std::vector<PointT> points;
     uint32_t width = 0, height = 1;
     bool is_dense = true;
+    double sensor_origin_[4] = {0, 0, 0, 0};      // Eigen::Vector4d::Zero (point_cloud.h:79)
+    double sensor_orientation_[4] = {1, 0, 0, 0}; // Eigen::Quaterniond::Identity, w first
     size_t size() const { return points.size(); }
     void push_back(const PointT& p)
     {
@@ -82,6 +92,9 @@ template <typename PointT> class PointCloud {
     PointT& operator[](size_t i) { return points[i]; }
     const PointT& operator[](size_t i) const { return points[i]; }
 };
+// boost::shared_array<LAS_POINT_PROPERTY> of the reference (calculate_feature.h:13-16): indexed as PointProperty[j]
+// (calculate_feature.cpp:229,341, extraction_tree.cpp:194); .get() gives the raw array
+typedef std::shared_ptr<LAS_POINT_PROPERTY[]> PointPropertyArray;
 typedef PointXYZRGBA CloudItem;              // cmm_types.h:11-14
 typedef PointCloud<CloudItem> Cloud;
 typedef Cloud::Ptr CloudPtr;
@@ -201,6 +214,21 @@ template <typename PointT> class KdTreeFLANN {
     pcp_index* index_ = nullptr;
 };
 
+// kd_tree_lod/kd_tree.h:8-22 (cloud_blend_double::KdTree, the float wrapper over trimesh2's KD-tree; dead code in the
+// reference: not in the project file, every use commented out).  Same two calls; the answers here are the exact
+// double-precision ones of KdTreeFLANN, not the float search + index recovery of kd_tree_lod/kd_tree.cpp:29-117.
+class KdTree {
+  public:
+    void setInputCloud(PointCloud<PointXYZRGBA>::ConstPtr cloud) { tree_.setInputCloud(cloud); }
+    int nearestKSearch(const PointXYZRGBA& point, int k, std::vector<int>& k_index, std::vector<double>& k_dis)
+    {
+        return tree_.nearestKSearch(point, k, k_index, k_dis);
+    }
+
+  private:
+    KdTreeFLANN<PointXYZRGBA> tree_;
+};
+
 // voxel_grid.h:454-1056 (no field filter).
 template <typename PointT> class VoxelGrid {
   public:
@@ -267,6 +295,9 @@ template <typename PointT> class VoxelGrid {
                       "VoxelGrid::filter");
         output.points.resize(m);
         output.width = (uint32_t)m, output.height = 1, output.is_dense = true; // voxel_grid.h:824-825,1055
+        output.header = input_->header;                                        // Filter::filter, voxel_grid.h:440-442
+        for (int a = 0; a < 4; a++)
+            output.sensor_origin_[a] = input_->sensor_origin_[a], output.sensor_orientation_[a] = input_->sensor_orientation_[a];
         for (int a = 0; a < 3; a++) max_b_[a] = min_b_[a] + div_b_[a] - 1;
         divb_mul_[0] = 1, divb_mul_[1] = div_b_[0], divb_mul_[2] = (long long)div_b_[0] * div_b_[1];
         if (save_leaf_layout_) { // outputs are in ascending cell index (voxel_grid.h:948, 1031)
@@ -341,10 +372,9 @@ class CalculateFeature {
     }
     // calculate_feature.h:15 (declared, never defined in the reference): per-point plane fit on the k nearest
     // neighbours (radius <= 0) or on the neighbours within `radius`
-    static std::shared_ptr<LAS_POINT_PROPERTY> calculate_plan_parameter(CloudPtr cloud, double radius, int k = 20)
+    static PointPropertyArray calculate_plan_parameter(CloudPtr cloud, double radius, int k = 20)
     {
-        std::shared_ptr<LAS_POINT_PROPERTY> out(new LAS_POINT_PROPERTY[cloud->points.size() ? cloud->points.size() : 1],
-                                                std::default_delete<LAS_POINT_PROPERTY[]>());
+        PointPropertyArray out(new LAS_POINT_PROPERTY[cloud->points.size() ? cloud->points.size() : 1]);
         pcp_index* ix = nullptr;
         pcp_ctx* c = detail::context();
         detail::check(c, pcp_index_build(c, cloud->points.data(), cloud->points.size(), sizeof(CloudItem), 0.0, &ix),
@@ -358,12 +388,11 @@ class CalculateFeature {
     // calculate_feature.cpp:208-368: the robust fit on the 20 nearest neighbours (Radius is unused there too, :233).
     // The reference's rand() hypotheses are replaced by a counter-based generator keyed by `seed`
     // (pcp_features_rpca), so the result is reproducible.
-    static std::shared_ptr<LAS_POINT_PROPERTY> calculate_plan_parameter_rpca(CloudPtr cloud, double /*Radius*/,
+    static PointPropertyArray calculate_plan_parameter_rpca(CloudPtr cloud, double /*Radius*/,
                                                                              float Pr = 0.99f, float epi = 0.5f,
                                                                              uint64_t seed = 1)
     {
-        std::shared_ptr<LAS_POINT_PROPERTY> out(new LAS_POINT_PROPERTY[cloud->points.size() ? cloud->points.size() : 1],
-                                                std::default_delete<LAS_POINT_PROPERTY[]>());
+        PointPropertyArray out(new LAS_POINT_PROPERTY[cloud->points.size() ? cloud->points.size() : 1]);
         pcp_index* ix = nullptr;
         pcp_ctx* c = detail::context();
         detail::check(c, pcp_index_build(c, cloud->points.data(), cloud->points.size(), sizeof(CloudItem), 0.0, &ix),
@@ -373,7 +402,8 @@ class CalculateFeature {
         detail::check(c, st, "calculate_plan_parameter_rpca");
         return out;
     }
-    static int compute_iteration_number(float Pr, float epi) { return pcp_rpca_iterations(Pr, epi); }
+    // calculate_feature.cpp:28-33: h_free is not read there either (the exponent is the literal 3)
+    static int compute_iteration_number(float Pr, float epi, int /*h_free*/ = 3) { return pcp_rpca_iterations(Pr, epi); }
 };
 
 // extraction_tree.h (the reference's spelling).  region_growning (extraction_tree.cpp:170-272): plane segments grown
@@ -382,7 +412,7 @@ class CalculateFeature {
 // `radius` is not read by the reference either.
 class TreeExtration {
   public:
-    std::vector<PlanSegment> region_growning(std::shared_ptr<LAS_POINT_PROPERTY> PointProperty, CloudPtr& cloud,
+    std::vector<PlanSegment> region_growning(PointPropertyArray PointProperty, CloudPtr& cloud,
                                              double distanceT, double /*radius*/, double cosfaT)
     {
         const size_t n = cloud->points.size();
@@ -414,7 +444,7 @@ class TreeExtration {
 // static.cpp:8-21: robust per-point plane fit, then region growing, with the reference's constants
 inline void point_segment(CloudPtr src_cloud, std::vector<PlanSegment>& Segment, uint64_t seed = 1)
 {
-    std::shared_ptr<LAS_POINT_PROPERTY> PointProperty = CalculateFeature::calculate_plan_parameter_rpca(src_cloud, 0.15, 0.99f, 0.5f, seed);
+    PointPropertyArray PointProperty = CalculateFeature::calculate_plan_parameter_rpca(src_cloud, 0.15, 0.99f, 0.5f, seed);
     TreeExtration Tree;
     Segment = Tree.region_growning(PointProperty, src_cloud, 0.5, 0.2, 0.940);
 }

@@ -202,11 +202,20 @@ int pcp_create(pcp_ctx** out, int cuda_device)
         return pcp_fail(nullptr, PCP_ERR_INVALID, "pcp_create: device %d out of range [0,%d)", cuda_device, n);
     pcp_ctx* c = new pcp_ctx();
     c->device = cuda_device;
-    PCP_CUDA_TRY(c, cudaSetDevice(cuda_device));
+    // on any failure below: the message goes to the thread's error slot, what was created is released
+    auto fail = [&](cudaError_t e, const char* what) {
+        pcp_fail(nullptr, PCP_ERR_CUDA, "pcp_create: %s failed: %s", what, cudaGetErrorString(e));
+        if (c->pool) cudaMemPoolDestroy(c->pool);
+        if (c->own_stream) cudaStreamDestroy(c->own_stream);
+        delete c;
+        return PCP_ERR_CUDA;
+    };
+    cudaError_t e2;
+    if ((e2 = cudaSetDevice(cuda_device)) != cudaSuccess) return fail(e2, "cudaSetDevice");
     cudaDeviceProp prop;
-    PCP_CUDA_TRY(c, cudaGetDeviceProperties(&prop, cuda_device));
+    if ((e2 = cudaGetDeviceProperties(&prop, cuda_device)) != cudaSuccess) return fail(e2, "cudaGetDeviceProperties");
     c->sm_count = prop.multiProcessorCount;
-    PCP_CUDA_TRY(c, cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+    if ((e2 = cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking)) != cudaSuccess) return fail(e2, "cudaStreamCreate");
     c->stream = c->own_stream;
     cudaMemPoolProps pp;
     memset(&pp, 0, sizeof(pp));
@@ -214,9 +223,9 @@ int pcp_create(pcp_ctx** out, int cuda_device)
     pp.handleTypes = cudaMemHandleTypeNone;
     pp.location.type = cudaMemLocationTypeDevice;
     pp.location.id = cuda_device;
-    PCP_CUDA_TRY(c, cudaMemPoolCreate(&c->pool, &pp));
+    if ((e2 = cudaMemPoolCreate(&c->pool, &pp)) != cudaSuccess) return fail(e2, "cudaMemPoolCreate");
     uint64_t thr = UINT64_MAX; // keep freed blocks cached: steady-state calls do no driver allocation
-    PCP_CUDA_TRY(c, cudaMemPoolSetAttribute(c->pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    if ((e2 = cudaMemPoolSetAttribute(c->pool, cudaMemPoolAttrReleaseThreshold, &thr)) != cudaSuccess) return fail(e2, "cudaMemPoolSetAttribute");
     *out = c;
     return PCP_OK;
 }

@@ -8,6 +8,7 @@
 // records are assembled by a kernel.
 #include "common.cuh"
 #include <cerrno>
+#include <cstdarg>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -153,10 +154,13 @@ unsigned lzf_decode(const unsigned char* in, size_t n, unsigned char* out, size_
 // ---- PCD v0.7 ------------------------------------------------------------------------------------------------
 namespace {
 
-int io_fail(int code, const char* fmt, const char* a = "")
+int io_fail(int code, const char* fmt, ...)
 {
     char buf[512];
-    snprintf(buf, sizeof buf, fmt, a);
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
     pcp_set_global_error(buf);
     return code;
 }
@@ -233,8 +237,37 @@ int parse_header(FILE* f, pcp_pcd_header* h)
         return io_fail(PCP_ERR_INVALID, "PCD header: HEIGHT given but no WIDTH");
     }
     if ((uint64_t)h->width * h->height != h->points) return io_fail(PCP_ERR_INVALID, "PCD header: HEIGHT x WIDTH != number of points");
+    // A header is untrusted input: every size below feeds an allocation or a device-side stride.  Field sizes the
+    // format knows (1, 2, 4, 8), positive bounded counts, the three type letters, floats of 4 or 8 bytes; and a binary
+    // payload must fit into the file (a compressed one is checked against its own size words by the readers).
+    uint64_t fsize = 0;
+    for (int i = 0; i < h->nfields; i++) {
+        const int sz = h->size[i], ct = h->count[i];
+        if (sz != 1 && sz != 2 && sz != 4 && sz != 8) return io_fail(PCP_ERR_INVALID, "PCD header: SIZE %d of field '%s' is not 1, 2, 4 or 8", sz, h->names[i]);
+        if (ct < 1 || ct > (1 << 20)) return io_fail(PCP_ERR_INVALID, "PCD header: COUNT %d of field '%s' out of range", ct, h->names[i]);
+        if (h->type[i] != 'I' && h->type[i] != 'U' && h->type[i] != 'F') return io_fail(PCP_ERR_INVALID, "PCD header: TYPE '%c' of field '%s' is not I, U or F", h->type[i], h->names[i]);
+        if (h->type[i] == 'F' && sz != 4 && sz != 8) return io_fail(PCP_ERR_INVALID, "PCD header: float field '%s' of %d bytes", h->names[i], sz);
+        fsize += (uint64_t)sz * (uint64_t)ct;
+    }
+    if (h->points > (1ull << 40) || fsize > (1ull << 24)) return io_fail(PCP_ERR_RANGE, "PCD header: %llu points of %llu bytes are beyond this reader", (unsigned long long)h->points, (unsigned long long)fsize);
+    if (h->data_type == PCP_PCD_BINARY) {
+        const long here = ftell(f);
+        fseek(f, 0, SEEK_END);
+        const uint64_t file_size = (uint64_t)ftell(f);
+        fseek(f, here, SEEK_SET);
+        if (h->data_offset + h->points * fsize > file_size)
+            return io_fail(PCP_ERR_INVALID, "PCD header: %llu points of %llu bytes do not fit into the file (%llu bytes after the header)",
+                           (unsigned long long)h->points, (unsigned long long)fsize, (unsigned long long)(file_size - h->data_offset));
+    }
     return PCP_OK;
 }
+
+// extern "C" entry points must not let an exception out (a failed allocation inside a std::vector, a worker thread)
+#define PCP_IO_GUARD_BEGIN try {
+#define PCP_IO_GUARD_END                                                                                              \
+    }                                                                                                                 \
+    catch (const std::bad_alloc&) { return io_fail(PCP_ERR_NOMEM, "PCD: out of host memory"); }                     \
+    catch (const std::exception& e) { return io_fail(PCP_ERR_INVALID, "PCD: %s", e.what()); }
 
 // the members a record can receive: name, PCD type, element size, offset in a PointXYZRGBA-shaped record
 struct Member {
@@ -345,7 +378,14 @@ int pcp_pcd_read_header(const char* path, pcp_pcd_header* header)
     return st;
 }
 
+static int pcd_load_impl(const char* path, int point_kind, void* pts, size_t cap, size_t stride, size_t* n_out, int* is_dense);
 int pcp_pcd_load(const char* path, int point_kind, void* pts, size_t cap, size_t stride, size_t* n_out, int* is_dense)
+{
+    PCP_IO_GUARD_BEGIN
+    return pcd_load_impl(path, point_kind, pts, cap, stride, n_out, is_dense);
+    PCP_IO_GUARD_END
+}
+static int pcd_load_impl(const char* path, int point_kind, void* pts, size_t cap, size_t stride, size_t* n_out, int* is_dense)
 {
     if (!path || !n_out || (cap && !pts) || stride < (size_t)(point_kind == PCP_PCD_POINT_XYZ ? 24 : 40))
         return io_fail(PCP_ERR_INVALID, "pcp_pcd_load: bad argument");
@@ -454,7 +494,17 @@ int pcp_pcd_load(const char* path, int point_kind, void* pts, size_t cap, size_t
     return PCP_OK;
 }
 
+static int pcd_save_impl(const char* path, int point_kind, const void* pts, size_t n, size_t stride, uint32_t width, uint32_t height,
+                 int mode, int precision)
+;
 int pcp_pcd_save(const char* path, int point_kind, const void* pts, size_t n, size_t stride, uint32_t width, uint32_t height,
+                 int mode, int precision)
+{
+    PCP_IO_GUARD_BEGIN
+    return pcd_save_impl(path, point_kind, pts, n, stride, width, height, mode, precision);
+    PCP_IO_GUARD_END
+}
+static int pcd_save_impl(const char* path, int point_kind, const void* pts, size_t n, size_t stride, uint32_t width, uint32_t height,
                  int mode, int precision)
 {
     if (!path || (n && !pts) || stride < (size_t)(point_kind == PCP_PCD_POINT_XYZ ? 24 : 40) || mode < 0 || mode > 2)
@@ -721,7 +771,15 @@ extern "C" int pcp_pcd_load_many(pcp_ctx* ctx, const char* const* paths, size_t 
                 const size_t i = next.fetch_add(1);
                 if (i >= nfiles) return;
                 loaded[i].reset(new PcdLoaded);
-                if (!stop.load()) load_one(paths[i], point_kind, stride, *loaded[i]);
+                if (!stop.load()) {
+                    try {
+                        load_one(paths[i], point_kind, stride, *loaded[i]);
+                    } catch (const std::bad_alloc&) {
+                        loaded[i]->status = PCP_ERR_NOMEM, loaded[i]->error = std::string("out of host memory (") + paths[i] + ")";
+                    } catch (const std::exception& e) {
+                        loaded[i]->status = PCP_ERR_INVALID, loaded[i]->error = std::string(e.what()) + " (" + paths[i] + ")";
+                    }
+                }
                 ready[i].set_value();
             }
         });

@@ -78,8 +78,10 @@ __device__ __forceinline__ float rpca_dist(const double* nb, int n, const RpcaPl
 
 // calculate_plan_parameter_h_points (:119-206) over the neighbours ord[0..h), optionally through the float members
 // of LAS_POINT_PROPERTY_sim (:262-266). Inlined at its three call sites (the Jacobi solver inside stays one shared
-// function): as a __noinline__ function ptxas 12.9 -O3 produced a kernel whose MAD inlier test kept a point it
+// function): as a __noinline__ function the kernel built by ptxas 12.9 -O3 kept, in its MAD inlier test, a point it
 // computed as an outlier (6 % of the records differed from the oracle; the same PTX assembled at -O1 was right).
+// Observed, not explained: compute-sanitizer (initcheck) is closed on this pool, so neither a compiler fault nor an
+// uninitialised read on our side is established; the inlined form is bit-equal to the oracle in every test.
 __device__ __forceinline__ void rpca_fit(const double* nb, const unsigned char* ord, int h, int as_float, pcp_plane& out)
 {
     double XAve = 0.0, YAve = 0.0, ZAve = 0.0;

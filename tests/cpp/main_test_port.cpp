@@ -58,8 +58,8 @@ static void test_kd_tree()
     printf("batch %d of %zu; by index %d: %d %d %d\n", self, cloud->size(), n5, index[0], index[1], index[2]);
     PointCloudHelper::remove_duplicate(cloud, 1.0f);
     printf("dedup %zu\n", cloud->size());
-    std::shared_ptr<LAS_POINT_PROPERTY> props = CalculateFeature::calculate_plan_parameter_rpca(cloud, 0.15);
-    printf("props %d %.9g\n", props.get()[0].PointID, props.get()[0].curvature);
+    PointPropertyArray props = CalculateFeature::calculate_plan_parameter_rpca(cloud, 0.15);
+    printf("props %d %.9g\n", props[0].PointID, props[0].curvature); // indexed like boost::shared_array (calculate_feature.cpp:229)
 }
 
 // calculate_plan_parameter_rpca (calculate_feature.cpp:208-368) on a jittered plane; the Python side of the test
@@ -72,11 +72,52 @@ static void test_rpca()
         p.x = 0.01 * (i % 50), p.y = 0.01 * (i / 50), p.z = 0.001 * ((i * 7919) % 13);
         cloud->push_back(p);
     }
-    std::shared_ptr<LAS_POINT_PROPERTY> props = CalculateFeature::calculate_plan_parameter_rpca(cloud, 0.15, 0.99f, 0.5f, 4);
+    PointPropertyArray props = CalculateFeature::calculate_plan_parameter_rpca(cloud, 0.15, 0.99f, 0.5f, 4);
     unsigned long long h = 1469598103934665603ull;
     const unsigned char* b = reinterpret_cast<const unsigned char*>(props.get());
     for (size_t i = 0; i < cloud->size() * sizeof(LAS_POINT_PROPERTY); i++) h = (h ^ b[i]) * 1099511628211ull;
-    printf("rpca %d %zu %llu\n", CalculateFeature::compute_iteration_number(0.99f, 0.5f), sizeof(LAS_POINT_PROPERTY), h);
+    printf("rpca %d %zu %llu\n", CalculateFeature::compute_iteration_number(0.99f, 0.5f, 3), sizeof(LAS_POINT_PROPERTY), h);
+}
+
+// The loop of calculate_feature.cpp:222-237 as the reference writes it: one tree shared by the OpenMP threads, one
+// nearestKSearch per point into thread-local vectors, PointProperty[j] indexed like boost::shared_array; plus the
+// kd_tree_lod call shape, and the header / sensor pose that VoxelGrid::filter copies (voxel_grid.h:440-442).
+static void test_openmp_loop()
+{
+    CloudPtr cloud(new Cloud);
+    for (int i = 0; i < 400; i++) {
+        CloudItem p;
+        p.x = 0.1 * (i % 20), p.y = 0.1 * (i / 20), p.z = 0.01 * ((i * 7919) % 13);
+        cloud->push_back(p);
+    }
+    KdTreeFLANN<CloudItem> kdtree;
+    kdtree.setInputCloud(cloud);
+    const int point_num = (int)cloud->size();
+    PointPropertyArray PointProperty(new LAS_POINT_PROPERTY[point_num]);
+    long long idsum = 0;
+#pragma omp parallel for schedule(dynamic) reduction(+ : idsum)
+    for (int j = 0; j < point_num; j++) {
+        std::vector<int> pointIdxNKNSearch(20);
+        std::vector<double> pointNKNSquaredDistance(20);
+        PointProperty[j].PointID = j;
+        PointProperty[j].SegmentID = -1;
+        const int N = kdtree.nearestKSearch(cloud->points[j], 20, pointIdxNKNSearch, pointNKNSquaredDistance);
+        if (N > 3 && pointIdxNKNSearch[0] == j && pointNKNSquaredDistance[0] == 0.0) idsum += pointIdxNKNSearch[N - 1];
+    }
+    KdTree lod;
+    lod.setInputCloud(cloud);
+    std::vector<int> k_index;
+    std::vector<double> k_dis;
+    const int n1 = lod.nearestKSearch(cloud->points[7], 1, k_index, k_dis);
+    cloud->header.seq = 42, cloud->header.frame_id = "velodyne";
+    cloud->sensor_origin_[2] = 1.5, cloud->sensor_orientation_[0] = 0.5;
+    VoxelGrid<CloudItem> vg;
+    vg.setInputCloud(cloud);
+    vg.setLeafSize(0.5, 0.5, 0.5);
+    Cloud out;
+    vg.filter(out);
+    printf("omp %lld %d %d %.3g %u %s %.3g %.3g\n", idsum, n1, k_index[0], k_dis[0], out.header.seq, out.header.frame_id.c_str(),
+           out.sensor_origin_[2], out.sensor_orientation_[0]);
 }
 
 // point_segment / tree_filter (static.cpp:8-36) on two sheets: the Python side runs the oracle on the same cloud
@@ -129,6 +170,7 @@ int main(int argc, char** argv)
         test_kd_tree();
         test_rpca();
         test_segment();
+        test_openmp_loop();
     } catch (const std::exception& e) {
         printf("error: %s\n", e.what());
         return 3;

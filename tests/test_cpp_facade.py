@@ -14,7 +14,7 @@ def _build(tmp_path):
     cxx = shutil.which("g++") or "/usr/bin/g++"
     exe = str(tmp_path / "main_test_port")
     libdir = os.path.join(ROOT, "pointcloudprocess_b200")
-    r = subprocess.run([cxx, "-std=c++17", "-O1", "-Wall", os.path.join(ROOT, "tests", "cpp", "main_test_port.cpp"), "-o", exe,
+    r = subprocess.run([cxx, "-std=c++17", "-O1", "-Wall", "-fopenmp", os.path.join(ROOT, "tests", "cpp", "main_test_port.cpp"), "-o", exe,
                         "-L" + libdir, "-lpcp_cuda", "-Wl,-rpath," + libdir], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     return exe
@@ -86,3 +86,10 @@ def test_reference_smoke_functions_known_answers(tmp_path):
     sizes = np.diff(rg["offsets"])
     assert lines[25] == "segment %d %d %d %d" % (len(sizes), len(rg["points"]), h, sizes[sizes > 50].sum())
     assert len(sizes) >= 2
+    # the reference's OpenMP loop (calculate_feature.cpp:222-237) over one shared tree, the kd_tree_lod call shape and
+    # the header / sensor pose copied by filter (voxel_grid.h:440-442)
+    i = np.arange(400)
+    G = np.c_[0.1 * (i % 20), 0.1 * (i // 20), 0.01 * ((i * 7919) % 13)]
+    idx, d2, found = orc.knn_brute(G, G, 20)
+    assert (idx[:, 0] == i).all() and (d2[:, 0] == 0).all()
+    assert lines[26] == "omp %d 1 7 0 42 velodyne 1.5 0.5" % int(idx[:, 19].sum())

@@ -144,3 +144,43 @@ def test_errors_follow_the_reference(pcp, tmp_path, capsys):
     assert pcp.io.loadPCDFile(bad, cl) == -1 and "decompressed lzf data" in capsys.readouterr().out
     assert pcp.io.savePCDFileBinary(tmp_path / "e.pcd", pcp.PointCloud()) == -1  # "Input point cloud has no data!"
     assert "no data" in capsys.readouterr().out
+
+
+def test_malformed_headers_are_rejected_not_trusted(tmp_path):
+    """A PCD header is untrusted input: sizes and counts that would wrap an allocation or a stride, unknown
+    types, and binary payloads that the file does not hold all fail with a status and a message -- no crash, no
+    over-read, no exception through the C ABI."""
+    import ctypes as C
+    from pointcloudprocess_b200 import _lib
+    L = _lib.load()
+    good = ("# .PCD v0.7\nVERSION 0.7\nFIELDS x y z rgba stamp_id\nSIZE 8 8 8 4 4\nTYPE F F F U U\nCOUNT 1 1 1 1 1\n"
+            "WIDTH 3\nHEIGHT 1\nVIEWPOINT 0 0 0 1 0 0 0\nPOINTS 3\nDATA binary\n")
+    cases = {
+        "size0": good.replace("SIZE 8 8 8 4 4", "SIZE 0 8 8 4 4"),
+        "size_neg": good.replace("SIZE 8 8 8 4 4", "SIZE -8 8 8 4 4"),
+        "size3": good.replace("SIZE 8 8 8 4 4", "SIZE 3 8 8 4 4"),
+        "count0": good.replace("COUNT 1 1 1 1 1", "COUNT 0 1 1 1 1"),
+        "count_huge": good.replace("COUNT 1 1 1 1 1", "COUNT 2000000000 1 1 1 1"),
+        "type": good.replace("TYPE F F F U U", "TYPE F Q F U U"),
+        "float2": good.replace("SIZE 8 8 8 4 4", "SIZE 2 8 8 4 4"),
+        "points_huge": good.replace("WIDTH 3", "WIDTH 4000000000").replace("POINTS 3", "POINTS 4000000000"),
+        "short_payload": good,  # 3 x 32 bytes promised, 10 delivered
+    }
+    pts = (C.c_char * (48 * 16))()
+    n, dense = C.c_size_t(0), C.c_int(1)
+    hdr = _lib.PcdHeader()
+    for name, text in cases.items():
+        path = tmp_path / (name + ".pcd")
+        path.write_bytes(text.encode() + b"\0" * 10)
+        st = L.pcp_pcd_load(str(path).encode(), 0, pts, 16, 48, C.byref(n), C.byref(dense))
+        assert st < 0, name
+        assert len(L.pcp_last_error(None)) > 0
+        assert L.pcp_pcd_read_header(str(path).encode(), C.byref(hdr)) < 0, name
+    ok = tmp_path / "ok.pcd"
+    ok.write_bytes(good.encode() + b"\0" * 96)
+    assert L.pcp_pcd_load(str(ok).encode(), 0, pts, 16, 48, C.byref(n), C.byref(dense)) == 0 and n.value == 3
+    # binary_compressed: size words that promise more than the file holds / planes beyond the uncompressed size
+    comp = good.replace("DATA binary", "DATA binary_compressed")
+    bad = tmp_path / "comp.pcd"
+    bad.write_bytes(comp.encode() + (1 << 30).to_bytes(4, "little") + (96).to_bytes(4, "little") + b"\0" * 8)
+    assert L.pcp_pcd_load(str(bad).encode(), 0, pts, 16, 48, C.byref(n), C.byref(dense)) < 0
