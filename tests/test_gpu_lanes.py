@@ -35,18 +35,23 @@ def test_copy_lanes_order_against_compute(ctx):
 
 
 def test_pipelined_host_to_host_equals_device_pass(ctx):
+    """Odd and even pass counts end in different buffer sets: both deliver the device-resident pass's records."""
+    import torch
+    import pointcloudprocess_b200 as pcp
     from pointcloudprocess_b200 import sharded
-    job = sharded.ShardedPipeline(ctx, 0, 1, 300000, seed=9, leaf=0.02, k=20)
-    job.generate()
     try:
+        job = sharded.ShardedPipeline(ctx, 0, 1, 300000, seed=9, leaf=0.02, k=20, torch=torch)
+        job.generate()
         m = job.step_device()
-        ref = np.empty(m * 48, dtype=np.uint8)
-        ctx.memcpy(ref.ctypes.data, job._p(job.props), m * 48)
-        keep = []
-        ms, h2d, d2h, feat = job.time_e2e(5, lambda: None, ctx.synchronize, keep=keep)
-        assert feat == m and h2d == 300000 * 48 and d2h == m * 48 and ms > 0
-        assert len(keep) == 2
-        for rec in keep:  # the last two passes went through different buffer sets
-            assert rec.tobytes() == ref.tobytes()
-    finally:
+        ref = np.zeros(m, dtype=pcp.PACKED_PROP_DTYPE)
+        ctx.props_pack(job._p(job.props), m, ref)
+        ctx.synchronize()
+        for steps in (4, 5):
+            keep = []
+            ms, h2d, d2h, feat = job.time_e2e(steps, lambda: None, torch.cuda.synchronize, keep=keep)
+            assert feat == m and h2d == 300000 * 32 and d2h == m * 24 and ms > 0
+            assert keep[0].tobytes() == ref.tobytes()
         job.close()
+    finally:
+        torch.cuda.synchronize()
+        ctx.set_stream(None)
