@@ -45,7 +45,7 @@ typedef enum pcp_status {
     PCP_ERR_CUDA = -2,    /* CUDA runtime error, see pcp_last_error */
     PCP_ERR_NOMEM = -3,
     PCP_ERR_RANGE = -4,   /* value not representable (e.g. > 2^31-1 points, voxel grid wider than 2^21) */
-    PCP_ERR_NCCL = -5,
+    PCP_ERR_NCCL = -5,    /* reserved: the library itself uses peer copies, not NCCL (pcp_mgpu_*) */
     PCP_ERR_IO = -6       /* file could not be opened / read / written */
 } pcp_status;
 
@@ -296,6 +296,31 @@ PCP_API int pcp_select_boundary(pcp_ctx* ctx, const void* pts, size_t m, size_t 
  * (calculate_feature.cpp:119-206); results go to props[point_id[q]] (device arrays). */
 PCP_API int pcp_features_merge(pcp_ctx* ctx, size_t nq, int k, int nlists, const double* xyz_lists,
                                const double* d2_lists, const int32_t* point_id, void* props, double* eig3, float* lps3);
+
+/* ---- several GPUs of one process ------------------------------------------------------------------------------
+ * The whole pipeline of point_cloud_spliter.cpp:127-128 -- remove_duplicate(leaf), then the per-point plane fit on the
+ * k nearest neighbours -- over the GPUs of one process, for a caller shaped like the reference's main.cpp: one cloud
+ * in host memory in, results in host memory out, no launcher, no torch, no NCCL (the exchanges are peer-to-peer
+ * copies over NVLink between host-thread barriers; one host thread per device inside).  The reference has no
+ * multi-device code; the cut follows its own chunking (5 m blocks, point_cloud_spliter.cpp:221-234) and CloudGrid's
+ * 1 m tiles (cloud_grid.cpp:34-78): slabs of 1 m voxel columns along the longer horizontal side, with a halo.
+ *   pts      n records of stride 32 (packed) or 48 (PointXYZRGBA) in HOST memory;
+ *   leaf     remove_duplicate's leaf (float, point_cloud_helper.h:16); <= 0 skips the voxel grid;
+ *   halo     metres of neighbouring slab each device also sees (>= the k-th neighbour distance of nearly all points;
+ *            2 m for street-scene clouds); the result does not depend on it (queries that outreach it are answered
+ *            by the neighbour exactly);
+ *   out_pts  capacity n records of the same stride: the voxelised cloud; props: capacity n records of 48 bytes,
+ *            props[i] describes out_pts[i] (PointID = i); *m = their number.
+ * The records are those of the single-device calls, point for point; their ORDER is slab after slab along the cut
+ * axis, each slab in voxel order (the single-device order is voxel order over the whole cloud). */
+typedef struct pcp_mgpu pcp_mgpu;
+PCP_API int pcp_mgpu_create(int ndev, const int* devices /* NULL: 0 .. ndev-1 */, pcp_mgpu** out);
+PCP_API void pcp_mgpu_destroy(pcp_mgpu* mg);
+PCP_API int pcp_mgpu_device_count(const pcp_mgpu* mg);
+PCP_API pcp_ctx* pcp_mgpu_ctx(pcp_mgpu* mg, int i); /* device i's context (profiling, synchronisation) */
+PCP_API const char* pcp_mgpu_last_error(const pcp_mgpu* mg);
+PCP_API int pcp_mgpu_features_knn(pcp_mgpu* mg, const void* pts, size_t n, size_t stride, float leaf, int k, double halo,
+                                  void* out_pts, void* props, size_t* m);
 
 /* compute3DCentroid (point_cloud_helper.h:192-230) and getMinMax3D (point_cloud_helper.h:59-90). */
 PCP_API int pcp_centroid(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, double c[3], uint64_t* count);

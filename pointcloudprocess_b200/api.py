@@ -404,6 +404,43 @@ class Context:
         return out
 
 
+class MultiGpu:
+    """pcp_mgpu: the remove_duplicate -> kNN -> plane-fit pipeline over several GPUs of this process (C ABI, no torch)."""
+
+    def __init__(self, ndev, devices=None):
+        self.L = _lib.load()
+        h = C.c_void_p()
+        dv = None if devices is None else np.ascontiguousarray(devices, dtype=np.int32)
+        st = self.L.pcp_mgpu_create(int(ndev), _ptr(dv), C.byref(h))
+        if st != 0:
+            raise _lib.PcpError(st, (self.L.pcp_last_error(None) or b"").decode())
+        self.h, self.ndev = h, int(ndev)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.pcp_mgpu_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def features_knn(self, cloud, leaf=0.02, k=20, halo=2.0):
+        """cloud: host array of POINT_DTYPE or PACKED_POINT_DTYPE.  -> (voxelised cloud, props), slab after slab."""
+        a = np.ascontiguousarray(cloud)
+        n, s = a.shape[0], a.dtype.itemsize
+        out = np.zeros(max(n, 1), dtype=a.dtype)
+        props = np.zeros(max(n, 1), dtype=PROP_DTYPE)
+        m = C.c_size_t(0)
+        st = self.L.pcp_mgpu_features_knn(self.h, a.ctypes.data, n, s, C.c_float(leaf if leaf else 0.0), int(k), float(halo),
+                                          out.ctypes.data, props.ctypes.data, C.byref(m))
+        if st != 0:
+            raise _lib.PcpError(st, (self.L.pcp_last_error(None) or b"").decode())
+        return out[:m.value], props[:m.value]
+
+
 class Index:
     """pcp_index: the search structure built by KdTreeFLANN.setInputCloud."""
 

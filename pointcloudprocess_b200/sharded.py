@@ -37,7 +37,8 @@ REC = 32  # bytes of a packed cloud record
 class ShardPlan:
     """What every rank must agree on: centre, grid box, slab boundaries (voxel columns along x)."""
 
-    def __init__(self, centre, count, min_b, div_b, leaf, bounds, halo):
+    def __init__(self, centre, count, min_b, div_b, leaf, bounds, halo, axis=0):
+        self.axis = int(axis)  # the slabs are cut along the longer horizontal extent of the cloud (0 = x, 1 = y)
         self.centre = np.asarray(centre, dtype=np.float64)
         self.count = int(count)
         self.min_b = np.asarray(min_b, dtype=np.int32)
@@ -47,8 +48,9 @@ class ShardPlan:
         self.halo = float(halo)
 
     def face_x(self, col):
-        """World x of the lower face of voxel column `col` (up to rounding; used only to place the halo)."""
-        return float(self.centre[0]) + (col + int(self.min_b[0])) * self.leaf
+        """World coordinate (along the cut axis) of the lower face of voxel column `col` (up to rounding; used only to
+        place the halo)."""
+        return float(self.centre[self.axis]) + (col + int(self.min_b[self.axis])) * self.leaf
 
 
 def grid_box(mn, mx, centre, leaf):
@@ -427,17 +429,20 @@ class ShardedPipeline:
         mn, mx = allst[:, 0:3].min(axis=0), allst[:, 3:6].max(axis=0)
         leaf = self.leaf or 0.02  # without a voxel grid the columns only serve the cut
         min_b, div_b = grid_box(mn, mx, centre, leaf)
+        # slabs along the longer horizontal side: a 2 km x 30 m strip scanned along y is cut along y, not into eight
+        # slabs 4 m thick and 2 km long
+        ax = 0 if (mx[0] - mn[0]) >= (mx[1] - mn[1]) else 1
         leaf_d = float(np.float32(leaf))
         cpb = max(1, int(round(1.0 / leaf_d)))          # ~1 m of columns per histogram bin (CloudGrid's tile edge)
-        nbins = int(div_b[0]) // cpb + 2
+        nbins = int(div_b[ax]) // cpb + 2
         if nbins > S["hist"].numel():
             raise RuntimeError("cloud spans %d one-metre columns along x, more than the histogram holds" % nbins)
         hist = S["hist"][:nbins]
         hist.zero_()
-        ctx.column_histogram(cloud, 0, leaf_d, centre[0], min_b[0], 0, cpb, (hist.data_ptr(), nbins))
+        ctx.column_histogram(cloud, ax, leaf_d, centre[ax], min_b[ax], 0, cpb, (hist.data_ptr(), nbins))
         yield ("allreduce", hist)
-        bounds = cut_slabs(self._peek(hist), self.world, cpb, int(div_b[0]), leaf, self.halo)
-        return ShardPlan(centre, count, min_b, div_b, leaf, bounds, self.halo)
+        bounds = cut_slabs(self._peek(hist), self.world, cpb, int(div_b[ax]), leaf, self.halo)
+        return ShardPlan(centre, count, min_b, div_b, leaf, bounds, self.halo, ax)
 
     def _step_gen(self, src_ptr):
         """Generator: yields communication requests (module docstring); returns the number of featured points.
@@ -462,7 +467,8 @@ class ShardedPipeline:
         H = self.halo
         self._mark("plan")
         # ---- redistribute: every voxel's points to the rank that owns its column, in point order ----
-        counts = ctx.partition_columns((src_ptr, self.n, REC), 0, P.leaf, P.centre[0], P.min_b[0], P.bounds, self._p(self.part))
+        ax = P.axis
+        counts = ctx.partition_columns((src_ptr, self.n, REC), ax, P.leaf, P.centre[ax], P.min_b[ax], P.bounds, self._p(self.part))
         nbytes = yield ("alltoall", (self.part, [int(c) * REC for c in counts], self.cloud))
         n_own = nbytes // REC
         self._mark("redistribute")
@@ -479,10 +485,10 @@ class ShardedPipeline:
         stage = self.cloud[n_own * REC:]
         cl = cr = 0
         if has_l:
-            cl = ctx.select_range((wp, m, REC), 0, -math.inf, xlo + H, stage.data_ptr(), cap=room)
+            cl = ctx.select_range((wp, m, REC), ax, -math.inf, xlo + H, stage.data_ptr(), cap=room)
             send_l = stage[:cl * REC]
         if has_r:
-            cr = ctx.select_range((wp, m, REC), 0, xhi - H, math.inf, stage.data_ptr() + cl * REC, cap=room - cl)
+            cr = ctx.select_range((wp, m, REC), ax, xhi - H, math.inf, stage.data_ptr() + cl * REC, cap=room - cl)
             send_r = stage[cl * REC:(cl + cr) * REC]
         self._mark("dedup+select")
         recv_l, recv_r = yield ("exchange", (send_l, send_r))
@@ -510,7 +516,7 @@ class ShardedPipeline:
                     self.bnd_xyz = t.empty((self.bnd_cap, 3), dtype=t.float64, device="cuda")
                     self.bnd_sub = [t.empty(self.bnd_cap, dtype=t.int32, device="cuda") for _ in range(2)]
                     self.bnd_sxyz = [t.empty((self.bnd_cap, 3), dtype=t.float64, device="cuda") for _ in range(2)]
-                nF = ctx.select_boundary((wp, m, REC), 0, self._p(self.kth), (xlo - H) if has_l else None,
+                nF = ctx.select_boundary((wp, m, REC), ax, self._p(self.kth), (xlo - H) if has_l else None,
                                          (xhi + H) if has_r else None, self.bnd_cap, self.bnd_idx.data_ptr(),
                                          self.bnd_xyz.data_ptr())
                 if nF >= 0:
@@ -524,7 +530,7 @@ class ShardedPipeline:
             for s, (has, lo, hi) in enumerate(((has_l, xlo - H, None), (has_r, None, xhi + H))):
                 if not has or nF == 0:
                     continue
-                c = ctx.select_boundary((qF.data_ptr(), nF, 24), 0, kthF.data_ptr(), lo, hi, nF, self.bnd_sub[s].data_ptr(),
+                c = ctx.select_boundary((qF.data_ptr(), nF, 24), ax, kthF.data_ptr(), lo, hi, nF, self.bnd_sub[s].data_ptr(),
                                         self.bnd_sxyz[s].data_ptr())
                 side[s] = (self.bnd_sub[s][:c], self.bnd_sxyz[s][:c])
             # ---- exchange 2: the flagged queries ----
@@ -575,7 +581,7 @@ class ShardedPipeline:
         self._mark("end")
         self.stats = {"halo_m": H, "own_in": int(n_own), "own": int(m), "halo_points": int(nl + nr), "boundary_queries": int(nF),
                       "sent": [0 if sd is None else int(sd[0].numel()) for sd in side],
-                      "slab_columns": [P.bounds[self.rank], P.bounds[self.rank + 1]]}
+                      "slab_columns": [P.bounds[self.rank], P.bounds[self.rank + 1]], "axis": "xy"[ax]}
         self.last_m = m
         return m
 

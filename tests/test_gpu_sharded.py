@@ -116,3 +116,30 @@ def test_plan_centroid_equals_the_serial_order_centroid(ctx, orc):
     for P in plans:
         assert P.count == cnt and P.centre.tobytes() == np.asarray(c_ref).tobytes()
         assert P.bounds == plans[0].bounds and (P.min_b == plans[0].min_b).all() and (P.div_b == plans[0].div_b).all()
+
+
+def test_slabs_follow_the_longer_horizontal_axis(ctx):
+    """A strip that runs along y is cut along y (ShardPlan.axis = 1): same results as the single-device run."""
+    import torch
+    import pointcloudprocess_b200 as pcp
+    from pointcloudprocess_b200 import sharded
+    n = 300_000
+    cloud = ctx.synth_cloud("strip", n, seed=6)
+    cloud["x"], cloud["y"] = cloud["y"].copy(), cloud["x"].copy()
+    packed = np.zeros(n, dtype=pcp.PACKED_POINT_DTYPE)
+    ctx.cloud_pack(cloud, n, packed)
+    try:
+        res = {}
+        for world in (1, 3):
+            jobs = [sharded.ShardedPipeline(ctx, r, world, n, leaf=0.02, k=20, torch=torch, halo=0.5) for r in range(world)]
+            for j in jobs:
+                j.set_input(packed[j.first:j.first + j.n])
+            ms = [jobs[0].step_device()] if world == 1 else sharded.run_lockstep([j._step_gen(j._p(j.src)) for j in jobs])
+            res[world] = sharded.combine_digests([sharded.digest(torch, j.work, j.props, m) for j, m in zip(jobs, ms)])
+            if world > 1:
+                assert all(j.plan.axis == 1 and j.stats["axis"] == "y" for j in jobs)
+                assert sum(j.stats["boundary_queries"] for j in jobs) > 0
+        assert res[1] == res[3]
+    finally:
+        torch.cuda.synchronize()
+        ctx.set_stream(None)
