@@ -120,6 +120,36 @@ static void test_openmp_loop()
            out.sensor_origin_[2], out.sensor_orientation_[0]);
 }
 
+// The sharded pipeline straight through the C ABI, as a caller shaped like main.cpp would use it: one cloud in host
+// memory, pcp_mgpu_create / pcp_mgpu_features_knn over 3 shards (on one device here: the contexts share it), against
+// remove_duplicate + calculate_plan_parameter on one context.
+static void test_mgpu()
+{
+    CloudPtr cloud(new Cloud);
+    for (int i = 0; i < 60000; i++) {
+        CloudItem p;
+        p.x = 0.004 * (i % 3000) + 1e-5 * ((i * 7919) % 17), p.y = 0.05 * (i / 3000) + 1e-5 * ((i * 31) % 13), p.z = 0.01 * ((i * 13) % 7);
+        cloud->push_back(p);
+    }
+    const size_t n = cloud->size();
+    std::vector<CloudItem> out(n);
+    std::vector<LAS_POINT_PROPERTY> props(n);
+    const int devices[3] = {0, 0, 0};
+    pcp_mgpu* mg = nullptr;
+    size_t m = 0;
+    int st = pcp_mgpu_create(3, devices, &mg);
+    if (st == PCP_OK) st = pcp_mgpu_features_knn(mg, cloud->points.data(), n, sizeof(CloudItem), 0.02f, 20, 0.5, out.data(), props.data(), &m);
+    if (st != PCP_OK) throw std::runtime_error(std::string("pcp_mgpu: ") + pcp_last_error(nullptr));
+    pcp_mgpu_destroy(mg);
+    PointCloudHelper::remove_duplicate(cloud, 0.02f);
+    PointPropertyArray ref = CalculateFeature::calculate_plan_parameter(cloud, 0.0, 20);
+    // order-independent sums: the shards come slab after slab, the single device in voxel order
+    double sx = 0, rx = 0, sc = 0, rc = 0;
+    for (size_t i = 0; i < m; i++) sx += out[i].x + out[i].y + out[i].z, sc += props[i].curvature + props[i].normal_z * props[i].normal_z;
+    for (size_t i = 0; i < cloud->size(); i++) rx += (*cloud)[i].x + (*cloud)[i].y + (*cloud)[i].z, rc += ref[i].curvature + ref[i].normal_z * ref[i].normal_z;
+    printf("mgpu %zu %zu %d %d\n", m, cloud->size(), fabs(sx - rx) <= 1e-9 * fabs(rx), fabs(sc - rc) <= 1e-9 * fabs(rc));
+}
+
 // point_segment / tree_filter (static.cpp:8-36) on two sheets: the Python side runs the oracle on the same cloud
 static void test_segment()
 {
@@ -171,6 +201,7 @@ int main(int argc, char** argv)
         test_rpca();
         test_segment();
         test_openmp_loop();
+        test_mgpu();
     } catch (const std::exception& e) {
         printf("error: %s\n", e.what());
         return 3;

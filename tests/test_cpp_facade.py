@@ -93,3 +93,6 @@ def test_reference_smoke_functions_known_answers(tmp_path):
     idx, d2, found = orc.knn_brute(G, G, 20)
     assert (idx[:, 0] == i).all() and (d2[:, 0] == 0).all()
     assert lines[26] == "omp %d 1 7 0 42 velodyne 1.5 0.5" % int(idx[:, 19].sum())
+    # pcp_mgpu_* through the C ABI: same points, same records as the single-context calls
+    t = lines[27].split()
+    assert t[0] == "mgpu" and t[1] == t[2] and int(t[1]) > 1000 and t[3:] == ["1", "1"]
