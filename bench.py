@@ -450,7 +450,7 @@ def run_gpu(args):
         job = sharded.ShardedPipeline(ctx, rank, world, n_total, seed=cfg["seed"], leaf=cfg["leaf"], k=cfg["k"],
                                       kind=cfg["kind"], comm=comm, torch=torch, halo=args.halo)
         if comm is not None:
-            comm.peek = job._peek
+            comm.peek, comm.poke = job._peek, job._poke
         job.generate()  # this rank's range of the cloud in point order, packed records resident in HBM (untimed)
         step = job.step_device
     else:

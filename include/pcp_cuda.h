@@ -269,9 +269,12 @@ PCP_API int pcp_cloud_stats(pcp_ctx* ctx, const void* pts, size_t n, size_t stri
  * to the GPU that owns its voxel. */
 PCP_API int pcp_partition_columns(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, int axis, float leaf, double centre,
                                   int32_t min_b, const int32_t* bounds, int nparts, void* out_pts, uint64_t* counts);
-/* At most 1024 bytes of device memory read on the host, ordered behind the work submitted to the context so far and
- * never queued behind a bulk download (a kernel writes them into mapped host memory). */
+/* At most 64 KiB of device memory read on the host (peek) / written from the host (poke), ordered behind the work
+ * submitted to the context so far and never queued behind a bulk copy on a copy lane: a kernel moves them through
+ * mapped host memory.  (A 4-byte cudaMemcpy waits for every piece of a gigabyte upload queued before it on the copy
+ * engine: that alone serialised the pipelined passes with their own uploads.)  Both wait for the kernel. */
 PCP_API int pcp_peek(pcp_ctx* ctx, const void* dev_src, size_t bytes, void* host_dst);
+PCP_API int pcp_poke(pcp_ctx* ctx, void* dev_dst, size_t bytes, const void* host_src);
 /* Histogram of voxel columns along `axis`: column = (int)((p + (-centre)) * (1/leaf) - min_b) as at
  * voxel_grid.h:936; bin = (column - col0) / cols_per_bin clamped to [0, nbins); counts are ADDED to hist_inout. */
 PCP_API int pcp_column_histogram(pcp_ctx* ctx, const void* pts, size_t n, size_t stride, int axis, float leaf,

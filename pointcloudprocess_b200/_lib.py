@@ -18,7 +18,7 @@ SYMBOLS = [
     "pcp_column_histogram", "pcp_select_range", "pcp_select_columns", "pcp_select_boundary", "pcp_features_merge", "pcp_centroid", "pcp_minmax", "pcp_synth_cloud",
     "pcp_features_rpca", "pcp_rpca_iterations", "pcp_region_growing",
     "pcp_remove_duplicate_to", "pcp_mgpu_create", "pcp_mgpu_destroy", "pcp_mgpu_device_count", "pcp_mgpu_ctx", "pcp_mgpu_last_error", "pcp_mgpu_features_knn",
-    "pcp_serial_sum_begin", "pcp_serial_sum_end", "pcp_cloud_stats", "pcp_partition_columns", "pcp_peek",
+    "pcp_serial_sum_begin", "pcp_serial_sum_end", "pcp_cloud_stats", "pcp_partition_columns", "pcp_peek", "pcp_poke",
     "pcp_props_pack", "pcp_props_unpack", "pcp_cloud_pack", "pcp_cloud_unpack", "pcp_sort_pairs", "pcp_exclusive_sum_u32", "pcp_exclusive_sum_u32_noalloc",
     "pcp_pcd_read_header", "pcp_pcd_load", "pcp_pcd_load_many", "pcp_pcd_save", "pcp_lzf_compress", "pcp_lzf_decompress",
 ]
@@ -117,6 +117,7 @@ def load():
         "pcp_cloud_stats": (i32, [vp, vp, sz, sz, vp]),
         "pcp_partition_columns": (i32, [vp, vp, sz, sz, i32, C.c_float, dbl, i32, vp, i32, vp, vp]),
         "pcp_peek": (i32, [vp, vp, sz, vp]),
+        "pcp_poke": (i32, [vp, vp, sz, vp]),
         "pcp_mgpu_create": (i32, [i32, vp, pp]),
         "pcp_mgpu_destroy": (None, [vp]),
         "pcp_mgpu_device_count": (i32, [vp]),

@@ -322,6 +322,11 @@ class Context:
         self._check(self.L.pcp_peek(self.h, _ptr(dev_ptr), out.nbytes, out.ctypes.data))
         return out
 
+    def poke(self, dev_ptr, arr):
+        """A small host array into device memory (pcp_poke: no place in the copy engine's queue)."""
+        a = np.ascontiguousarray(arr)
+        self._check(self.L.pcp_poke(self.h, _ptr(dev_ptr), a.nbytes, a.ctypes.data))
+
     def column_histogram(self, cloud, axis, leaf, centre, min_b, col0, cols_per_bin, hist):
         """hist: uint64 numpy array, or a (device pointer, nbins) tuple; counts are ADDED."""
         p, n, s, keep = _pts(cloud)

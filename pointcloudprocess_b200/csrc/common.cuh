@@ -40,6 +40,7 @@ struct pcp_ctx {
     std::vector<cudaEvent_t> ev_free;
     // copy lanes (pcp_copy_async): streams created on first use, one reusable event per direction
     void* rb_host = nullptr; // mapped pinned scratch of pcp_readback
+    void* wb_host = nullptr; // ... and of pcp_writeto
     // one grow-only device buffer kept between calls (pcp_scratch_get): the neighbour rows of the kNN kernels.  A
     // 2 GB block allocated and freed on every call made the pool's other allocations slow and erratic (sharded
     // steps: 4 ms -> 7..37 ms for the same remove_duplicate); kept here it is allocated once.
@@ -55,8 +56,11 @@ int pcp_fail(pcp_ctx* ctx, int code, const char* fmt, ...);
 // A few bytes from device memory to the host, ordered on the context's stream, and a wait for them.  A kernel
 // writes them into mapped host memory: a cudaMemcpy would queue behind whatever bulk download a copy lane
 // has in flight on the device-to-host copy engine (pcp_copy_async).
-#define PCP_READBACK_MAX 1024
+#define PCP_READBACK_MAX 65536
 int pcp_readback(pcp_ctx* ctx, void* host_dst, const void* dev_src, size_t bytes);
+// The mirror: a few bytes from the host into device memory, ordered on the context's stream, without a place in the
+// host-to-device copy engine's queue (a kernel reads them from mapped host memory).  Waits for the kernel.
+int pcp_writeto(pcp_ctx* ctx, void* dev_dst, const void* host_src, size_t bytes);
 void pcp_set_global_error(const char* msg);
 
 #define PCP_CUDA_TRY(ctx, expr)                                                                              \

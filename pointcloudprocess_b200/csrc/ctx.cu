@@ -1,6 +1,7 @@
 // ctx.cu -- context lifecycle, arena, staging, stage timing, raw memory helpers (include/pcp_cuda.h).
 #include "common.cuh"
 #include <cstring>
+#include <cstdlib>
 #include <algorithm>
 #include <cstdarg>
 
@@ -86,7 +87,10 @@ int InStage::open(pcp_ctx* c, const void* p, size_t bytes)
         return PCP_OK;
     }
     PCP_TRY(pcp_arena_alloc(c, bytes, &owned));
-    PCP_CUDA_TRY(c, cudaMemcpyAsync(owned, p, bytes, cudaMemcpyHostToDevice, c->stream));
+    // small inputs (a few coordinates, offsets) do not take a place in the copy engine's queue, where a bulk upload on
+    // a copy lane may be ahead of them
+    if (bytes <= PCP_READBACK_MAX) PCP_TRY(pcp_writeto(c, owned, p, bytes));
+    else PCP_CUDA_TRY(c, cudaMemcpyAsync(owned, p, bytes, cudaMemcpyHostToDevice, c->stream));
     dptr = owned;
     return PCP_OK;
 }
@@ -107,7 +111,10 @@ int OutStage::open(pcp_ctx* c, void* p, size_t nbytes, bool preload)
         return PCP_OK;
     }
     PCP_TRY(pcp_arena_alloc(c, nbytes, &owned));
-    if (preload) PCP_CUDA_TRY(c, cudaMemcpyAsync(owned, p, nbytes, cudaMemcpyHostToDevice, c->stream));
+    if (preload) {
+        if (nbytes <= PCP_READBACK_MAX) PCP_TRY(pcp_writeto(c, owned, p, nbytes));
+        else PCP_CUDA_TRY(c, cudaMemcpyAsync(owned, p, nbytes, cudaMemcpyHostToDevice, c->stream));
+    }
     dptr = owned;
     return PCP_OK;
 }
@@ -117,6 +124,7 @@ int OutStage::commit(size_t nbytes_override)
     if (!owned || !user) return PCP_OK;
     size_t nb = nbytes_override == (size_t)-1 ? bytes : nbytes_override;
     if (nb > bytes) nb = bytes;
+    if (nb && nb <= PCP_READBACK_MAX) return pcp_readback(ctx, user, owned, nb); // (waits)
     if (nb) PCP_CUDA_TRY(ctx, cudaMemcpyAsync(user, owned, nb, cudaMemcpyDeviceToHost, ctx->stream));
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
     return PCP_OK;
@@ -245,6 +253,7 @@ void pcp_destroy(pcp_ctx* ctx)
         cudaEventDestroy(ctx->lane_out[l]);
     }
     if (ctx->rb_host) cudaFreeHost(ctx->rb_host);
+    if (ctx->wb_host) cudaFreeHost(ctx->wb_host);
     if (ctx->scratch) cudaFree(ctx->scratch);
     if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -364,6 +373,24 @@ static __global__ void readback_kernel(unsigned char* __restrict__ dst, const un
 
 } // extern "C"
 
+int pcp_writeto(pcp_ctx* ctx, void* dev_dst, const void* host_src, size_t bytes)
+{
+    if (!bytes) return PCP_OK;
+    if (bytes > PCP_READBACK_MAX) {
+        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(dev_dst, host_src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+        return PCP_OK;
+    }
+    if (!ctx->wb_host) PCP_CUDA_TRY(ctx, cudaHostAlloc(&ctx->wb_host, PCP_READBACK_MAX, cudaHostAllocMapped));
+    void* dalias = nullptr;
+    PCP_CUDA_TRY(ctx, cudaHostGetDevicePointer(&dalias, ctx->wb_host, 0));
+    memcpy(ctx->wb_host, host_src, bytes);
+    readback_kernel<<<1, 256, 0, ctx->stream>>>(static_cast<unsigned char*>(dev_dst), static_cast<const unsigned char*>(dalias), (unsigned)bytes);
+    PCP_CUDA_TRY(ctx, cudaGetLastError());
+    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream)); // the staging word is free again
+    return PCP_OK;
+}
+
 int pcp_readback(pcp_ctx* ctx, void* host_dst, const void* dev_src, size_t bytes)
 {
     if (!bytes) return PCP_OK;
@@ -375,7 +402,7 @@ int pcp_readback(pcp_ctx* ctx, void* host_dst, const void* dev_src, size_t bytes
     if (!ctx->rb_host) PCP_CUDA_TRY(ctx, cudaHostAlloc(&ctx->rb_host, PCP_READBACK_MAX, cudaHostAllocMapped));
     void* dalias = nullptr;
     PCP_CUDA_TRY(ctx, cudaHostGetDevicePointer(&dalias, ctx->rb_host, 0));
-    readback_kernel<<<1, 128, 0, ctx->stream>>>(static_cast<unsigned char*>(dalias), static_cast<const unsigned char*>(dev_src),
+    readback_kernel<<<1, 256, 0, ctx->stream>>>(static_cast<unsigned char*>(dalias), static_cast<const unsigned char*>(dev_src),
                                                 (unsigned)bytes);
     PCP_CUDA_TRY(ctx, cudaGetLastError());
     PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
@@ -406,7 +433,7 @@ int pcp_copy_async(pcp_ctx* ctx, int lane, void* dst, const void* src, size_t by
     PCP_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->lane[lane], ctx->lane_in[lane], 0));
     // In pieces: a copy engine serves one copy at a time, and the few-byte read-backs of the compute stream
     // (counts, cell totals) must not queue behind a gigabyte transfer.
-    const size_t piece = (size_t)32 << 20;
+    static const size_t piece = ((size_t)(getenv("PCP_COPY_PIECE_MB") ? std::max(1, atoi(getenv("PCP_COPY_PIECE_MB"))) : 32)) << 20;
     for (size_t off = 0; off < bytes; off += piece)
         PCP_CUDA_TRY(ctx, cudaMemcpyAsync(static_cast<char*>(dst) + off, static_cast<const char*>(src) + off,
                                           std::min(piece, bytes - off), cudaMemcpyDefault, ctx->lane[lane]));

@@ -301,7 +301,7 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 fprintf(stderr, "[pcp knn] far failures: overflow=%llu (cells %llu) beyond=%llu uncert=%llu no-bound=%llu mean level=%.2f\n",
                         h[18], h[23], h[19], h[20], h[21], hc[4] ? (double)h[22] / hc[4] : 0.0);
             }
-            if (nfail) PCP_CUDA_TRY(ctx, cudaMemcpyAsync(counters.p, &hc[4], 4, cudaMemcpyHostToDevice, ctx->stream));
+            if (nfail) PCP_TRY(pcp_writeto(ctx, counters.p, &hc[4], 4));
         } else {
             // k too large for the cell kernel's shared-memory lists: every query takes the warp kernel
             nfail = (uint32_t)nv;
@@ -415,7 +415,7 @@ extern "C" int pcp_knn(const pcp_index* ix, const void* q, size_t nq, size_t qst
         if (use_far) {
             PCP_TRY(fail.alloc(ctx, nq));
             const uint32_t nq32 = (uint32_t)nq;
-            PCP_CUDA_TRY(ctx, cudaMemcpyAsync(counter.p, &nq32, 4, cudaMemcpyHostToDevice, ctx->stream));
+            PCP_TRY(pcp_writeto(ctx, counter.p, &nq32, 4));
             pcp_fknn_params P;
             P.rec = ix->rec, P.fpt = ix->fpt, P.htab = ix->htab, P.hmask = ix->hmask, P.ltab = ix->ltab, P.lmask = ix->lmask;
             P.cinfo = ix->cinfo, P.ckey = ix->ckey, P.cstart = ix->cstart, P.ncell = ix->ncell;

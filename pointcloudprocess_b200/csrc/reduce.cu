@@ -158,8 +158,7 @@ extern "C" int pcp_cloud_stats(pcp_ctx* ctx, const void* pts, size_t n, size_t s
     for (int d = 0; d < 3; d++) h[d] = bb.mn[d], h[3 + d] = bb.mx[d], h[6 + d] = bb.sum[d];
     h[9] = (double)bb.count;
     if (pcp_classify(ctx, out10) == PCP_PTR_DEVICE) {
-        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(out10, h, sizeof(h), cudaMemcpyHostToDevice, ctx->stream));
-        PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+        PCP_TRY(pcp_writeto(ctx, out10, h, sizeof(h)));
     } else {
         memcpy(out10, h, sizeof(h));
     }

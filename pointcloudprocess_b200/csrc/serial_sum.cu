@@ -419,7 +419,7 @@ extern "C" int pcp_serial_sum_begin(pcp_ctx* ctx, const void* dev_pts, size_t n,
     DevBuf<double> pred;
     if (predicted3) {
         PCP_TRY(pred.alloc(ctx, 3));
-        PCP_CUDA_TRY(ctx, cudaMemcpyAsync(pred.p, predicted3, 24, cudaMemcpyDefault, ctx->stream));
+        PCP_TRY(pcp_writeto(ctx, pred.p, predicted3, 24));
     }
     pcp_serial_plan* P = nullptr;
     StageTimer t(ctx, "shard.serial_sum_begin", 24.0 * n);
@@ -450,7 +450,7 @@ extern "C" int pcp_serial_sum_end(void* handle, double* carry3_inout)
             } else {
                 DevBuf<double> c;
                 st = c.alloc(ctx, 3);
-                if (st == PCP_OK && cudaMemcpyAsync(c.p, carry3_inout, 24, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) st = PCP_ERR_CUDA;
+                if (st == PCP_OK) st = pcp_writeto(ctx, c.p, carry3_inout, 24);
                 if (st == PCP_OK) st = pcp_serial_sum_finish(ctx, H->plan, c.p);
                 if (st == PCP_OK) st = pcp_readback(ctx, carry3_inout, c.p, 24);
             }

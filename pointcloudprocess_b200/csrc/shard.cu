@@ -106,8 +106,7 @@ extern "C" int pcp_serial_sum(pcp_ctx* ctx, const void* pts, size_t n, size_t st
     PCP_TRY(in.open(ctx, pts, n * stride));
     DevBuf<double> s3;
     PCP_TRY(s3.alloc(ctx, 3));
-    PCP_CUDA_TRY(ctx, cudaMemcpyAsync(s3.p, sum3, 24, cudaMemcpyHostToDevice, ctx->stream));
-    PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+    PCP_TRY(pcp_writeto(ctx, s3.p, sum3, 24));
     PCP_TRY(pcp_serial_sum_device(ctx, in.dptr, n, stride, s3.p, 1));
     pcp_bbox bb;
     PCP_TRY(pcp_bbox_host(ctx, in.dptr, n, stride, &bb));
@@ -474,6 +473,15 @@ extern "C" int pcp_partition_columns(pcp_ctx* ctx, const void* pts, size_t n, si
     for (int p = 0; p < nparts; p++) counts[p] = hf[p + 1] - hf[p];
     PCP_TRY(o.commit((size_t)hf[nparts] * stride));
     return PCP_OK;
+}
+
+// ... and the other way: a few host bytes into device memory without a place in the copy engine's queue
+extern "C" int pcp_poke(pcp_ctx* ctx, void* dev_dst, size_t bytes, const void* host_src)
+{
+    if (!ctx || !dev_dst || !host_src || bytes > PCP_READBACK_MAX) return pcp_fail(ctx, PCP_ERR_INVALID, "pcp_poke: bad argument (at most %d bytes)", PCP_READBACK_MAX);
+    std::lock_guard<std::recursive_mutex> lock(ctx->mu);
+    PCP_CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+    return pcp_writeto(ctx, dev_dst, host_src, bytes);
 }
 
 // A few bytes of device memory read on the host, ordered behind the work submitted to the context so far, without

@@ -96,10 +96,15 @@ class DistComm:
     travel in band (a one-word message before the payload), read back through `peek` -- on a GPU the library's mapped
     read-back, which does not queue behind a bulk download on the copy engine."""
 
-    def __init__(self, dist, torch, rank, world, device, peek=None):
+    def __init__(self, dist, torch, rank, world, device, peek=None, poke=None):
         self.dist, self.torch, self.rank, self.world, self.device = dist, torch, rank, world, device
         self.peek = peek or (lambda t: t.cpu().numpy())
+        # poke(device tensor, numpy array): small host values into device memory.  On a GPU the library's mapped write:
+        # a plain copy takes a place in the copy engine's queue BEHIND the bulk upload of the next pass, and every
+        # size word of every exchange then waits for that upload -- the passes and their uploads ran one after the other
+        self.poke = poke or (lambda ten, arr: ten.copy_(torch.from_numpy(np.ascontiguousarray(arr)).view(ten.dtype).reshape(ten.shape)))
         self._sz = None
+        self._cnt = None
 
     # -- small helpers --
     def _p2p(self, ops):
@@ -116,7 +121,7 @@ class DistComm:
         host = np.zeros(2 * self.world, dtype=np.int64)
         for j, (peer, nb) in enumerate(pairs):
             host[j] = nb
-        out.copy_(t.from_numpy(host), non_blocking=False)
+        self.poke(out, host)
         ops = []
         for j, (peer, nb) in enumerate(pairs):
             ops += [d.P2POp(d.isend, out[j:j + 1], peer), d.P2POp(d.irecv, inn[j:j + 1], peer)]
@@ -168,7 +173,10 @@ class DistComm:
             return recv.get(self.rank - 1), recv.get(self.rank + 1)
         if kind == "alltoall":
             buf, counts, out = arg  # counts[q]: bytes for rank q, consecutive in buf; out: receive buffer (uint8)
-            cnt = t.from_numpy(np.asarray(counts, dtype=np.int64)).to(self.device)
+            if self._cnt is None:
+                self._cnt = t.zeros(self.world, dtype=t.int64, device=self.device)
+            cnt = self._cnt
+            self.poke(cnt, np.asarray(counts, dtype=np.int64))
             allc = self.handle(("allgather", cnt))
             m = np.asarray(self.peek(allc)).reshape(self.world, self.world)  # m[src][dst]
             recv_counts = [int(m[q][self.rank]) for q in range(self.world)]
@@ -191,7 +199,10 @@ class DistComm:
             return total
         if kind == "gather":
             ten, nbytes = arg  # to rank 0: returns (uint8 tensor, byte offsets per rank) there, None elsewhere
-            cnt = t.tensor([int(nbytes)], dtype=t.int64, device=self.device)
+            if self._cnt is None:
+                self._cnt = t.zeros(self.world, dtype=t.int64, device=self.device)
+            cnt = self._cnt[:1]
+            self.poke(cnt, np.asarray([int(nbytes)], dtype=np.int64))
             allc = [int(v) for v in np.asarray(self.peek(self.handle(("allgather", cnt)))).reshape(-1)]
             if self.rank == 0:
                 off = np.concatenate([[0], np.cumsum(allc)]).astype(np.int64)
@@ -341,12 +352,19 @@ class ShardedPipeline:
     def _p(buf):
         return buf.data_ptr() if hasattr(buf, "data_ptr") else buf.ptr
 
+    def _poke(self, ten, arr):
+        """A small host array into a device tensor through the library's mapped write (pcp_poke)."""
+        if ten.is_cuda:
+            self.ctx.poke(ten.data_ptr(), np.ascontiguousarray(arr))
+        else:
+            ten.copy_(self.torch.from_numpy(np.ascontiguousarray(arr)).view(ten.dtype).reshape(ten.shape))
+
     def _peek(self, ten):
-        """A small device tensor on the host, through the library's mapped read-back (<= 1 KiB), else a plain copy."""
+        """A small device tensor on the host, through the library's mapped read-back (<= 64 KiB), else a plain copy."""
         nb = ten.numel() * ten.element_size()
         dt = {self.torch.int64: np.int64, self.torch.float64: np.float64, self.torch.int32: np.int32,
               self.torch.uint8: np.uint8}[ten.dtype]
-        if nb <= 1024 and ten.is_cuda:
+        if nb <= 65536 and ten.is_cuda:
             return self.ctx.peek(ten.contiguous().data_ptr(), dt, ten.numel()).reshape(tuple(ten.shape))
         return ten.cpu().numpy()
 
