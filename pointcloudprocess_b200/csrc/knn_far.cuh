@@ -15,7 +15,7 @@
 #pragma once
 #include "knn_fast.cuh"
 
-#define PCP_FAR_NSEL 128   // selected base cells per attempt
+#define PCP_FAR_NSEL 128   // selected base cells per attempt (256, with a 128-entry cell cache to stay at 4 blocks per SM: 1.4 k instead of 7 k queries overflow to the streaming kernel, but the kernel itself 11.6 -> 12.6 ms)
 #define PCP_FAR_CCACHE 256 // cells whose (nearest-corner distance, first point, count) are kept between passes
 
 template <int CAP> struct pcp_far_smem : pcp_fk_smem<CAP, 32> {

@@ -114,7 +114,45 @@ template <int KPL> static __global__ void __launch_bounds__(128) knn_warp_kernel
             const int by = min(max(pcp_cell_coord(qy, P.g.org[1], P.g.inv_h, 0), 0), P.g.dims[1] - 1);
             const int bz = min(max(pcp_cell_coord(qz, P.g.org[2], P.g.inv_h, 0), 0), P.g.dims[2] - 1);
             if (level > P.g.top_level) level = P.g.top_level;
-            for (; level <= P.g.top_level; level++) {
+            // the points [s0, s1) against the list: four chunks of 32 points in flight per lane (the scan is bound by the
+            // latency of its loads; insertions are rare once the list is warm, and the result does not depend on the order)
+            auto scan_range = [&](pcp_wlist<KPL>& Ls, double& kd, int& ki, uint32_t s0, uint32_t s1) {
+                constexpr int WU = 4;
+                for (uint32_t c0 = s0; c0 < s1; c0 += 32 * WU) {
+                    pcp_rec r[WU];
+#pragma unroll
+                    for (int u = 0; u < WU; u++) {
+                        const uint32_t t = c0 + 32 * u + lane;
+                        if (t < s1) r[u] = pcp_load_rec(P.rec, t);
+                    }
+#pragma unroll
+                    for (int u = 0; u < WU; u++) {
+                        const uint32_t t0 = c0 + 32 * u;
+                        if (t0 >= s1) break;
+                        const uint32_t t = t0 + lane;
+                        double d2 = DBL_MAX;
+                        int ci = 0x7fffffff;
+                        if (t < s1) {
+                            d2 = pcp_dist2(qx, qy, qz, r[u].x, r[u].y, r[u].z);
+                            ci = (int)r[u].idx;
+                        }
+                        unsigned qual = __ballot_sync(0xffffffffu, t < s1 && pcp_less(d2, ci, kd, ki));
+                        while (qual) {
+                            const int src = __ffs(qual) - 1;
+                            qual &= qual - 1;
+                            const double xd = __shfl_sync(0xffffffffu, d2, src);
+                            const int xi = __shfl_sync(0xffffffffu, ci, src);
+                            if (!pcp_less(xd, xi, kd, ki)) continue; // threshold moved since the ballot
+                            pcp_wlist_insert<KPL>(Ls, lane, xd, xi, t0 + src);
+                            pcp_wlist_kth<KPL>(Ls, P.kk, kd, ki);
+                        }
+                    }
+                }
+            };
+            // (measured and dropped: with the far kernel's bound, streaming only the base cells that the bound sphere
+            // touches -- the overflow queries' bounds are corner bounds, their boxes thousands of cells: no faster)
+            const bool settled = false;
+            for (; !settled && level <= P.g.top_level; level++) {
 #pragma unroll
                 for (int s = 0; s < KPL; s++) L.d[s] = DBL_MAX, L.idx[s] = 0x7fffffff, L.pos[s] = 0xffffffffu;
                 const int cx = bx >> level, cy = by >> level, cz = bz >> level;
@@ -143,39 +181,7 @@ template <int KPL> static __global__ void __launch_bounds__(128) knn_warp_kernel
                 for (int nb = 0; nb < 27; nb++) {
                     const uint32_t s0 = __shfl_sync(0xffffffffu, lo, nb);
                     const uint32_t s1 = __shfl_sync(0xffffffffu, hi, nb);
-                    // four chunks of 32 points in flight per lane: the scan is bound by the latency of its loads (the
-                    // insertions are rare once the list is warm), and the result does not depend on the order
-                    constexpr int WU = 4;
-                    for (uint32_t c0 = s0; c0 < s1; c0 += 32 * WU) {
-                        pcp_rec r[WU];
-#pragma unroll
-                        for (int u = 0; u < WU; u++) {
-                            const uint32_t t = c0 + 32 * u + lane;
-                            if (t < s1) r[u] = pcp_load_rec(P.rec, t);
-                        }
-#pragma unroll
-                        for (int u = 0; u < WU; u++) {
-                            const uint32_t t0 = c0 + 32 * u;
-                            if (t0 >= s1) break;
-                            const uint32_t t = t0 + lane;
-                            double d2 = DBL_MAX;
-                            int ci = 0x7fffffff;
-                            if (t < s1) {
-                                d2 = pcp_dist2(qx, qy, qz, r[u].x, r[u].y, r[u].z);
-                                ci = (int)r[u].idx;
-                            }
-                            unsigned qual = __ballot_sync(0xffffffffu, t < s1 && pcp_less(d2, ci, kd, ki));
-                            while (qual) {
-                                const int src = __ffs(qual) - 1;
-                                qual &= qual - 1;
-                                const double xd = __shfl_sync(0xffffffffu, d2, src);
-                                const int xi = __shfl_sync(0xffffffffu, ci, src);
-                                if (!pcp_less(xd, xi, kd, ki)) continue; // threshold moved since the ballot
-                                pcp_wlist_insert<KPL>(L, lane, xd, xi, t0 + src);
-                                pcp_wlist_kth<KPL>(L, P.kk, kd, ki);
-                            }
-                        }
-                    }
+                    scan_range(L, kd, ki, s0, s1);
                 }
                 const double g2 = pcp_guarantee2(P.g, level, cx, cy, cz, qx, qy, qz);
                 if (P.dbg) {
