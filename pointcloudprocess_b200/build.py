@@ -17,6 +17,8 @@ NVCC = os.environ.get("PCP_NVCC", "/usr/local/cuda/bin/nvcc")
 HOSTCXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-fmad=false",
          "-Xcompiler", "-fPIC,-fvisibility=hidden,-O3", "-ccbin", HOSTCXX, "--expt-relaxed-constexpr"]
+# measurement builds only (e.g. PCP_NVCC_DEFS="PCP_FD_REASONS"); objects are cached by time stamp, not by flags: use force
+FLAGS += ["-D" + d for d in os.environ.get("PCP_NVCC_DEFS", "").split()]
 
 
 def _sources():

@@ -3,6 +3,7 @@
 // (KdTreeFLANN::nearestKSearch, kd_tree.h:814-845).
 #include "knn_warp.cuh"
 #include "knn_far.cuh"
+#include "knn_wide.cuh"
 #include <algorithm>
 #include <climits>
 #include <cstdlib>
@@ -95,6 +96,24 @@ int launch_fknn(pcp_ctx* ctx, const pcp_fknn_params& P)
     return launch_fknn_t<160, 8, 480, true>(ctx, P);
 }
 
+// the third pass: leaves with open queries, over the box of their bound spheres (knn_wide.cuh)
+template <int CAP, int GS, int CAND> int launch_wide_t(pcp_ctx* ctx, const pcp_fknn_params& P)
+{
+    const size_t smem = PCP_FK_WARPS * pcp_wide_layout<CAP, GS, CAND>::bytes();
+    PCP_CUDA_TRY(ctx, cudaFuncSetAttribute(knn_wide_kernel<CAP, GS, CAND>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    PCP_CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, knn_wide_kernel<CAP, GS, CAND>, 32 * PCP_FK_WARPS, smem));
+    if (per_sm < 1) return pcp_fail(ctx, PCP_ERR_CUDA, "knn_wide_kernel does not fit an SM");
+    knn_wide_kernel<CAP, GS, CAND><<<ctx->sm_count * per_sm, 32 * PCP_FK_WARPS, smem, ctx->stream>>>(P);
+    PCP_LAUNCH_CHECK(ctx);
+    return PCP_OK;
+}
+int launch_wide(pcp_ctx* ctx, const pcp_fknn_params& P)
+{
+    if (P.kk <= 24) return launch_wide_t<32, 8, 256>(ctx, P);
+    return launch_wide_t<64, 8, 480>(ctx, P);
+}
+
 // the second pass over the items the first one found too dense to stage (k <= 52)
 #ifndef PCP_FK_CAND2
 #define PCP_FK_CAND2 800
@@ -174,8 +193,8 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
         PCP_TRY(fail_u.alloc(ctx, nv));
         DevBuf<uint32_t> fail2;
         PCP_TRY(fail2.alloc(ctx, nv));
-        PCP_TRY(counters.alloc(ctx, 8));
-        PCP_CUDA_TRY(ctx, cudaMemsetAsync(counters.p, 0, 32, ctx->stream));
+        PCP_TRY(counters.alloc(ctx, 12));
+        PCP_CUDA_TRY(ctx, cudaMemsetAsync(counters.p, 0, 48, ctx->stream));
         uint32_t nfail = 0;
         if (kk <= 128) {
             // work items = octree leaves whose capacity follows k (index.cu; 24 for k = 20)
@@ -216,8 +235,8 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
             unsigned long long hfast6 = 0, hfast7 = 0;
             const bool want_dbg = getenv("PCP_KNN_DEBUG") != nullptr;
             if (want_dbg) {
-                PCP_TRY(dbg.alloc(ctx, 24));
-                PCP_CUDA_TRY(ctx, cudaMemsetAsync(dbg.p, 0, 24 * 8, ctx->stream));
+                PCP_TRY(dbg.alloc(ctx, 32));
+                PCP_CUDA_TRY(ctx, cudaMemsetAsync(dbg.p, 0, 32 * 8, ctx->stream));
                 P.dbg = dbg.p;
             }
             // deferred features: the search kernels only write neighbour rows; one thread-per-query kernel fits the planes
@@ -233,6 +252,24 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 mark_rows_kernel<<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(rows.p, nv, k);
                 PCP_LAUNCH_CHECK(ctx);
                 P.nbr_out = rows.p;
+            }
+            // lists the FP32 search cannot order go to knn_rerank_kernel (about 1 % of the queries; room for 1 in 16)
+            DevBuf<uint32_t> rr_list;
+            const int rr_cap_words = kk <= 24 ? 32 : 64; // the list capacity CAP of launch_fknn's instances
+            if (defer && kk <= 52 && !getenv("PCP_FK_NORERANK")) {
+                const size_t cap = std::max<size_t>(nv / 16, 1024);
+                PCP_TRY(rr_list.alloc(ctx, cap * (size_t)(rr_cap_words + PCP_RR_HEAD)));
+                P.rr.list = rr_list.p;
+                P.rr.count = counters.p + 5;
+                P.rr.cap = (uint32_t)cap;
+            }
+            DevBuf<uint2> wide_list;
+            const bool wide = defer && kk <= 52 && !getenv("PCP_FK_NOWIDE");
+            if (wide) {
+                PCP_TRY(wide_list.alloc(ctx, nv)); // a record holds at least one of the far list's entries
+                P.wide_list = wide_list.p;
+                P.wide_count = counters.p + 8;
+                P.wide_work = counters.p + 9;
             }
             DevBuf<uint32_t> dense_list;
             const bool two_pass = kk <= 52 && !getenv("PCP_FK_ONEPASS");
@@ -256,6 +293,16 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 P2.dense_count = nullptr;
                 P2.work_counter = counters.p + 7;
                 PCP_TRY(launch_fknn_dense2(ctx, P2));
+            }
+            if (wide) {
+                StageTimer t(ctx, "knn.wide_kernel");
+                PCP_TRY(launch_wide(ctx, P));
+            }
+            if (P.rr.list) {
+                StageTimer t(ctx, "knn.rerank_kernel");
+                if (rr_cap_words == 32) knn_rerank_kernel<32><<<ctx->sm_count * 8, 128, 0, ctx->stream>>>(P);
+                else knn_rerank_kernel<64><<<ctx->sm_count * 8, 128, 0, ctx->stream>>>(P);
+                PCP_LAUNCH_CHECK(ctx);
             }
             if (want_dbg) {
                 unsigned long long h[16];
@@ -290,13 +337,16 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
             PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
             nfail = hc[4];
             if (want_dbg) {
-                unsigned long long h[24];
-                PCP_TRY(pcp_readback(ctx, h, dbg.p, 24 * 8));
+                unsigned long long h[32];
+                PCP_TRY(pcp_readback(ctx, h, dbg.p, 32 * 8));
                 PCP_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
                 fprintf(stderr, "[pcp knn] far queries=%u attempts=%llu (block too sparse %llu) cells/attempt=%.1f searches=%llu "
                                 "cand/search=%.1f selected cells/search=%.1f uncertified=%llu tightened=%llu streaming-kernel queries=%u\n",
                         hc[0], h[10], h[16], h[10] ? (double)h[11] / h[10] : 0.0, h[12], h[12] ? (double)h[13] / h[12] : 0.0,
                         h[12] ? (double)h[14] / h[12] : 0.0, h[15], h[17], hc[4]);
+                fprintf(stderr, "[pcp knn] wide pass: leaves=%llu (no bounded query %llu, cells hold too many or too few points %llu, box over capacity %llu) "
+                                "queries=%llu settled=%llu points in cells/leaf=%.1f staged/leaf=%.1f\n", h[24], h[25], h[26], h[27], h[28],
+                        h[29], h[24] ? (double)h[31] / h[24] : 0.0, h[24] ? (double)h[30] / h[24] : 0.0);
                 fprintf(stderr, "[pcp knn] far searches with bound >= certified radius: %llu, of which certified anyway %llu\n", h[6] - hfast6, h[7] - hfast7);
                 fprintf(stderr, "[pcp knn] far failures: overflow=%llu (cells %llu) beyond=%llu uncert=%llu no-bound=%llu mean level=%.2f\n",
                         h[18], h[23], h[19], h[20], h[21], hc[4] ? (double)h[22] / hc[4] : 0.0);

@@ -189,6 +189,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
         qi = __shfl_sync(0xffffffffu, qi, 0);
         if (qi >= nq) break;
         const uint32_t qpos = A.ext_q ? qi : __ldg(A.list + qi);
+        if (!A.ext_q && qpos == 0xffffffffu) continue; // settled by the third dense pass (knn_wide.cuh)
         float U = A.ext_q ? INF : __ldg(A.listU + qi);
         pcp_rec q;
         if (A.ext_q) {

@@ -34,6 +34,13 @@
 #define PCP_FK_MINB 6
 #endif
 
+// lists the FP32 search could not order (see pcp_fd_search): entries of PCP_RR_HEAD + CAP words
+struct pcp_rr {
+    uint32_t* list = nullptr;
+    uint32_t* count = nullptr;
+    uint32_t cap = 0;
+};
+
 struct pcp_fknn_params {
     const pcp_rec* rec;
     const float4* fpt; // (float)(p - grid origin); w unused
@@ -76,6 +83,12 @@ struct pcp_fknn_params {
     // of one SM sit in both at once: the instruction working set exceeded the 32 KB L1.5 instruction cache and
     // 'no instruction' was the top stall of the fused kernels (6.5 cycles per issue).
     uint32_t* nbr_out = nullptr;
+    pcp_rr rr;               // re-rank list (deferred rows only)
+    // the third pass (knn_wide.cuh): one record per leaf that put queries on the far list -- x: its first entry there,
+    // y: entries | level << 8
+    uint2* wide_list = nullptr;
+    uint32_t* wide_count = nullptr;
+    uint32_t* wide_work = nullptr;
     unsigned long long* dbg; // optional counters (PCP_KNN_DEBUG=1), NULL in production
 };
 
@@ -488,6 +501,8 @@ template <int CAP, int GS, int CAND, bool DEFER = false> struct pcp_fd_smem {
 #define PCP_FD_BEYOND 1 // fewer than kk candidates inside `top`, or list overflow: no bound known
 #define PCP_FD_AMBIG 2  // kk nearest found among the staged candidates but order / certification not provable in FP32
 #define PCP_FD_IDLE 4
+#define PCP_FD_RERANK 5 // as AMBIG for the order alone: handed to knn_rerank_kernel with its list
+#define PCP_RR_HEAD 8   // words before the positions of a re-rank entry: qpos, m, edge, amb2, g2, delta
 
 // acc + (x < 0): the sign bit as the increment (PTX, so that the compiler does not turn it back into a compare, a
 // select and two moves)
@@ -506,7 +521,7 @@ template <int G, int CAP, int CAND, bool DEFER>
 __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CAND, DEFER>& S, int lane, bool active,
                                              uint32_t* nbr_base, uint32_t nbr_off, int nbr_stride, int kk, float qfx,
                                              float qfy, float qfz,
-                                             float top, float g2, float e1, float& dku)
+                                             float top, float g2, float e1, float& dku, const pcp_rr& rr, uint32_t qpos)
 {
     constexpr int SL = CAP / G;
     constexpr int NBL = PCP_FD_NB / G;
@@ -657,9 +672,31 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
 #pragma unroll
     for (int o = G / 2; o > 0; o >>= 1) dkl = fmaxf(dkl, __shfl_xor_sync(0xffffffffu, dkl, o));
     ambig = ((__ballot_sync(0xffffffffu, ambig) >> gbase) & gmask) != 0u;
+    // FP32 could not order the list (two entries closer than the error bound, an entry at a bucket edge): the list
+    // -- EVERY staged candidate below the upper edge of bucket b* -- goes to the re-rank list with the thresholds the
+    // exact k-th distance has to clear, and knn_rerank_kernel orders it on exact distances.  (Done here, inside the
+    // search, the doubles and the call cost the 64-register kernel 0.9 ms to save the far kernel 1.1.)
+    if constexpr (DEFER && CAP <= 64) {
+        if (live && ambig && rr.list) { // uniform over the group
+            uint32_t slot = 0;
+            if (gl == 0) slot = atomicAdd(rr.count, 1u);
+            slot = __shfl_sync(gmask << gbase, slot, gbase);
+            if (slot < rr.cap) {
+                uint32_t* const ent = rr.list + (size_t)slot * (CAP + PCP_RR_HEAD);
+                if (gl == 0) {
+                    ent[0] = qpos, ent[1] = m, ent[2] = __float_as_uint(edge), ent[3] = __float_as_uint(amb2);
+                    ent[4] = __float_as_uint(g2), ent[5] = __float_as_uint(delta);
+                }
+#pragma unroll
+                for (int s = 0; s < SL; s++)
+                    if (s * G + gl < (int)m) ent[PCP_RR_HEAD + s * G + gl] = S.pos_at(lpos[s * G + gl]);
+                st = PCP_FD_RERANK;
+            }
+        }
+    }
     // the k-th against bucket b*+1 and against the certified radius
     dku = ((dkl >= 0.0f && !ambig) ? dkl : edge) + delta;
-    if (live) {
+    if (live && st != PCP_FD_RERANK) {
         if (ambig || dkl < 0.0f || edge - dkl <= amb2 || !(dkl + amb2 < g2)) st = PCP_FD_AMBIG;
     }
     __syncwarp();
@@ -698,11 +735,39 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
         if (item >= nitem) break;
         if (P.item_list) item = __ldg(P.item_list + item);
         const uint32_t cell = __ldg(P.item_cell + item);
-        const uint32_t first = __ldg(P.item_first + item);
+        const uint32_t first0 = __ldg(P.item_first + item);
         const uint32_t meta = __ldg(P.item_meta + item);
         // the item is an octree leaf: a cell of edge h0 = h * 2^level holding the nq queries first..first+nq-1
-        const int level = (int)(meta >> 8);
-        const int nq = (int)(meta & 0xffu);
+        const int level0 = (int)(meta >> 8);
+        const int nq0 = (int)(meta & 0xffu);
+        // Sub-items (the second pass only): a leaf whose 3x3x3 block holds more points than even this pass stages --
+        // a sparse leaf beside a dense surface -- is cut into its child cells (one level down: an eighth of the block's
+        // volume), each searched as an item of its own.  Its queries' neighbours are mostly the surface's points, close
+        // by, and the far kernel, which would take them otherwise, spends 72 k cycles on each.
+        uint32_t first = first0;
+        int nq = nq0, level = level0;
+        int ccx, ccy, ccz;
+        pcp_demorton(__ldg(P.ckey + cell) >> (3 * level0), ccx, ccy, ccz);
+        int scx = 0, scy = 0, scz = 0; // lane j: the child cell of the leaf's query j
+        int split_lo = -1;             // -1: the leaf itself; else the child that starts at the leaf's query split_lo
+        bool split_start = false;
+        auto next_sub = [&]() -> bool {
+            if constexpr (CAND <= 480) return false;
+            if (split_start) split_start = false, split_lo = 0;
+            else if (split_lo < 0) return false;
+            else split_lo += nq;
+            if (split_lo >= nq0) return false;
+            ccx = __shfl_sync(0xffffffffu, scx, split_lo), ccy = __shfl_sync(0xffffffffu, scy, split_lo),
+            ccz = __shfl_sync(0xffffffffu, scz, split_lo);
+            // the points of a leaf are in Morton order: a child's queries are consecutive
+            const unsigned grp = __ballot_sync(0xffffffffu, lane >= split_lo && lane < nq0 && scx == ccx && scy == ccy && scz == ccz);
+            const unsigned run = ~(grp >> split_lo);
+            nq = run ? __ffs(run) - 1 : 32;
+            first = first0 + (uint32_t)split_lo;
+            level = level0 - 1;
+            return true;
+        };
+        for (bool more = true; more; more = next_sub()) {
         const double h0 = P.g.h * (double)(1 << level);
         // |float - true| of a block-relative coordinate difference: operands up to 2h and 3h in magnitude, each
         // rounded once (2^-24 relative), plus the rounding of the double subtraction p - origin
@@ -719,8 +784,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
                 fill = 0;
             }
         }
-        int cx, cy, cz;
-        pcp_demorton(__ldg(P.ckey + cell) >> (3 * level), cx, cy, cz);
+        const int cx = ccx, cy = ccy, cz = ccz;
         const int dimx = ((P.g.dims[0] - 1) >> level) + 1, dimy = ((P.g.dims[1] - 1) >> level) + 1,
                   dimz = ((P.g.dims[2] - 1) >> level) + 1;
         const double ox = P.g.org[0] + (double)cx * h0, oy = P.g.org[1] + (double)cy * h0, oz = P.g.org[2] + (double)cz * h0;
@@ -756,6 +820,16 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
             if (lane == 0) P.dense_list[atomicAdd(P.dense_count, 1u)] = item;
             continue;
         }
+        if constexpr (CAND > 480) {
+            if (!P.dense_list && total > (uint32_t)CAND && level > 0 && split_lo < 0) {
+                const int sh = level - 1;
+                scx = min(max(pcp_cell_coord(myq.x, P.g.org[0], P.g.inv_h, 0), 0), P.g.dims[0] - 1) >> sh;
+                scy = min(max(pcp_cell_coord(myq.y, P.g.org[1], P.g.inv_h, 0), 0), P.g.dims[1] - 1) >> sh;
+                scz = min(max(pcp_cell_coord(myq.z, P.g.org[2], P.g.inv_h, 0), 0), P.g.dims[2] - 1) >> sh;
+                split_start = true;
+                continue; // next_sub() sets up the first child
+            }
+        }
         const bool staged = total <= (uint32_t)CAND && total >= (uint32_t)P.kk;
         PCP_FK_DBG(0, 1);
         PCP_FK_DBG(1, staged ? 1 : 0);
@@ -764,7 +838,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
         PCP_FK_DBG(4, total > (uint32_t)CAND);
         PCP_FK_DBG(8, total > (uint32_t)CAND ? nwant : 0);
         PCP_FK_DBG(9, total < (uint32_t)P.kk ? nwant : 0);
-        unsigned okmask = 0;
+        unsigned okmask = 0, rrmask = 0; // settled; left to knn_rerank_kernel
         // lane j: upper bound of query j's k-th squared distance (+inf: none; -1: none, block too dense to stage)
         // (PCP_FAR_HINT: no bound, but a level to start from -- the block of this leaf's level holds too many points
         // to stage, so the level below it is the first worth trying; or too few, so the level above it is)
@@ -851,7 +925,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
                 }
                 float dku;
                 const int st = pcp_fd_search<GS, CAP, CAND, DEFER>((int)total, S, lane, active, nbr_base, nbr_off, nbr_stride, P.kk,
-                                                                   qfx, qfy, qfz, top0, g2, e1, dku);
+                                                                   qfx, qfy, qfz, top0, g2, e1, dku, P.rr, first + (uint32_t)sj);
                 if constexpr (DEFER) {
                     if (active && st != PCP_FD_OK && (lane & (GS - 1)) == 0) nbr_base[nbr_off] = 0xffffffffu;
                 }
@@ -865,6 +939,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
                         PCP_FK_DBG(6, sg == PCP_FD_BEYOND);
                         PCP_FK_DBG(7, sg == PCP_FD_AMBIG);
                         if (sg == PCP_FD_OK) okmask |= 1u << jg;
+                        if (sg == PCP_FD_RERANK) rrmask |= 1u << jg;
                         if ((sg == PCP_FD_AMBIG || sg == PCP_FD_OK) && lane == jg) myU = dg * 1.000001f;
                     }
                 }
@@ -881,10 +956,16 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
             fill += nwant;
         }
         {
-            const unsigned fm = want & ~okmask;
+            const unsigned fm = want & ~okmask & ~rrmask;
             if (fm) {
                 uint32_t basei = 0;
-                if (lane == 0) basei = atomicAdd(P.fail_count, (uint32_t)__popc(fm));
+                // (a record for the third pass if one of the open queries has a bound: see knn_wide.cuh)
+                const unsigned bounded = __ballot_sync(0xffffffffu, myU >= 0.f && myU < 3.0e38f) & fm;
+                if (lane == 0) {
+                    basei = atomicAdd(P.fail_count, (uint32_t)__popc(fm));
+                    if (P.wide_list && bounded)
+                        P.wide_list[atomicAdd(P.wide_count, 1u)] = make_uint2(basei, (uint32_t)__popc(fm) | ((uint32_t)level << 8));
+                }
                 basei = __shfl_sync(0xffffffffu, basei, 0);
                 if ((fm >> lane) & 1u) {
                     const uint32_t at = basei + __popc(fm & ((1u << lane) - 1u));
@@ -893,6 +974,72 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, pcp_fd_min_blocks(CA
                 }
             }
         }
+        } // sub-items
     }
     if constexpr (!DEFER) pcp_fk_flush<Smem, false>(P, S, lane);
+}
+
+
+// ---- exact re-rank of the lists the FP32 search could not order ------------------------------------------------
+// One warp per entry: squared distances in double from the records, rank by (d2, original index) ascending -- the far
+// kernel's rule, the order of the reference's result set -- and the row is written.  The exact k-th distance then has
+// to clear the same thresholds as in pcp_fd_search (the upper edge of bucket b*, beyond which candidates were left
+// out of the list, and the certified radius); a query that does not joins the far list with its bound.
+template <int CAP>
+static __global__ void __launch_bounds__(128) knn_rerank_kernel(pcp_fknn_params P)
+{
+    constexpr int SL = CAP / 32;
+    const int lane = threadIdx.x & 31;
+    const uint32_t n = min(*P.rr.count, P.rr.cap);
+    for (uint32_t w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w < n; w += gridDim.x * (blockDim.x >> 5)) {
+        const uint32_t* ent = P.rr.list + (size_t)w * (CAP + PCP_RR_HEAD);
+        const uint32_t qpos = ent[0], m = ent[1];
+        const float edge = __uint_as_float(ent[2]), amb2 = __uint_as_float(ent[3]), g2 = __uint_as_float(ent[4]),
+                    delta = __uint_as_float(ent[5]);
+        const pcp_rec q = pcp_load_rec(P.rec, qpos);
+        double d2s[SL];
+        int ids[SL], rank[SL];
+        uint32_t ps[SL];
+#pragma unroll
+        for (int s = 0; s < SL; s++) {
+            const uint32_t e = s * 32 + lane;
+            d2s[s] = DBL_MAX, ids[s] = 0x7fffffff, ps[s] = 0, rank[s] = 0;
+            if (e < m) {
+                ps[s] = ent[PCP_RR_HEAD + e];
+                const pcp_rec r = pcp_load_rec(P.rec, ps[s]);
+                d2s[s] = pcp_dist2(q.x, q.y, q.z, r.x, r.y, r.z);
+                ids[s] = (int)r.idx;
+            }
+        }
+#pragma unroll
+        for (int s2 = 0; s2 < SL; s2++) {
+            const int mt = min(32, (int)m - 32 * s2);
+#pragma unroll 1
+            for (int t = 0; t < mt; t++) {
+                const double dj = __shfl_sync(0xffffffffu, d2s[s2], t);
+                const int ij = __shfl_sync(0xffffffffu, ids[s2], t);
+#pragma unroll
+                for (int s = 0; s < SL; s++) rank[s] += (dj < d2s[s] || (dj == d2s[s] && ij < ids[s])) ? 1 : 0;
+            }
+        }
+        double dk = -1.0;
+        uint32_t* row = P.nbr_out + (size_t)qpos * P.k;
+#pragma unroll
+        for (int s = 0; s < SL; s++)
+            if ((uint32_t)(s * 32 + lane) < m && rank[s] < P.kk) {
+                row[rank[s]] = ps[s];
+                if (rank[s] == P.kk - 1) dk = d2s[s];
+            }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) dk = fmax(dk, __shfl_xor_sync(0xffffffffu, dk, o));
+        const float dkl = dk < 0.0 ? -1.0f : __double2float_ru(dk);
+        const bool ok = dkl >= 0.0f && !(edge - dkl <= amb2) && dkl + amb2 < g2;
+        __syncwarp();
+        if (!ok && lane == 0) {
+            row[0] = 0xffffffffu; // not settled: the far kernel writes the row whole
+            const uint32_t at = atomicAdd(P.fail_count, 1u);
+            P.fail_list[at] = qpos;
+            P.fail_u[at] = ((dkl >= 0.0f ? dkl : edge) + delta) * 1.000001f;
+        }
+    }
 }

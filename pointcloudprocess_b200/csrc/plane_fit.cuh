@@ -14,19 +14,18 @@ struct pcp_plane {
     double l1, l2, l3;
 };
 
+// OpenCV's scaled hypot (a > b: a * sqrt(1 + (b/a)^2); else b > 0: b * sqrt(1 + (a/b)^2); else 0), with the larger
+// and the smaller operand chosen by selects: the two sides of the branch are the same arithmetic, and a warp whose
+// lanes disagree on a > b paid for the division and the square root twice.
 __device__ __forceinline__ double pcp_cv_hypot(double a, double b)
 {
     a = fabs(a);
     b = fabs(b);
-    if (a > b) {
-        b = b / a;
-        return a * sqrt(1.0 + b * b);
-    }
-    if (b > 0) {
-        a = a / b;
-        return b * sqrt(1.0 + a * a);
-    }
-    return 0.0;
+    const bool ab = a > b;
+    const double big = ab ? a : b, small = ab ? b : a;
+    const double r = small / big;
+    const double v = big * sqrt(1.0 + r * r);
+    return big > 0 ? v : 0.0;
 }
 
 #define PCP_ROT(v0, v1)                                                                                      \
@@ -69,31 +68,27 @@ static __device__ __noinline__ void pcp_jacobi3(double s00, double s01, double s
         s = p / s;
         t = (p / t) * p;
         if (y < 0) s = -s, t = -t;
-        if (pair == 0) {
-            a01 = 0;
-            w0 -= t;
-            w1 += t;
-            PCP_ROT(a02, a12); // i = 2 > l
-            PCP_ROT(v00, v10);
-            PCP_ROT(v01, v11);
-            PCP_ROT(v02, v12);
-        } else if (pair == 1) {
-            a02 = 0;
-            w0 -= t;
-            w2 += t;
-            PCP_ROT(a01, a12); // k < i = 1 < l
-            PCP_ROT(v00, v20);
-            PCP_ROT(v01, v21);
-            PCP_ROT(v02, v22);
-        } else {
-            a12 = 0;
-            w1 -= t;
-            w2 += t;
-            PCP_ROT(a01, a02); // i = 0 < k
-            PCP_ROT(v10, v20);
-            PCP_ROT(v11, v21);
-            PCP_ROT(v12, v22);
-        }
+        // the rotation of rows/columns (k, l) = (0,1) (0,2) (1,2), operands chosen by selects instead of three
+        // copies of the same 26 operations under a three-way branch (the lanes of a warp rarely agree on the pivot)
+        const bool p0 = pair == 0, p2 = pair == 2;
+        const double nwk = wk - t, nwl = wl + t;
+        w0 = p2 ? w0 : nwk;
+        w1 = p0 ? nwl : (p2 ? nwk : w1);
+        w2 = p0 ? w2 : nwl;
+        double ra = p0 ? a02 : a01; // pair 0: (a02, a12), i = 2 > l; pair 1: (a01, a12), k < i = 1 < l;
+        double rb = p2 ? a02 : a12; // pair 2: (a01, a02), i = 0 < k
+        PCP_ROT(ra, rb);
+        a01 = p0 ? 0.0 : ra;
+        a02 = p0 ? ra : (p2 ? rb : 0.0);
+        a12 = p2 ? 0.0 : rb;
+        double k0 = p2 ? v10 : v00, k1 = p2 ? v11 : v01, k2 = p2 ? v12 : v02; // row k of V
+        double l0 = p0 ? v10 : v20, l1 = p0 ? v11 : v21, l2 = p0 ? v12 : v22; // row l of V
+        PCP_ROT(k0, l0);
+        PCP_ROT(k1, l1);
+        PCP_ROT(k2, l2);
+        v00 = p2 ? v00 : k0, v01 = p2 ? v01 : k1, v02 = p2 ? v02 : k2;
+        v10 = p0 ? l0 : (p2 ? k0 : v10), v11 = p0 ? l1 : (p2 ? k1 : v11), v12 = p0 ? l2 : (p2 ? k2 : v12);
+        v20 = p0 ? v20 : l0, v21 = p0 ? v21 : l1, v22 = p0 ? v22 : l2;
         // OpenCV refreshes indR/indC only for idx in {k, l}
         if (k == 0) indR0 = (fabs(a01) < fabs(a02)) ? 2 : 1;
         if (l == 2) indC2 = (fabs(a02) < fabs(a12)) ? 1 : 0;
