@@ -513,6 +513,47 @@ __device__ __forceinline__ uint32_t pcp_add_sign(uint32_t acc, int x)
     return r;
 }
 
+// Bitonic sort, ascending, of G x SL (key, payload) pairs held SL per lane by the G lanes of a group: element
+// i = gl SL + s.  Compare-exchange distance j < SL: inside the lane; else with lane gl ^ (j / SL), same slot.
+template <int G, int SL>
+__device__ __forceinline__ void pcp_fd_bitonic(int (&key)[SL], uint32_t (&pay)[SL], int gl)
+{
+    constexpr int N = G * SL;
+#pragma unroll
+    for (int k = 2; k <= N; k <<= 1) {
+        // direction of the run of k elements that holds element i: ascending iff (i & k) == 0
+        const bool up_lane = k >= N || ((gl * SL) & k) == 0; // (k >= SL: the same for every slot of the lane)
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j < SL) {
+#pragma unroll
+                for (int a = 0; a < SL; a++) {
+                    const int b = a ^ j;
+                    if (b > a) {
+                        const bool up = k < SL ? ((a & k) == 0) : up_lane;
+                        const bool sw = (key[a] > key[b]) == up;
+                        const int ka = key[a], kb = key[b];
+                        const uint32_t pa = pay[a], pb = pay[b];
+                        key[a] = sw ? kb : ka, key[b] = sw ? ka : kb;
+                        pay[a] = sw ? pb : pa, pay[b] = sw ? pa : pb;
+                    }
+                }
+            } else {
+                const int lj = j / SL;
+                const bool keepmin = ((gl & lj) == 0) == up_lane;
+#pragma unroll
+                for (int a = 0; a < SL; a++) {
+                    const int ok = __shfl_xor_sync(0xffffffffu, key[a], lj);
+                    const uint32_t op = __shfl_xor_sync(0xffffffffu, pay[a], lj);
+                    const int nk = keepmin ? min(key[a], ok) : max(key[a], ok); // (selects: no branch around the shuffles)
+                    pay[a] = nk != key[a] ? op : pay[a];
+                    key[a] = nk;
+                }
+            }
+        }
+    }
+}
+
 // Every group of G lanes searches the staged block for its own query.  dku: upper bound of the k-th squared
 // distance (valid for OK and AMBIG).
 // The kk nearest go to nbr_base[nbr_off + rank * nbr_stride] (a column of the parked lists, or the query's row in
@@ -640,33 +681,73 @@ __device__ __forceinline__ int pcp_fd_search(int T, const pcp_fd_smem<CAP, G, CA
     const float amb2 = 2.0f * delta;
     bool ambig = false;
     float dkl = -1.0f;
-#pragma unroll 1 // code size: the body holds a loop of its own, and the kernel has to stay inside the instruction cache
-    for (int s = 0; s < SL; s++) {
-        const int e = s * G + gl;
-        if (live && e < (int)m) {
-            const float d = ld2[e];
-            const int b = pcp_fd_bucket(d, key0);
-            const uint32_t lo = b ? hist[b - 1] : 0u, hi = hist[b];
-            // bucket edges: an entry this close to one may belong to the other side
-            if (b > 0 && d - pcp_fk_edge(b - 1, key0) <= amb2 && lo > 0) ambig = true;
-            if (b < bstar && pcp_fk_edge(b, key0) - d <= amb2) ambig = true;
-            // rank = entries of the earlier buckets + smaller entries of this one; `near` = entries within the error
-            // bound of d, the entry itself included.  Counted on the bit patterns (non-negative floats order like
-            // their bits; a difference of two such patterns, or of |x|'s and amb2's, cannot overflow): the sign bit
-            // of the difference is the increment, two instructions per count instead of compare + select + move.
-            const int dbits = __float_as_int(d), abits = __float_as_int(amb2) + 1;
-            uint32_t less = 0, near = 0;
-            const float* pj = ld2 + lo;
-#pragma unroll 1 // a bucket holds a handful of entries: unrolled by 8 the remainder code is what runs
-            for (const float* const pe = ld2 + hi; pj != pe; pj++) {
-                const float dj = *pj;
-                less = pcp_add_sign(less, __float_as_int(dj) - dbits);            // dj < d
-                near = pcp_add_sign(near, __float_as_int(fabsf(dj - d)) - abits); // |dj - d| <= amb2
+    if constexpr (CAP <= 64) {
+        // The list, G lanes x SL entries (lane gl: entries gl SL .. gl SL + SL - 1, empty ones at +inf), sorted by a
+        // bitonic network on the bit patterns of d2 (non-negative floats order like their bits) with the candidate
+        // as payload: strides below SL inside the lane, the others by shuffle.  After it the entry's place IS its
+        // rank, and the order is the exact one iff every neighbouring pair up to (kk-1, kk) lies farther apart than
+        // the error bound: then no pair at all up to rank kk does, and everything behind rank kk lies behind the
+        // k-th.  (Before: every entry counted the smaller and the near ones of its bucket -- twice the instructions,
+        // and pairs behind rank kk counted as ambiguous.)
+        int key[SL];
+        uint32_t pay[SL];
+        {
+            const int4* kp = reinterpret_cast<const int4*>(ld2 + gl * SL);
+            const uint2* pp = reinterpret_cast<const uint2*>(lpos + gl * SL);
+#pragma unroll
+            for (int v = 0; v < SL / 4; v++) {
+                const int4 kv = kp[v];
+                const uint2 pv = pp[v];
+                key[4 * v + 0] = kv.x, key[4 * v + 1] = kv.y, key[4 * v + 2] = kv.z, key[4 * v + 3] = kv.w;
+                pay[4 * v + 0] = pv.x & 0xffffu, pay[4 * v + 1] = pv.x >> 16, pay[4 * v + 2] = pv.y & 0xffffu, pay[4 * v + 3] = pv.y >> 16;
             }
-            const uint32_t r = lo + less;
-            if (near > 1u) ambig = true;
-            if (r < (uint32_t)kk) nbr_base[nbr_off + r * (uint32_t)nbr_stride] = S.pos_at(lpos[e]);
-            if (r == (uint32_t)kk - 1u) dkl = d;
+#pragma unroll
+            for (int t = 0; t < SL; t++)
+                if (!live || gl * SL + t >= (int)m) key[t] = 0x7f800000, pay[t] = 0;
+        }
+        pcp_fd_bitonic<G, SL>(key, pay, gl);
+        // neighbouring pairs: the next entry is the next slot, or the next lane's first
+        const int nextlane = __shfl_down_sync(0xffffffffu, key[0], 1, G);
+#pragma unroll
+        for (int t = 0; t < SL; t++) {
+            const int r = gl * SL + t;
+            const int nk = t + 1 < SL ? key[t + 1] : (gl == G - 1 ? 0x7f800000 : nextlane);
+            if (r < kk) {
+                if (__int_as_float(nk) - __int_as_float(key[t]) <= amb2) ambig = true;
+                if (live) nbr_base[nbr_off + (uint32_t)r * (uint32_t)nbr_stride] = S.pos_at(pay[t]);
+                if (r == kk - 1) dkl = __int_as_float(key[t]);
+            }
+        }
+        if (!live) dkl = -1.0f, ambig = false;
+    } else {
+#pragma unroll 1 // code size: the body holds a loop of its own, and the kernel has to stay inside the instruction cache
+        for (int s = 0; s < SL; s++) {
+            const int e = s * G + gl;
+            if (live && e < (int)m) {
+                const float d = ld2[e];
+                const int b = pcp_fd_bucket(d, key0);
+                const uint32_t lo = b ? hist[b - 1] : 0u, hi = hist[b];
+                // bucket edges: an entry this close to one may belong to the other side
+                if (b > 0 && d - pcp_fk_edge(b - 1, key0) <= amb2 && lo > 0) ambig = true;
+                if (b < bstar && pcp_fk_edge(b, key0) - d <= amb2) ambig = true;
+                // rank = entries of the earlier buckets + smaller entries of this one; `near` = entries within the error
+                // bound of d, the entry itself included.  Counted on the bit patterns (non-negative floats order like
+                // their bits; a difference of two such patterns, or of |x|'s and amb2's, cannot overflow): the sign bit
+                // of the difference is the increment, two instructions per count instead of compare + select + move.
+                const int dbits = __float_as_int(d), abits = __float_as_int(amb2) + 1;
+                uint32_t less = 0, near = 0;
+                const float* pj = ld2 + lo;
+#pragma unroll 1 // a bucket holds a handful of entries: unrolled by 8 the remainder code is what runs
+                for (const float* const pe = ld2 + hi; pj != pe; pj++) {
+                    const float dj = *pj;
+                    less = pcp_add_sign(less, __float_as_int(dj) - dbits);            // dj < d
+                    near = pcp_add_sign(near, __float_as_int(fabsf(dj - d)) - abits); // |dj - d| <= amb2
+                }
+                const uint32_t r = lo + less;
+                if (near > 1u) ambig = true;
+                if (r < (uint32_t)kk) nbr_base[nbr_off + r * (uint32_t)nbr_stride] = S.pos_at(lpos[e]);
+                if (r == (uint32_t)kk - 1u) dkl = d;
+            }
         }
     }
 #pragma unroll

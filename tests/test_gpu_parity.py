@@ -446,7 +446,9 @@ def test_calculate_plan_parameter_rpca_mirror(ctx, orc):
 # ---- alternative code paths must agree bit for bit -----------------------------------------------------------
 def test_fused_and_single_pass_variants_equal_the_default_path(ctx):
     """PCP_FK_FUSED (plane fit inside the search kernels), PCP_FK_ONEPASS (no second dense pass), PCP_FK_NOFLAT (the
-    block staged cell by cell) and the default (deferred fit, two passes, flat staging) are the same function; PCP_RADIUS_WARP is the warp-per-query radius kernel."""
+    block staged cell by cell), PCP_FK_NOWIDE (no third pass over the box of the bounded queries), PCP_FK_NORERANK (lists
+    the FP32 search cannot order go to the far kernel instead of knn_rerank_kernel) and the default (deferred fit, three
+    passes, flat staging, re-rank) are the same function; PCP_RADIUS_WARP is the warp-per-query radius kernel."""
     import os
     import pointcloudprocess_b200 as pcp
     cloud = ctx.synth_cloud("city", 300000, seed=12)
@@ -455,7 +457,7 @@ def test_fused_and_single_pass_variants_equal_the_default_path(ctx):
     ref32 = ix.features_knn(32, want_idx=True)
     rad = ix.features_radius(0.3)
     try:
-        for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS", "PCP_FK_NOFLAT"):
+        for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS", "PCP_FK_NOFLAT", "PCP_FK_NOWIDE", "PCP_FK_NORERANK"):
             os.environ[env] = "1"
             got = ix.features_knn(20, want_idx=True)
             got32 = ix.features_knn(32, want_idx=True)
@@ -470,9 +472,29 @@ def test_fused_and_single_pass_variants_equal_the_default_path(ctx):
         assert np.array_equal(radw["counts"], rad["counts"])
         check_features_tolerance(radw["props"], radw["eig"], rad["props"], rad["eig"])
     finally:
-        for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS", "PCP_FK_NOFLAT", "PCP_RADIUS_WARP"):
+        for env in ("PCP_FK_FUSED", "PCP_FK_ONEPASS", "PCP_FK_NOFLAT", "PCP_FK_NOWIDE", "PCP_FK_NORERANK", "PCP_RADIUS_WARP"):
             os.environ.pop(env, None)
         ix.free()
+
+
+def test_rerank_and_third_pass_on_ties_and_sparse_leaves(ctx, orc):
+    """The two kernels behind the dense passes against the oracle where they have most to do: a jittered lattice (FP32
+    cannot order near-equal distances: knn_rerank_kernel), an exact lattice (ties ranked by index), and a forest plot
+    (sparse leaves beside dense ones: knn_wide_kernel) -- neighbour lists and records, k = 20 and k = 32."""
+    import pointcloudprocess_b200 as pcp
+    rng = np.random.default_rng(21)
+    lat = ctx.synth_cloud("lattice", 32768, seed=8, centred=True)
+    jit = lat.copy()
+    for f in ("x", "y", "z"):
+        jit[f] = (jit[f].astype(np.float64) + rng.uniform(-1e-6, 1e-6, len(jit))).astype(jit[f].dtype)
+    for cloud in (lat, jit, ctx.synth_cloud("forest", 200000, seed=14)):
+        for k in (20, 32):
+            ix = pcp.Index(ctx, cloud)
+            got = ix.features_knn(k, want_idx=True)
+            ix.free()
+            props, eig, lps, kidx = orc.features_knn(cloud, k, want_idx=True)
+            assert np.array_equal(got["knn_idx"], kidx)
+            assert_props_equal(got["props"], props)
 
 
 def test_knn_batched_external_queries_edge_cases(ctx, orc):
