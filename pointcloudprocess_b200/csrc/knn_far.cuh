@@ -224,6 +224,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
         }
         const int slot = fill;
         int st = PCP_FK_BEYOND;
+        int partial = 0; // attempts on a truncated cell selection (see below)
         for (; level <= P.g.top_level; level++) {
             const int lx = bx >> level, ly = by >> level, lz = bz >> level;
             const double g2 = pcp_guarantee2(P.g, level, lx, ly, lz, q.x, q.y, q.z);
@@ -373,9 +374,18 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
                 inner = pass == 0;
             }
             if (nsel > PCP_FAR_NSEL) {
-                PCP_FK_DBG(23, 1);
-                st = PCP_FK_OVERFLOW;
-                break;
+                // Still too many (a point metres above a dense surface: the corner bound's sphere cuts a disc of
+                // hundreds of cells out of it).  ANY k points bound the k-th distance: search the cells that did fit,
+                // take their exact k-th as the bound -- now the true scale of the neighbourhood, a handful of cells
+                // -- and run this level again.  Twice at most; then the streaming kernel.
+                if (partial >= 2) {
+                    PCP_FK_DBG(23, 1);
+                    st = PCP_FK_OVERFLOW;
+                    break;
+                }
+                partial++;
+                nsel = PCP_FAR_NSEL;
+                inner = true;
             }
             const uint32_t T = prefix_counts(nsel);
             PCP_FK_DBG(17, inner);
