@@ -18,18 +18,24 @@
 #define PCP_FAR_NSEL 128   // selected base cells per attempt (256, with a 128-entry cell cache to stay at 4 blocks per SM: 1.4 k instead of 7 k queries overflow to the streaming kernel, but the kernel itself 11.6 -> 12.6 ms)
 #define PCP_FAR_CCACHE 256 // cells whose (nearest-corner distance, first point, count) are kept between passes
 
+// The cell cache and the staged candidates are never alive together (the cache carries the corner distances from the
+// bound pass to the selection; staging starts after it), and they lie side by side -- [ccache | the base struct's
+// candidate array] -- so the far kernel stages PCP_FAR_CAND = CCACHE + PCP_FK_CAND candidates at a time out of the
+// shared memory of 256: a selection of 256..512 points (the mean is 283) is staged once, not once per pass.
+#define PCP_FAR_CAND (PCP_FAR_CCACHE + PCP_FK_CAND)
 template <int CAP> struct pcp_far_smem : pcp_fk_smem<CAP, 32> {
     uint32_t* selpre;   // [NSEL]  exclusive prefix of the selected cells' point counts (0xffffffff beyond)
     uint32_t* selstart; // [NSEL]  first point of the selected cell
-    float4* ccache;     // [CCACHE] nearest-corner d2, first point, count of the block's cells (pass A -> B)
+    float4* ccache;     // [CCACHE] nearest-corner d2, first point, count of the block's cells (pass A -> B);
+                        //          later the first CCACHE of the PCP_FAR_CAND staged candidates
     static __host__ __device__ size_t bytes(int k)
     {
         return pcp_fk_smem<CAP, 32>::bytes(k) + PCP_FAR_NSEL * 8 + PCP_FAR_CCACHE * 16;
     }
-    __device__ pcp_far_smem(unsigned char* base, int k) : pcp_fk_smem<CAP, 32>(base, k)
+    __device__ pcp_far_smem(unsigned char* base, int k) : pcp_fk_smem<CAP, 32>(base + PCP_FAR_CCACHE * 16, k)
     {
-        ccache = reinterpret_cast<float4*>(base + pcp_fk_smem<CAP, 32>::bytes(k));
-        selpre = reinterpret_cast<uint32_t*>(base + pcp_fk_smem<CAP, 32>::bytes(k) + PCP_FAR_CCACHE * 16);
+        ccache = reinterpret_cast<float4*>(base);
+        selpre = reinterpret_cast<uint32_t*>(base + PCP_FAR_CCACHE * 16 + pcp_fk_smem<CAP, 32>::bytes(k));
         selstart = selpre + PCP_FAR_NSEL;
     }
 };
@@ -43,7 +49,7 @@ static __device__ __noinline__ void pcp_far_stage(const pcp_rec* __restrict__ re
 {
     __syncwarp();
 #pragma unroll 1
-    for (int part = 0; part < PCP_FK_CAND / 64 && c0 + part * 64 < T; part++) {
+    for (int part = 0; part < PCP_FAR_CAND / 64 && c0 + part * 64 < T; part++) {
         pcp_rec r[2];
         uint32_t ps[2];
 #pragma unroll
@@ -84,9 +90,9 @@ struct pcp_far_src {
     }
     template <class F> __device__ __forceinline__ void for_each(int lane, F f) const
     {
-        for (uint32_t c0 = 0; c0 < T; c0 += PCP_FK_CAND) {
+        for (uint32_t c0 = 0; c0 < T; c0 += PCP_FAR_CAND) {
             if (!resident) stage(c0, lane);
-            const int n = (int)min((uint32_t)PCP_FK_CAND, T - c0);
+            const int n = (int)min((uint32_t)PCP_FAR_CAND, T - c0);
             for (int f0 = 0; f0 < n; f0 += 32) {
                 const int i = f0 + lane;
                 const bool valid = i < n;
@@ -392,7 +398,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
             PCP_FK_DBG(12, 1);
             PCP_FK_DBG(13, T);
             PCP_FK_DBG(14, nsel);
-            pcp_far_src src{P.rec, S.cand, S.selpre, S.selstart, T, q.x, q.y, q.z, T <= PCP_FK_CAND};
+            pcp_far_src src{P.rec, S.ccache, S.selpre, S.selstart, T, q.x, q.y, q.z, T <= PCP_FAR_CAND};
             if (src.resident) src.stage(0, lane);
             double dk;
             const float top = Ueff * 1.001f;
