@@ -49,13 +49,6 @@ __global__ void __launch_bounds__(256) knn_export_kernel(const pcp_rec* __restri
     }
 }
 
-// deferred-feature rows start as "not written"
-__global__ void __launch_bounds__(256) mark_rows_kernel(uint32_t* __restrict__ rows, size_t n, int k)
-{
-    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-    if (i < n) rows[i * (size_t)k] = 0xffffffffu;
-}
-
 template <int KPL> int launch_wknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint32_t expected)
 {
     int blocks = ctx->sm_count * 4;
@@ -249,8 +242,7 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
                 void* q = nullptr;
                 PCP_TRY(pcp_scratch_get(ctx, nv * (size_t)k * 4, &q)); // kept by the context between calls
                 rows.p = static_cast<uint32_t*>(q);
-                mark_rows_kernel<<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(rows.p, nv, k);
-                PCP_LAUNCH_CHECK(ctx);
+                // (no pass over the rows: the dense kernels mark every row they leave without an answer)
                 P.nbr_out = rows.p;
             }
             // lists the FP32 search cannot order go to knn_rerank_kernel (about 1 % of the queries; room for 1 in 16)
