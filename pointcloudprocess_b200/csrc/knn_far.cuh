@@ -372,7 +372,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
             // entirely inside that sphere hold k points by construction, and their exact k-th distance is a much
             // tighter bound; search those, take it and run this level again.
             uint32_t nsel = 0;
-            bool inner = false;
+            bool inner = false, truncated = false;
 #pragma unroll 1
             for (int pass = 0; pass < 2; pass++) {
                 nsel = select_cells(Ueff, pass == 1, pass == 0 && U == INF); // pass A filled the cache
@@ -392,6 +392,7 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
                 partial++;
                 nsel = PCP_FAR_NSEL;
                 inner = true;
+                truncated = true;
             }
             const uint32_t T = prefix_counts(nsel);
             PCP_FK_DBG(17, inner);
@@ -401,15 +402,26 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
             pcp_far_src src{P.rec, S.ccache, S.selpre, S.selstart, T, q.x, q.y, q.z, T <= PCP_FAR_CAND};
             if (src.resident) src.stage(0, lane);
             double dk;
-            const float top = Ueff * 1.001f;
+            // (the points of a cell whose nearest corner lies inside the sphere reach a cell diagonal beyond it: the
+            // truncated selection is searched up to there, or its k-th may fall off the histogram)
+            const float rtop = sqrtf(Ueff) + 1.8f * (float)P.g.h;
+            const float top = truncated ? rtop * rtop * 1.001f : Ueff * 1.001f;
             st = pcp_fk_search<32, CAP>(src, S, P.rec, lane, true, slot, P.kk, 0.f, 0.f, 0.f, q.x, q.y, q.z, top,
                                         inner ? 0.0 : g2, e1, dk);
             if (inner) {
+#ifdef PCP_FAR_TRACE
+                if (st != PCP_FK_UNCERT && lane == 0) printf("far inner: qpos %u st %d level %d Ueff %g T %u nsel %u truncated %d dk %g\n", qpos, st, level, (double)Ueff, T, nsel, (int)truncated, dk);
+#endif
                 if (st != PCP_FK_UNCERT) {
                     st = PCP_FK_OVERFLOW;
                     break;
                 }
-                U = __double2float_ru(dk) * 1.000001f;
+                const float Unew = __double2float_ru(dk) * 1.000001f;
+                if (truncated && !(Unew < Ueff)) { // no tighter than the corner bound: nothing gained by another round
+                    st = PCP_FK_OVERFLOW;
+                    break;
+                }
+                U = Unew;
                 level--;
                 continue;
             }
@@ -430,6 +442,9 @@ static __global__ void __launch_bounds__(32 * PCP_FK_WARPS, 4) knn_far_kernel(pc
             PCP_FK_DBG(20, st == PCP_FK_UNCERT);
             PCP_FK_DBG(21, U == INF);
             PCP_FK_DBG(22, level);
+#ifdef PCP_FAR_TRACE
+            if (lane == 0) printf("far fail: qpos %u st %d level %d U %g partial %d q=(%.3f %.3f %.3f)\n", qpos, st, level, (double)U, partial, q.x, q.y, q.z);
+#endif
             if (lane == 0) A.fail_list[atomicAdd(A.fail_count, 1u)] = qpos;
         }
     }

@@ -285,19 +285,28 @@ __device__ __forceinline__ int pcp_fk_search(const Src& src, const pcp_fk_smem<C
             below = __shfl_sync(0xffffffffu, below, L);
             upto = __shfl_sync(0xffffffffu, upto, L);
         }
-        if (st == PCP_FK_OK && upto > (uint32_t)CAP) {
-            const float lo = bstar ? pcp_fk_edge(bstar - 1, key0) : 0.0f;
+        // (Up to three times: a point metres above a dense plane sees hundreds of points at distances that differ
+        // in the fourth digit -- one slice of the bucket, 0.3 % of d2, still holds more than the list.)
+        float lo = bstar ? pcp_fk_edge(bstar - 1, key0) : 0.0f;
+#pragma unroll 1
+        // (+ 4: the list takes the candidates up to edge + 3 delta -- a few more than the buckets count)
+        for (int round = 0; round < 3 && st == PCP_FK_OK && upto + 4 > (uint32_t)CAP; round++) {
             const float w = (edge - lo) * (1.0f / PCP_FK_NB), iw = 1.0f / w;
+            if (!(w > 0.0f)) break;
             __syncwarp();
             hist[lane] = 0, hist[lane + 32] = 0;
             __syncwarp();
+            uint32_t nb = 0; // candidates below the interval, counted again (round 0: the buckets before b*)
             src.for_each(gl, [&](bool valid, float x, float y, float z, uint32_t) {
                 const float dx = qfx - x, dy = qfy - y, dz = qfz - z;
                 const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, dx * dx));
-                if (valid && pcp_fk_bucket(d2, key0) == bstar)
+                if (valid && d2 < lo) nb++;
+                if (valid && d2 >= lo && d2 < edge)
                     atomicAdd(&hist[min(max((int)((d2 - lo) * iw), 0), PCP_FK_NB - 1)], 1u);
             });
             __syncwarp();
+            below = __reduce_add_sync(0xffffffffu, nb);
+            if (below >= (uint32_t)kk) break; // (cannot happen; the interval as it is holds the k-th in any case)
             const uint32_t s0 = hist[2 * lane], s1 = hist[2 * lane + 1];
             uint32_t si = s0 + s1;
 #pragma unroll
@@ -305,15 +314,18 @@ __device__ __forceinline__ int pcp_fk_search(const Src& src, const pcp_fk_smem<C
                 const uint32_t v = __shfl_up_sync(0xffffffffu, si, o);
                 if (lane >= o) si += v;
             }
-            const uint32_t need = (uint32_t)kk - below; // >= 1: the count reaches kk inside b*
+            const uint32_t need = (uint32_t)kk - below; // >= 1
             const unsigned sb = __ballot_sync(0xffffffffu, si >= need);
-            if (sb) {
-                const int SLn = __ffs(sb) - 1;
-                const uint32_t before = __shfl_sync(0xffffffffu, si - s1, SLn); // cumulative through slice 2*SLn
-                const int slice = before >= need ? 2 * SLn : 2 * SLn + 1;
-                // slice(d2) <= slice for every d2 below this value (and a little beyond: harmless)
-                edge = fminf(edge, __fmaf_rn((float)(slice + 1), w, lo) * 1.000002f);
-            }
+            if (!sb) break;
+            const int SLn = __ffs(sb) - 1;
+            const uint32_t before = __shfl_sync(0xffffffffu, si - s1, SLn); // cumulative through slice 2*SLn
+            const uint32_t through = __shfl_sync(0xffffffffu, si, SLn);     // ... through slice 2*SLn + 1
+            const int slice = before >= need ? 2 * SLn : 2 * SLn + 1;
+            upto = below + (before >= need ? before : through);
+            // slice(d2) <= slice for every d2 below the new edge (and a little beyond: harmless); slice(d2) < slice
+            // for every d2 below the new lower end
+            edge = fminf(edge, __fmaf_rn((float)(slice + 1), w, lo) * 1.000002f);
+            lo = __fmaf_rn((float)slice * 0.999998f, w, lo);
         }
     }
     const float delta = 4.0f * sqrtf(edge) * e1 + 4.0f * e1 * e1 + 1e-6f * edge;
@@ -330,7 +342,13 @@ __device__ __forceinline__ int pcp_fk_search(const Src& src, const pcp_fk_smem<C
         if (in && at < (uint32_t)CAP) lpos[at] = pos;
         m += __popc(mask);
     });
-    if (live && m > (uint32_t)CAP) st = PCP_FK_OVERFLOW, live = false;
+#ifdef PCP_FAR_TRACE
+    if constexpr (G == 32) {
+        if (live && (m > (uint32_t)CAP || m < (uint32_t)kk) && lane == 0)
+            printf("fk overflow: m %u kk %d edge %g thr %g top %g bstar %d\n", m, kk, (double)edge, (double)thr, (double)top, bstar);
+    }
+#endif
+    if (live && (m > (uint32_t)CAP || m < (uint32_t)kk)) st = PCP_FK_OVERFLOW, live = false; // (m < kk: cannot happen)
     __syncwarp();
     // ---- refine: exact squared distances, rank by (d2, original index) ----
     double d2s[SL];
