@@ -139,8 +139,25 @@ int launch_far(pcp_ctx* ctx, const pcp_fknn_params& P, const pcp_far_args& A)
     return launch_far_t<160>(ctx, P, A);
 }
 
+// a handful of queries: a block of 8 warps per query (the longest query is the kernel's time)
+#define PCP_BKNN_W 8
+#define PCP_BKNN_MAXQ 512
+template <int KPL> int launch_bknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint32_t expected)
+{
+    const size_t smem = (size_t)(PCP_BKNN_W - 1) * P.kk * sizeof(pcp_bent);
+    int blocks = (int)std::min<uint32_t>(std::max<uint32_t>(expected, 1u), (uint32_t)ctx->sm_count * 2u);
+    knn_block_kernel<KPL, PCP_BKNN_W><<<blocks, 32 * PCP_BKNN_W, smem, ctx->stream>>>(P);
+    PCP_LAUNCH_CHECK(ctx);
+    return PCP_OK;
+}
+
 int run_wknn(pcp_ctx* ctx, const pcp_wknn_params& P, uint32_t expected)
 {
+    if (expected && expected <= PCP_BKNN_MAXQ && !P.dbg && !getenv("PCP_KNN_NOBLOCK")) {
+        if (P.k <= 32) return launch_bknn<1>(ctx, P, expected);
+        if (P.k <= 64) return launch_bknn<2>(ctx, P, expected);
+        if (P.k <= 128) return launch_bknn<4>(ctx, P, expected);
+    }
     if (P.k <= 32) return launch_wknn<1>(ctx, P, expected);
     if (P.k <= 64) return launch_wknn<2>(ctx, P, expected);
     if (P.k <= 128) return launch_wknn<4>(ctx, P, expected);

@@ -206,6 +206,161 @@ template <int KPL> static __global__ void __launch_bounds__(128) knn_warp_kernel
     }
 }
 
+// ---- the same search, one BLOCK per query ----------------------------------------------------------------------
+// For a handful of queries (what the far kernel could not settle: a point metres above a dense surface, whose block
+// holds 10^5 points) the warp kernel's time is the time of its longest query, and a single warp keeps only 4 KB of
+// loads in flight.  Here the W warps of a block share one query: every warp scans its W-th of each of the 27 cell
+// ranges into a list of its own; the lists meet in shared memory and warp 0 merges them (the k nearest of a union are
+// among the k nearest of its parts), decides whether the level certifies, and tells the others.  Same order
+// (d2, original index), same levels, same answer as knn_warp_kernel.
+struct pcp_bent {
+    double d;
+    int idx;
+    uint32_t pos;
+};
+
+template <int KPL, int W> static __global__ void __launch_bounds__(32 * W) knn_block_kernel(pcp_wknn_params P)
+{
+    extern __shared__ __align__(16) unsigned char bsm_raw[];
+    pcp_bent* const part = reinterpret_cast<pcp_bent*>(bsm_raw); // [W - 1][kk]
+    __shared__ uint32_t s_qi;
+    __shared__ int s_done;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t nq = P.qcount_dev ? *P.qcount_dev : P.qcount;
+    while (true) {
+        __syncthreads();
+        if (threadIdx.x == 0) s_qi = atomicAdd(P.work_counter, 1u);
+        __syncthreads();
+        const uint32_t qi = s_qi;
+        if (qi >= nq) return;
+        double qx, qy, qz;
+        int level = 0;
+        const uint32_t row = (!P.qlist && P.qsel) ? __ldg(P.qsel + qi) : qi;
+        if (P.qlist) {
+            const uint32_t code = __ldg(P.qlist + qi);
+            level = (code & 0x80000000u) ? 1 : 0;
+            const pcp_rec q = pcp_load_rec(P.rec, code & 0x7fffffffu);
+            qx = q.x, qy = q.y, qz = q.z;
+        } else {
+            const double* qp = reinterpret_cast<const double*>(P.qpts + (size_t)row * P.qstride);
+            qx = qp[0], qy = qp[1], qz = qp[2];
+        }
+        pcp_wlist<KPL> L;
+        int found = 0;
+        const bool finite_q = isfinite(qx) && isfinite(qy) && isfinite(qz);
+        if (finite_q && P.kk > 0) {
+            const int bx = min(max(pcp_cell_coord(qx, P.g.org[0], P.g.inv_h, 0), 0), P.g.dims[0] - 1);
+            const int by = min(max(pcp_cell_coord(qy, P.g.org[1], P.g.inv_h, 0), 0), P.g.dims[1] - 1);
+            const int bz = min(max(pcp_cell_coord(qz, P.g.org[2], P.g.inv_h, 0), 0), P.g.dims[2] - 1);
+            if (level > P.g.top_level) level = P.g.top_level;
+            double kd = DBL_MAX;
+            int ki = 0x7fffffff;
+            // candidate (xd, xi, xp) of lane src against the list
+            auto offer = [&](unsigned qual, double d2, int ci, uint32_t pos) {
+                while (qual) {
+                    const int src = __ffs(qual) - 1;
+                    qual &= qual - 1;
+                    const double xd = __shfl_sync(0xffffffffu, d2, src);
+                    const int xi = __shfl_sync(0xffffffffu, ci, src);
+                    const uint32_t xp = __shfl_sync(0xffffffffu, pos, src);
+                    if (!pcp_less(xd, xi, kd, ki)) continue; // threshold moved since the ballot
+                    pcp_wlist_insert<KPL>(L, lane, xd, xi, xp);
+                    pcp_wlist_kth<KPL>(L, P.kk, kd, ki);
+                }
+            };
+            for (;; level++) {
+#pragma unroll
+                for (int s = 0; s < KPL; s++) L.d[s] = DBL_MAX, L.idx[s] = 0x7fffffff, L.pos[s] = 0xffffffffu;
+                kd = DBL_MAX, ki = 0x7fffffff;
+                const int cx = bx >> level, cy = by >> level, cz = bz >> level;
+                uint32_t lo = 0, hi = 0;
+                if (lane < 27) {
+                    int dx, dy, dz;
+                    pcp_nb_offset(lane, dx, dy, dz);
+                    const int nx = cx + dx, ny = cy + dy, nz = cz + dz;
+                    const int mx = (P.g.dims[0] - 1) >> level, my = (P.g.dims[1] - 1) >> level,
+                              mz = (P.g.dims[2] - 1) >> level;
+                    if (nx >= 0 && ny >= 0 && nz >= 0 && nx <= mx && ny <= my && nz <= mz) {
+                        if (P.htab && level == 0) {
+                            uint32_t cs = 0, cc = 0;
+                            if (pcp_hash_find(P.htab, P.hmask, pcp_morton(nx, ny, nz), cs, cc)) lo = cs, hi = cs + cc;
+                        } else if (P.ltab && level < PCP_HLEVELS) {
+                            uint32_t a = 0, cn = 0;
+                            if (pcp_hash_find(P.ltab, P.lmask, PCP_LKEY(level, pcp_morton(nx, ny, nz)), a, cn))
+                                lo = __ldg(P.cstart + a), hi = __ldg(P.cstart + a + cn);
+                        } else {
+                            pcp_level_range(P.ckey, P.cstart, P.ncell, level, nx, ny, nz, lo, hi);
+                        }
+                    }
+                }
+                for (int nb = 0; nb < 27; nb++) {
+                    const uint32_t s0 = __shfl_sync(0xffffffffu, lo, nb);
+                    const uint32_t s1 = __shfl_sync(0xffffffffu, hi, nb);
+                    // this warp's part of the range, in chunks of 4 x 32 points in flight
+                    const unsigned long long len = s1 - s0;
+                    const uint32_t a = s0 + (uint32_t)(len * (unsigned)warp / W), b = s0 + (uint32_t)(len * (unsigned)(warp + 1) / W);
+                    constexpr int WU = 4;
+                    for (uint32_t c0 = a; c0 < b; c0 += 32 * WU) {
+                        pcp_rec r[WU];
+#pragma unroll
+                        for (int u = 0; u < WU; u++) {
+                            const uint32_t t = c0 + 32 * u + lane;
+                            if (t < b) r[u] = pcp_load_rec(P.rec, t);
+                        }
+#pragma unroll
+                        for (int u = 0; u < WU; u++) {
+                            const uint32_t t0 = c0 + 32 * u;
+                            if (t0 >= b) break;
+                            const uint32_t t = t0 + lane;
+                            double d2 = DBL_MAX;
+                            int ci = 0x7fffffff;
+                            if (t < b) {
+                                d2 = pcp_dist2(qx, qy, qz, r[u].x, r[u].y, r[u].z);
+                                ci = (int)r[u].idx;
+                            }
+                            offer(__ballot_sync(0xffffffffu, t < b && pcp_less(d2, ci, kd, ki)), d2, ci, t);
+                        }
+                    }
+                }
+                // the lists of warps 1 .. W-1 go to warp 0
+                if (warp > 0) {
+#pragma unroll
+                    for (int s = 0; s < KPL; s++) {
+                        const int e = s * 32 + lane;
+                        if (e < P.kk) part[(size_t)(warp - 1) * P.kk + e] = pcp_bent{L.d[s], L.idx[s], L.pos[s]};
+                    }
+                }
+                __syncthreads();
+                if (warp == 0) {
+                    for (int w = 0; w < W - 1; w++)
+                        for (int e0 = 0; e0 < P.kk; e0 += 32) {
+                            const int e = e0 + lane;
+                            pcp_bent x{DBL_MAX, 0x7fffffff, 0xffffffffu};
+                            if (e < P.kk) x = part[(size_t)w * P.kk + e];
+                            offer(__ballot_sync(0xffffffffu, x.d < DBL_MAX && pcp_less(x.d, x.idx, kd, ki)), x.d, x.idx, x.pos);
+                        }
+                    const double g2 = pcp_guarantee2(P.g, level, cx, cy, cz, qx, qy, qz);
+                    if (lane == 0) s_done = (level >= P.g.top_level || (kd < DBL_MAX && kd < g2)) ? 1 : 0;
+                }
+                __syncthreads();
+                if (s_done) break;
+            }
+            found = P.kk;
+        }
+        if (warp == 0) {
+#pragma unroll
+            for (int s = 0; s < KPL; s++) {
+                const int e = s * 32 + lane;
+                if (e < P.k) {
+                    const bool have = e < found && L.d[s] < DBL_MAX;
+                    P.out_pos[(size_t)row * P.k + e] = have ? L.pos[s] : 0xffffffffu;
+                    if (P.out_d2) P.out_d2[(size_t)row * P.k + e] = have ? L.d[s] : __longlong_as_double(0x7ff0000000000000ll);
+                }
+            }
+        }
+    }
+}
+
 // thread per fall-back query: neighbour positions -> plane fit -> LAS_POINT_PROPERTY
 static __global__ void __launch_bounds__(128) features_from_list_kernel(const pcp_rec* __restrict__ rec,
                                                                  const uint32_t* __restrict__ qlist,

@@ -477,6 +477,33 @@ def test_fused_and_single_pass_variants_equal_the_default_path(ctx):
         ix.free()
 
 
+def test_block_per_query_streaming_equals_warp_per_query(ctx, orc):
+    """A handful of streaming queries take knn_block_kernel (8 warps share a query, lists merged by warp 0); PCP_KNN_NOBLOCK
+    keeps them on knn_warp_kernel.  Same lists and distances, and both equal the oracle's: queries inside, far outside
+    and metres above the cloud, k = 20, 50, 100."""
+    import os
+    import pointcloudprocess_b200 as pcp
+    cloud = ctx.synth_cloud("city", 400000, seed=17, centred=True)
+    rng = np.random.default_rng(3)
+    xyz = np.stack([cloud["x"], cloud["y"], cloud["z"]], 1)
+    q = np.concatenate([xyz[rng.integers(0, len(cloud), 24)] + rng.normal(0, 0.3, (24, 3)),
+                        xyz[rng.integers(0, len(cloud), 8)] + np.array([0.0, 0.0, 25.0]),
+                        np.array([[1e4, -1e4, 50.0], [-500.0, 3.0, 2.0]])])
+    ix = pcp.Index(ctx, cloud)
+    try:
+        for k in (20, 50, 100):
+            a = ix.knn(q, k)                       # < 64 queries: the streaming path, block per query
+            os.environ["PCP_KNN_NOBLOCK"] = "1"
+            b = ix.knn(q, k)
+            del os.environ["PCP_KNN_NOBLOCK"]
+            ridx, rd2, rfound = orc.KdTree(cloud).knn(q, k)
+            for got in (a, b):
+                assert np.array_equal(got[0], ridx) and np.array_equal(got[1], rd2) and np.array_equal(got[2], rfound)
+    finally:
+        os.environ.pop("PCP_KNN_NOBLOCK", None)
+        ix.free()
+
+
 def test_rerank_and_third_pass_on_ties_and_sparse_leaves(ctx, orc):
     """The two kernels behind the dense passes against the oracle where they have most to do: a jittered lattice (FP32
     cannot order near-equal distances: knn_rerank_kernel), an exact lattice (ties ranked by index), and a forest plot
