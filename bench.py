@@ -547,7 +547,7 @@ def run_gpu(args):
                                     "k = 20 search examines ~270 candidates per query from shared memory)",
                             "issue_slots_busy_pct": issue, "source": cap_note},
                 "stage_knn": {"ms": knn_ms, "achieved": algo / (knn_ms * 1e-3) / 1e9, "frac": algo / (knn_ms * 1e-3) / 1e9 / peak,
-                              "what": "all knn.* kernels (dense, second dense pass, far, plane fits, streaming fallback)"},
+                              "what": "all knn.* kernels (three dense passes, re-rank, far, plane fits, streaming fallback)"},
                 "step": {"ms": step_ms_rank, "achieved": algo / (step_ms_rank * 1e-3) / 1e9,
                          "frac": algo / (step_ms_rank * 1e-3) / 1e9 / peak}}
     elif cfg["op"] != "pipeline":
