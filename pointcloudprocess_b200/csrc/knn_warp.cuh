@@ -410,7 +410,7 @@ static __global__ void __launch_bounds__(128) features_from_list_kernel(const pc
             s12 += Y * Z;
             s22 += Z * Z;
         }
-        pcp_plane_from_scatter(s00, s01, s02, s11, s12, s22, XAve, YAve, ZAve, pl);
+        pcp_plane_from_scatter<true>(s00, s01, s02, s11, s12, s22, XAve, YAve, ZAve, pl);
     }
     pcp_store_props(props, jq, fitted, pl);
     pcp_store_extra(eig3, lps3, jq, fitted, pl);

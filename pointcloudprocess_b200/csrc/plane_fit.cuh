@@ -36,8 +36,11 @@ __device__ __forceinline__ double pcp_cv_hypot(double a, double b)
     }
 
 // S = [[s00 s01 s02],[. s11 s12],[. . s22]].  Outputs W (descending) and rows of V.
-static __device__ __noinline__ void pcp_jacobi3(double s00, double s01, double s02, double s11, double s12, double s22,
-                                         double W[3], double V[9])
+// (INLINE: the plane-fit kernel takes it inline -- the eigenvalues and vectors stay in registers; the kernels whose
+// code has to stay small call the copy below)
+template <bool INLINE = true>
+__device__ __forceinline__ void pcp_jacobi3_impl(double s00, double s01, double s02, double s11, double s12, double s22,
+                                                 double W[3], double V[9])
 {
     const double eps = DBL_EPSILON;
     double a01 = s01, a02 = s02, a12 = s12;
@@ -127,14 +130,21 @@ static __device__ __noinline__ void pcp_jacobi3(double s00, double s01, double s
     V[0] = v00, V[1] = v01, V[2] = v02, V[3] = v10, V[4] = v11, V[5] = v12, V[6] = v20, V[7] = v21, V[8] = v22;
 }
 #undef PCP_ROT
+static __device__ __noinline__ void pcp_jacobi3(double s00, double s01, double s02, double s11, double s12, double s22,
+                                                double W[3], double V[9])
+{
+    pcp_jacobi3_impl(s00, s01, s02, s11, s12, s22, W, V);
+}
 
 // Everything after cvMatMul in calculate_plan_parameter_h_points (:165-199).
+template <bool INLINE = false>
 __device__ __forceinline__ void pcp_plane_from_scatter(double s00, double s01, double s02, double s11, double s12,
                                                        double s22, double XAve, double YAve, double ZAve,
                                                        pcp_plane& out)
 {
     double W[3], V[9];
-    pcp_jacobi3(s00, s01, s02, s11, s12, s22, W, V);
+    if constexpr (INLINE) pcp_jacobi3_impl(s00, s01, s02, s11, s12, s22, W, V);
+    else pcp_jacobi3(s00, s01, s02, s11, s12, s22, W, V);
     double valuemin = W[0], valuemax = W[0];
     int nummin = 0, nummax = 0;
 #pragma unroll
