@@ -206,6 +206,83 @@ template <int KPL> static __global__ void __launch_bounds__(128) knn_warp_kernel
     }
 }
 
+// ---- the plane fit of the deferred rows in two kernels ----------------------------------------------------------
+// The fit is two different programs: gathering twenty records and summing them in order (loads, little state), and
+// the Jacobi iteration (sixty live doubles, no loads).  In one kernel the first waits on memory at the occupancy the
+// second's registers allow, and the FP64 pipe idles half the time (54 % busy).  Split, the moments pass runs at
+// full occupancy and hands nine doubles per row to a pass that only computes.  mom: [10][rows] (column-major, so both
+// passes are coalesced): s00 s01 s02 s11 s12 s22 XAve YAve ZAve, and N << 32 | original index (N = -1: no row).
+static __global__ void __launch_bounds__(256) moments_from_rows_kernel(const pcp_rec* __restrict__ rec,
+                                                                       const uint32_t* __restrict__ nbr_pos, int k, int kk,
+                                                                       uint32_t row0, uint32_t nrows, double* __restrict__ mom,
+                                                                       int32_t* knn_idx, float* kth_d2)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nrows) return;
+    const uint32_t qi = row0 + t;
+    const uint32_t* row = nbr_pos + (size_t)qi * k;
+    long long tag = -1ll << 32;
+    if (row[0] != 0xffffffffu) {
+        const size_t jq = (size_t)rec[qi].idx;
+        int N = 0;
+        for (int e = 0; e < kk; e++)
+            if (row[e] != 0xffffffffu) N++;
+        if (knn_idx)
+            for (int e = 0; e < k; e++) knn_idx[jq * k + e] = e < N ? (int32_t)rec[row[e]].idx : -1;
+        if (kth_d2 && N > 0) {
+            const pcp_rec q = pcp_load_rec(rec, qi), r = pcp_load_rec(rec, row[N - 1]);
+            kth_d2[jq] = __double2float_ru(pcp_dist2(q.x, q.y, q.z, r.x, r.y, r.z));
+        }
+        tag = ((long long)N << 32) | (long long)(uint32_t)jq;
+        if (N > 3) {
+            double XAve = 0.0, YAve = 0.0, ZAve = 0.0;
+            for (int e = 0; e < N; e++) {
+                const pcp_rec r = pcp_load_rec(rec, row[e]);
+                XAve += r.x;
+                YAve += r.y;
+                ZAve += r.z;
+            }
+            XAve /= (double)N;
+            YAve /= (double)N;
+            ZAve /= (double)N;
+            double s00 = 0, s01 = 0, s02 = 0, s11 = 0, s12 = 0, s22 = 0;
+            for (int e = 0; e < N; e++) {
+                const pcp_rec r = pcp_load_rec(rec, row[e]);
+                const double X = r.x - XAve, Y = r.y - YAve, Z = r.z - ZAve;
+                s00 += X * X;
+                s01 += X * Y;
+                s02 += X * Z;
+                s11 += Y * Y;
+                s12 += Y * Z;
+                s22 += Z * Z;
+            }
+            mom[0 * (size_t)nrows + t] = s00, mom[1 * (size_t)nrows + t] = s01, mom[2 * (size_t)nrows + t] = s02;
+            mom[3 * (size_t)nrows + t] = s11, mom[4 * (size_t)nrows + t] = s12, mom[5 * (size_t)nrows + t] = s22;
+            mom[6 * (size_t)nrows + t] = XAve, mom[7 * (size_t)nrows + t] = YAve, mom[8 * (size_t)nrows + t] = ZAve;
+        }
+    }
+    mom[9 * (size_t)nrows + t] = __longlong_as_double(tag);
+}
+
+static __global__ void __launch_bounds__(128) plane_from_moments_kernel(const double* __restrict__ mom, uint32_t nrows, void* props,
+                                                                        double* eig3, float* lps3)
+{
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= nrows) return;
+    const long long tag = __double_as_longlong(mom[9 * (size_t)nrows + t]);
+    const int N = (int)(tag >> 32);
+    if (N < 0) return;
+    const size_t jq = (size_t)(uint32_t)tag;
+    pcp_plane pl;
+    const bool fitted = N > 3;
+    if (fitted)
+        pcp_plane_from_scatter<true>(mom[0 * (size_t)nrows + t], mom[1 * (size_t)nrows + t], mom[2 * (size_t)nrows + t],
+                                     mom[3 * (size_t)nrows + t], mom[4 * (size_t)nrows + t], mom[5 * (size_t)nrows + t],
+                                     mom[6 * (size_t)nrows + t], mom[7 * (size_t)nrows + t], mom[8 * (size_t)nrows + t], pl);
+    pcp_store_props(props, jq, fitted, pl);
+    pcp_store_extra(eig3, lps3, jq, fitted, pl);
+}
+
 // ---- the same search, one BLOCK per query ----------------------------------------------------------------------
 // For a handful of queries (what the far kernel could not settle: a point metres above a dense surface, whose block
 // holds 10^5 points) the warp kernel's time is the time of its longest query, and a single warp keeps only 4 KB of
