@@ -166,3 +166,19 @@ struct StageTimer {
 void pcp_profile_resolve(pcp_ctx* ctx);
 
 static inline unsigned pcp_blocks_for(size_t n, unsigned threads) { return (unsigned)((n + threads - 1) / threads); }
+
+// 256-bit global loads and stores (LDG.E.256 / STG.E.256, sm_100): one instruction and one L1 wavefront for a 32-byte
+// record; the address must be 32-byte aligned.
+struct pcp_d4 {
+    double a, b, c, d;
+};
+__device__ __forceinline__ pcp_d4 pcp_ld256(const void* p)
+{
+    pcp_d4 v;
+    asm volatile("ld.global.v4.f64 {%0, %1, %2, %3}, [%4];" : "=d"(v.a), "=d"(v.b), "=d"(v.c), "=d"(v.d) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void pcp_st256(void* p, const pcp_d4& v)
+{
+    asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" : : "l"(p), "d"(v.a), "d"(v.b), "d"(v.c), "d"(v.d) : "memory");
+}

@@ -33,19 +33,22 @@ __global__ void __launch_bounds__(256) morton_key_kernel(const char* __restrict_
 __global__ void __launch_bounds__(256) gather_rec_kernel(const char* __restrict__ pts, size_t stride,
                                                          const uint32_t* __restrict__ vals, size_t nv,
                                                          pcp_rec* __restrict__ rec, float4* __restrict__ fpt,
-                                                         double ox, double oy, double oz)
+                                                         double ox, double oy, double oz, int vec)
 {
     size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= nv) return;
     uint32_t o = vals[i];
-    const double* p = reinterpret_cast<const double*>(pts + (size_t)o * stride);
-    pcp_rec r;
-    r.x = p[0];
-    r.y = p[1];
-    r.z = p[2];
-    r.idx = (long long)o;
-    rec[i] = r;
-    fpt[i] = make_float4((float)(r.x - ox), (float)(r.y - oy), (float)(r.z - oz), 0.f);
+    const char* src = pts + (size_t)o * stride;
+    pcp_d4 v;
+    if (vec) { // packed 32-byte records on a 32-byte boundary: one 256-bit load
+        v = pcp_ld256(src);
+    } else {
+        const double* p = reinterpret_cast<const double*>(src);
+        v.a = p[0], v.b = p[1], v.c = p[2];
+    }
+    v.d = __longlong_as_double((long long)o);
+    pcp_st256(rec + i, v); // (x, y, z, idx): the record, in one store
+    fpt[i] = make_float4((float)(v.a - ox), (float)(v.b - oy), (float)(v.c - oz), 0.f);
 }
 
 __global__ void __launch_bounds__(256) cell_flag_kernel(const unsigned long long* __restrict__ keys, size_t nv,
@@ -515,7 +518,8 @@ int pcp_index_build_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t stri
         StageTimer t(ctx, "index.gather", 72.0 * nv);
         gather_rec_kernel<<<pcp_blocks_for(nv, 256), 256, 0, ctx->stream>>>(static_cast<const char*>(dpts), stride,
                                                                           vals, nv, ix->rec, ix->fpt, ix->grid.org[0],
-                                                                          ix->grid.org[1], ix->grid.org[2]);
+                                                                          ix->grid.org[1], ix->grid.org[2],
+                                                                          (stride == 32 && ((uintptr_t)dpts & 31) == 0) ? 1 : 0);
         ctx->launches++;
         IX_CUDA(cudaGetLastError());
     }

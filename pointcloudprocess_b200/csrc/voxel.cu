@@ -83,24 +83,38 @@ __global__ void __launch_bounds__(128) voxel_centroid_kernel(const char* __restr
                                                              const uint32_t* __restrict__ cell_start,
                                                              const uint32_t* __restrict__ m_ptr, int downsample_all,
                                                              char* __restrict__ out, size_t out_stride,
-                                                             int32_t* __restrict__ cell_count, const VoxParams P)
+                                                             int32_t* __restrict__ cell_count, const VoxParams P, int vec)
 {
     uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= *m_ptr) return;
     uint32_t b = cell_start[c], e = cell_start[c + 1];
     double s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    // vec & 1: packed 32-byte input records on a 32-byte boundary -- a record is one 256-bit load; vec & 2: the same for
+    // the output and one store
     for (uint32_t t = b; t < e; t++) {
         const char* rec = pts + (size_t)vals[t] * stride;
-        const double* pp = reinterpret_cast<const double*>(rec);
-        double p[3] = {pp[0], pp[1], pp[2]};
+        double p[3];
+        uint32_t rgba_in = 0, stamp_in = 0;
+        if (vec & 1) {
+            const pcp_d4 v = pcp_ld256(rec);
+            p[0] = v.a, p[1] = v.b, p[2] = v.c;
+            const unsigned long long w = (unsigned long long)__double_as_longlong(v.d);
+            rgba_in = (uint32_t)w, stamp_in = (uint32_t)(w >> 32);
+        } else {
+            const double* pp = reinterpret_cast<const double*>(rec);
+            p[0] = pp[0], p[1] = pp[1], p[2] = pp[2];
+        }
         if (P.use_shift) p[0] = __dadd_rn(p[0], P.shift[0]), p[1] = __dadd_rn(p[1], P.shift[1]), p[2] = __dadd_rn(p[2], P.shift[2]);
         double v[8];
         if (downsample_all) {
             // PointXYZRGBA keeps rgba / stamp_id at bytes 32 / 36; the packed 32-byte record (a PCD binary payload
             // record: x, y, z, rgba, stamp_id) at 24 / 28
             const size_t ao = stride == 32 ? 24 : 32;
-            uint32_t rgba = *reinterpret_cast<const uint32_t*>(rec + ao);
-            uint32_t stamp = *reinterpret_cast<const uint32_t*>(rec + ao + 4);
+            uint32_t rgba = rgba_in, stamp = stamp_in;
+            if (!(vec & 1)) {
+                rgba = *reinterpret_cast<const uint32_t*>(rec + ao);
+                stamp = *reinterpret_cast<const uint32_t*>(rec + ao + 4);
+            }
             v[0] = (double)(float)p[0];
             v[1] = (double)(float)p[1];
             v[2] = (double)(float)p[2];
@@ -128,15 +142,20 @@ __global__ void __launch_bounds__(128) voxel_centroid_kernel(const char* __restr
     double* od = reinterpret_cast<double*>(o);
     if (P.use_shift && isfinite(s[0]) && isfinite(s[1]) && isfinite(s[2])) // transformPointCloud skips the others
         s[0] = __dadd_rn(s[0], P.unshift[0]), s[1] = __dadd_rn(s[1], P.unshift[1]), s[2] = __dadd_rn(s[2], P.unshift[2]);
-    od[0] = s[0];
-    od[1] = s[1];
-    od[2] = s[2];
     uint32_t rgb = 0, stamp = 0;
     if (downsample_all) {
         float r = (float)s[5], g = (float)s[6], bl = (float)s[7];
         rgb = (uint32_t)(((int)r << 16) | ((int)g << 8) | (int)bl);
         stamp = (uint32_t)s[4]; // cvt.rzi.u32.f64 == static_cast<uint32_t> for in-range values
     }
+    if ((vec & 2) && downsample_all) { // packed record on a 32-byte boundary: one store
+        pcp_st256(o, pcp_d4{s[0], s[1], s[2], __longlong_as_double((long long)((unsigned long long)rgb | ((unsigned long long)stamp << 32)))});
+        if (cell_count) cell_count[c] = (int32_t)(e - b);
+        return;
+    }
+    od[0] = s[0];
+    od[1] = s[1];
+    od[2] = s[2];
     if (out_stride == 32 && downsample_all) { // packed record: no w, no padding
         *reinterpret_cast<uint32_t*>(o + 24) = rgb;
         *reinterpret_cast<uint32_t*>(o + 28) = stamp;
@@ -276,7 +295,8 @@ int pcp_voxel_grid_device(pcp_ctx* ctx, const void* dpts, size_t n, size_t strid
         // grid sized for the worst case M == nv; threads beyond *m_ptr exit
         voxel_centroid_kernel<<<pcp_blocks_for(nv, 128), 128, 0, ctx->stream>>>(
             static_cast<const char*>(dpts), stride, vals, cell_start.p, m_dev.p, downsample_all,
-            static_cast<char*>(dout), out_stride, d_cell_count, P);
+            static_cast<char*>(dout), out_stride, d_cell_count, P,
+            ((stride == 32 && ((uintptr_t)dpts & 31) == 0) ? 1 : 0) | ((out_stride == 32 && ((uintptr_t)dout & 31) == 0) ? 2 : 0));
         PCP_LAUNCH_CHECK(ctx);
     }
     uint32_t m = 0;
