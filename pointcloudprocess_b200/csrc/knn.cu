@@ -199,10 +199,13 @@ extern "C" int pcp_features_knn_ex(const pcp_index* ix, int k, int64_t query_lim
     if (nv > 0 && kk > 0) {
         DevBuf<uint32_t> fail_list, counters;
         DevBuf<float> fail_u;
-        PCP_TRY(fail_list.alloc(ctx, nv));
-        PCP_TRY(fail_u.alloc(ctx, nv));
+        // (room for every query once, plus the ones the re-rank kernel puts back after the third pass had struck them:
+        // at most its list's capacity, nv / 16)
+        const size_t nfar_max = nv + nv / 16 + 1024;
+        PCP_TRY(fail_list.alloc(ctx, nfar_max));
+        PCP_TRY(fail_u.alloc(ctx, nfar_max));
         DevBuf<uint32_t> fail2;
-        PCP_TRY(fail2.alloc(ctx, nv));
+        PCP_TRY(fail2.alloc(ctx, nfar_max));
         PCP_TRY(counters.alloc(ctx, 12));
         PCP_CUDA_TRY(ctx, cudaMemsetAsync(counters.p, 0, 48, ctx->stream));
         uint32_t nfail = 0;
